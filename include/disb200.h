@@ -1,0 +1,145 @@
+/* disb200 — C-ABI of the B200-native DIS optical-flow / depth-from-stereo hot path.
+ *
+ * Drop-in boundary for lordnn/OF_DIS (reference paths are relative to the upstream tree):
+ *   - the parameter block mirrors the 20 positional CLI parameters of run_dense.cpp:272-292
+ *     plus the two compile-time switches SELECTMODE / SELECTCHANNEL (CMakeLists.txt:38-61);
+ *   - disb200_ofclass      replaces the OFC::OFClass constructor (oflow.h:99-126; only call
+ *                          site run_dense.cpp:392-401): same padded host pyramids in, same
+ *                          low-resolution interleaved flow out;
+ *   - disb200_run_batch*   replace main() of run_dense.cpp:297-415 between imread and the file
+ *                          writers: dimension padding, ConstructImgPyramide, OFClass, final
+ *                          upsample and crop, for a batch of independent frame pairs;
+ *   - disb200_save_flo / disb200_save_pfm replace SaveFlowFile / SavePFMFile
+ *                          (run_dense.cpp:17-82).
+ * All functions return 0 on success and a non-zero DISB200_E* code otherwise (the reference
+ * has no error path: void ctor, exit(1) on OOM — image.cpp:25-41); disb200_last_error()
+ * returns a thread-local message.  No function ever falls back to a CPU implementation:
+ * without a CUDA device every compute entry point fails with DISB200_ECUDA.
+ */
+#ifndef DISB200_H_
+#define DISB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+  DISB200_OK = 0,
+  DISB200_EINVAL = 1,   /* bad dimensions / parameters */
+  DISB200_ECUDA = 2,    /* CUDA runtime error or no device */
+  DISB200_ENOMEM = 3,   /* device or host allocation failed */
+  DISB200_EUNSUPPORTED = 4, /* parameter combination the kernels do not cover */
+  DISB200_EIO = 5
+};
+
+enum { DISB200_MODE_OF = 1, DISB200_MODE_DE = 2 };       /* SELECTMODE    (patch.h:28-34) */
+enum { DISB200_SOR_LEXICOGRAPHIC = 0, DISB200_SOR_REDBLACK = 1 };
+
+/* run_dense.cpp:272-292 in CLI order, then the compile-time variant selectors. */
+typedef struct DisParams {
+  int sc_f;          /* coarsest scale                                   (argv 4) */
+  int sc_l;          /* finest scale                                     (argv 5) */
+  int max_iter;      /* inverse-search iterations, upper bound            (6) */
+  int min_iter;      /*                            lower bound            (7) */
+  float dp_thresh;   /* min rate of change of the step norm               (8) */
+  float dr_thresh;   /* min rate of change of the residual                (9) */
+  float res_thresh;  /* stop when mean |residual| falls below            (10) */
+  int patchsz;       /* patch edge length in px; also the level padding   (11) */
+  float patove;      /* patch overlap in [0,1)                            (12) */
+  int usefbcon;      /* forward-backward merging                          (13) */
+  int patnorm;       /* mean-normalise patches                            (14) */
+  int costfct;       /* 0 L2, 1 L1, 2 pseudo-Huber, 10 NCC                (15) */
+  int usetvref;      /* variational refinement on/off                     (16) */
+  float tv_alpha;    /* smoothness weight                                 (17) */
+  float tv_gamma;    /* gradient-constancy weight                         (18) */
+  float tv_delta;    /* colour-constancy weight                           (19) */
+  int tv_innerit;    /* fixed-point iterations (x (level+1))              (20) */
+  int tv_solverit;   /* SOR sweeps per fixed-point iteration              (21) */
+  float tv_sor;      /* SOR omega                                         (22) */
+  int verbosity;     /* 0 silent, 1 total time, 2 per-scale times         (23) */
+  int mode;          /* DISB200_MODE_OF | DISB200_MODE_DE  (SELECTMODE)        */
+  int channels;      /* 1 grey | 3 BGR interleaved        (SELECTCHANNEL)     */
+  int sor_mode;      /* DISB200_SOR_LEXICOGRAPHIC (parity with solver.c:83-433) | _REDBLACK */
+} DisParams;
+
+typedef struct DisHandle DisHandle;
+
+/* Operating points 1..4 of run_dense.cpp:226-268 (anything else selects 2), including
+ * AutoFirstScaleSelect (run_dense.cpp:181-184) on the unpadded image width. */
+int disb200_operating_point(int op, int width, int mode, int channels, DisParams* out);
+
+/* Dimension padding of run_dense.cpp:299-312: W,H = dimensions padded to a multiple of
+ * 2^sc_f, padl/padt = columns/rows added on the left/top (floor(pad/2)). */
+int disb200_padded_dims(int w0, int h0, int sc_f, int* W, int* H, int* padl, int* padt);
+
+/* Number of devices visible to the library (0 when there is no GPU or no driver). */
+int disb200_device_count(void);
+
+/* One handle per (GPU, stream set): owns every device workspace for batches of up to
+ * max_batch pairs of w0 x h0 x channels u8 frames.  No allocation happens in run_batch*. */
+int disb200_create(const DisParams* params, int w0, int h0, int max_batch, int device, DisHandle** out);
+int disb200_destroy(DisHandle* h);
+
+/* Host-side batch: imgA[i], imgB[i] are h0*w0*channels u8 (row-major, channels interleaved,
+ * BGR like cv::imread), out[i] receives h0*w0*nop f32 (nop = 2 for OF: u,v interleaved; 1 for
+ * DE).  Includes the host->device and device->host copies; returns when out[] is complete.
+ * n may exceed max_batch (processed in chunks). */
+int disb200_run_batch(DisHandle* h, const uint8_t* const* imgA, const uint8_t* const* imgB, int n, float* const* out);
+
+/* Same, but frames and results are contiguous in pinned or pageable host memory:
+ * A, B: n*h0*w0*channels u8; out: n*h0*w0*nop f32.  Chunks are double-buffered so copies
+ * overlap compute. */
+int disb200_run_batch_host(DisHandle* h, const uint8_t* A, const uint8_t* B, int n, float* out);
+
+/* Device-resident batch (n <= max_batch): dA, dB, dOut are device pointers laid out as above.
+ * Asynchronous on the handle's stream; call disb200_sync before reading dOut. */
+int disb200_run_batch_device(DisHandle* h, const uint8_t* dA, const uint8_t* dB, int n, float* dOut);
+int disb200_sync(DisHandle* h);
+
+/* CUDA-event stopwatch on the handle's stream (the stream every kernel is launched on). */
+int disb200_timer_begin(DisHandle* h);
+int disb200_timer_end(DisHandle* h, float* elapsed_ms);
+/* Kernels launched by the most recent run_batch* call on this handle. */
+int disb200_last_launch_count(const DisHandle* h);
+/* Device time in ms the most recent run spent in stage s (0 pyramid, 1 inverse search,
+ * 2 densification, 3 variational refinement, 4 upsample); only recorded while
+ * disb200_set_stage_timing(h, 1) is on (it serialises the stream with events). */
+int disb200_set_stage_timing(DisHandle* h, int on);
+int disb200_stage_ms(const DisHandle* h, int stage, float* ms);
+
+/* Intermediate results of the most recent run (parity tests): copies to host
+ *   kind 0/1/2 : padded pyramid image / dx / dy of frame `which` (0 = A, 1 = B) at `level`
+ *   kind 3     : dense flow of direction `which` (0 fw, 1 bw) at `level` after refinement
+ *   kind 4/5/6 : per-patch p_iter / pt_iter / pweight of direction `which` at level sc_l
+ * nbytes must equal the size of the object; see INTEGRATION.md for shapes. */
+int disb200_fetch(DisHandle* h, int kind, int which, int level, int pair, void* dst, size_t nbytes);
+
+/* OFClass-level entry (oflow.h:99-126), one pair, padded host pyramids valid for levels
+ * sc_l..sc_f; outflow: (H>>sc_l)*(W>>sc_l)*nop f32; initflow optional (may be NULL). */
+int disb200_ofclass(const DisParams* params, const float* const* im_ao, const float* const* im_ao_dx,
+                    const float* const* im_ao_dy, const float* const* im_bo, const float* const* im_bo_dx,
+                    const float* const* im_bo_dy, int W, int H, float* outflow, const float* initflow);
+
+/* VarRefClass-level entry (refine_variational.h:35-37): refine `flow` (h_l*w_l*nop, in place)
+ * on one level given the padded level images of both frames. */
+int disb200_varref_level(const DisParams* params, const float* im_a, const float* im_b, int w_l, int h_l,
+                         int level, int camlr, float* flow);
+
+/* File writers with the reference's framing (run_dense.cpp:17-82). */
+int disb200_save_flo(const char* path, const float* flow, int w, int h, int nc);
+int disb200_save_pfm(const char* path, const float* disp, int w, int h);
+/* Binary PGM (P5) / PPM (P6) reader standing in for cv::imread (run_dense.cpp:209-210):
+ * want_channels 1 -> grey, 3 -> BGR interleaved.  *data is malloc'ed; release with disb200_free. */
+int disb200_read_pnm(const char* path, int want_channels, uint8_t** data, int* w, int* h);
+void disb200_free(void* p);
+
+const char* disb200_last_error(void);
+const char* disb200_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DISB200_H_ */

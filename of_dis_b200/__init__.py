@@ -1,0 +1,253 @@
+"""of_dis_b200 - Python host bindings of libdisb200.so (include/disb200.h).
+
+The product is the CUDA library; this module is the thin ctypes layer the tests and bench.py
+call it through.  It never computes anything itself and has no CPU path: if the shared
+library is missing, or there is no CUDA device, the calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libdisb200.so")
+
+MODE_OF, MODE_DE = 1, 2
+SOR_LEXICOGRAPHIC, SOR_REDBLACK = 0, 1
+STAGES = ("pyramid", "inverse_search", "densify", "varref", "upsample")
+
+
+class DisError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("disb200 error %d: %s" % (code, msg))
+        self.code = code
+
+
+class DisParams(C.Structure):
+    """Mirror of struct DisParams (run_dense.cpp:272-292 order + mode/channels/sor_mode)."""
+    _fields_ = [
+        ("sc_f", C.c_int), ("sc_l", C.c_int), ("max_iter", C.c_int), ("min_iter", C.c_int),
+        ("dp_thresh", C.c_float), ("dr_thresh", C.c_float), ("res_thresh", C.c_float),
+        ("patchsz", C.c_int), ("patove", C.c_float),
+        ("usefbcon", C.c_int), ("patnorm", C.c_int), ("costfct", C.c_int), ("usetvref", C.c_int),
+        ("tv_alpha", C.c_float), ("tv_gamma", C.c_float), ("tv_delta", C.c_float),
+        ("tv_innerit", C.c_int), ("tv_solverit", C.c_int), ("tv_sor", C.c_float),
+        ("verbosity", C.c_int), ("mode", C.c_int), ("channels", C.c_int), ("sor_mode", C.c_int),
+    ]
+
+    def copy(self, **kw):
+        q = DisParams()
+        C.memmove(C.byref(q), C.byref(self), C.sizeof(DisParams))
+        for k, v in kw.items():
+            setattr(q, k, v)
+        return q
+
+    @property
+    def nop(self):
+        return 2 if self.mode == MODE_OF else 1
+
+    def cli_args(self):
+        """The 20 positional parameters in the reference's CLI order."""
+        return [self.sc_f, self.sc_l, self.max_iter, self.min_iter, self.dp_thresh, self.dr_thresh, self.res_thresh,
+                self.patchsz, self.patove, self.usefbcon, self.patnorm, self.costfct, self.usetvref, self.tv_alpha,
+                self.tv_gamma, self.tv_delta, self.tv_innerit, self.tv_solverit, self.tv_sor, self.verbosity]
+
+
+_lib = None
+
+
+def lib():
+    """Load libdisb200.so; raises if it has not been built (no fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError("%s is missing: run `python -m of_dis_b200.build` (needs nvcc). "
+                              "There is no CPU implementation to fall back to." % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        L.disb200_last_error.restype = C.c_char_p
+        L.disb200_version.restype = C.c_char_p
+        L.disb200_free.restype = None
+        _lib = L
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise DisError(rc, lib().disb200_last_error().decode())
+
+
+def _ptr(a, t=C.c_float):
+    return None if a is None else a.ctypes.data_as(C.POINTER(t))
+
+
+def operating_point(op: int, width: int, mode: int = MODE_OF, channels: int = 1) -> DisParams:
+    p = DisParams()
+    _check(lib().disb200_operating_point(op, width, mode, channels, C.byref(p)))
+    return p
+
+
+def padded_dims(w0: int, h0: int, sc_f: int):
+    W, H, pl, pt = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+    _check(lib().disb200_padded_dims(w0, h0, sc_f, C.byref(W), C.byref(H), C.byref(pl), C.byref(pt)))
+    return W.value, H.value, pl.value, pt.value
+
+
+def device_count() -> int:
+    return lib().disb200_device_count()
+
+
+class Handle:
+    """disb200_create / run_batch* / destroy."""
+
+    def __init__(self, params: DisParams, w0: int, h0: int, max_batch: int = 1, device: int = 0):
+        self.p = params.copy()
+        self.w0, self.h0, self.max_batch, self.device = w0, h0, max_batch, device
+        self.h = C.c_void_p()
+        _check(lib().disb200_create(C.byref(self.p), w0, h0, max_batch, device, C.byref(self.h)))
+        self.W, self.H, self.padl, self.padt = padded_dims(w0, h0, params.sc_f)
+
+    def close(self):
+        if self.h:
+            lib().disb200_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # -- host buffers (numpy) ---------------------------------------------------------------
+    def run_host(self, A: np.ndarray, B: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
+        """A, B: uint8 (n, h0, w0[, C]) contiguous; returns float32 (n, h0, w0, nop)."""
+        n = A.shape[0]
+        assert A.dtype == np.uint8 and B.dtype == np.uint8 and A.flags.c_contiguous and B.flags.c_contiguous
+        assert A.size == n * self.h0 * self.w0 * self.p.channels and B.shape == A.shape
+        if out is None:
+            out = np.empty((n, self.h0, self.w0, self.p.nop), np.float32)
+        _check(lib().disb200_run_batch_host(self.h, _ptr(A, C.c_uint8), _ptr(B, C.c_uint8), n, _ptr(out)))
+        return out
+
+    def run_host_ptr(self, a_ptr: int, b_ptr: int, n: int, out_ptr: int):
+        _check(lib().disb200_run_batch_host(self.h, C.c_void_p(a_ptr), C.c_void_p(b_ptr), n, C.c_void_p(out_ptr)))
+
+    def run_list(self, As, Bs):
+        n = len(As)
+        outs = [np.empty((self.h0, self.w0, self.p.nop), np.float32) for _ in range(n)]
+        pa = (C.POINTER(C.c_uint8) * n)(*[_ptr(a, C.c_uint8) for a in As])
+        pb = (C.POINTER(C.c_uint8) * n)(*[_ptr(b, C.c_uint8) for b in Bs])
+        po = (C.POINTER(C.c_float) * n)(*[_ptr(o) for o in outs])
+        _check(lib().disb200_run_batch(self.h, pa, pb, n, po))
+        return outs
+
+    # -- device buffers (raw pointers, e.g. torch tensor .data_ptr()) --------------------------
+    def run_device(self, dA: int, dB: int, n: int, dOut: int):
+        _check(lib().disb200_run_batch_device(self.h, C.c_void_p(dA), C.c_void_p(dB), n, C.c_void_p(dOut)))
+
+    def sync(self):
+        _check(lib().disb200_sync(self.h))
+
+    def timer_begin(self):
+        _check(lib().disb200_timer_begin(self.h))
+
+    def timer_end(self) -> float:
+        ms = C.c_float()
+        _check(lib().disb200_timer_end(self.h, C.byref(ms)))
+        return ms.value
+
+    def launch_count(self) -> int:
+        return lib().disb200_last_launch_count(self.h)
+
+    def set_stage_timing(self, on: bool):
+        _check(lib().disb200_set_stage_timing(self.h, int(on)))
+
+    def stage_ms(self):
+        out = {}
+        for i, name in enumerate(STAGES):
+            ms = C.c_float()
+            _check(lib().disb200_stage_ms(self.h, i, C.byref(ms)))
+            out[name] = ms.value
+        return out
+
+    # -- intermediates ---------------------------------------------------------------------
+    def level_shape(self, level):
+        return self.H >> level, self.W >> level
+
+    def fetch_pyramid(self, which: int, level: int, pair: int = 0):
+        hl, wl = self.level_shape(level)
+        pad = self.p.patchsz
+        outs = []
+        for kind in range(3):
+            a = np.empty((hl + 2 * pad, wl + 2 * pad, self.p.channels), np.float32)
+            _check(lib().disb200_fetch(self.h, kind, which, level, pair, _ptr(a), C.c_size_t(a.nbytes)))
+            outs.append(a)
+        return outs
+
+    def fetch_flow(self, which: int, level: int, pair: int = 0):
+        hl, wl = self.level_shape(level)
+        a = np.empty((hl, wl, self.p.nop), np.float32)
+        _check(lib().disb200_fetch(self.h, 3, which, level, pair, _ptr(a), C.c_size_t(a.nbytes)))
+        return a
+
+    def fetch_patches(self, which: int = 0, pair: int = 0):
+        hl, wl = self.level_shape(self.p.sc_l)
+        steps = max(1, int(np.floor(np.float32(self.p.patchsz) * (np.float32(1) - np.float32(self.p.patove)))))
+        n = int(np.ceil(np.float32(wl) / np.float32(steps))) * int(np.ceil(np.float32(hl) / np.float32(steps)))
+        nv = self.p.channels * self.p.patchsz ** 2
+        r = {"p_iter": np.empty((n, self.p.nop), np.float32), "pt_iter": np.empty((n, 2), np.float32),
+             "pweight": np.empty((n, nv), np.float32)}
+        for kind, key in ((4, "p_iter"), (5, "pt_iter"), (6, "pweight")):
+            _check(lib().disb200_fetch(self.h, kind, which, self.p.sc_l, pair, _ptr(r[key]), C.c_size_t(r[key].nbytes)))
+        return r
+
+
+def ofclass(params: DisParams, A, B, W: int, H: int, initflow=None) -> np.ndarray:
+    """OFClass-level entry: A, B are (img, dx, dy) dict triples {level: ndarray} of padded arrays."""
+    fp = C.POINTER(C.c_float)
+    ptrs = []
+    for d in (*A, *B):
+        arr = (fp * (params.sc_f + 1))()
+        for l, a in d.items():
+            assert a.dtype == np.float32 and a.flags.c_contiguous
+            arr[l] = a.ctypes.data_as(fp)
+        ptrs.append(arr)
+    out = np.zeros((H >> params.sc_l, W >> params.sc_l, params.nop), np.float32)
+    _check(lib().disb200_ofclass(C.byref(params), *ptrs, W, H, _ptr(out), _ptr(initflow)))
+    return out
+
+
+def varref_level(params: DisParams, im_a, im_b, w_l: int, h_l: int, level: int, camlr: int, flow) -> np.ndarray:
+    flow = np.ascontiguousarray(flow, np.float32).copy()
+    _check(lib().disb200_varref_level(C.byref(params), _ptr(im_a), _ptr(im_b), w_l, h_l, level, camlr, _ptr(flow)))
+    return flow
+
+
+def save_flo(path: str, flow: np.ndarray):
+    flow = np.ascontiguousarray(flow, np.float32)
+    h, w = flow.shape[:2]
+    nc = 1 if flow.ndim == 2 else flow.shape[2]
+    _check(lib().disb200_save_flo(path.encode(), _ptr(flow), w, h, nc))
+
+
+def save_pfm(path: str, disp: np.ndarray):
+    disp = np.ascontiguousarray(disp, np.float32)
+    h, w = disp.shape[:2]
+    _check(lib().disb200_save_pfm(path.encode(), _ptr(disp), w, h))
+
+
+def read_pnm(path: str, channels: int) -> np.ndarray:
+    data = C.POINTER(C.c_uint8)()
+    w, h = C.c_int(), C.c_int()
+    _check(lib().disb200_read_pnm(path.encode(), channels, C.byref(data), C.byref(w), C.byref(h)))
+    n = w.value * h.value * channels
+    arr = np.ctypeslib.as_array(data, shape=(n,)).copy()
+    lib().disb200_free(data)
+    return arr.reshape((h.value, w.value) if channels == 1 else (h.value, w.value, 3))

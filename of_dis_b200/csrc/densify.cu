@@ -1,0 +1,189 @@
+// Stage 3 — densification, PatGridClass::AggregateFlowDense (patchgrid.cpp:213-397), recast
+// from the reference's sequential scatter into a deterministic per-pixel gather.
+//
+// Forward part: the patches covering pixel (x, y) sit on a regular grid, so the pixel
+// enumerates them directly, in ascending patch index ip = gx * noph + gy — the order in which
+// the reference's scatter loop adds them — and divides by the weight sum in the same thread
+// (the normalisation loop of patchgrid.cpp:377-394 is fused).
+//
+// Forward-backward merging (cg != null): patches of the complementary grid are splatted
+// around their END positions, which are irregular.  They are first binned by the cell
+// (cell edge = patch size) holding their top-left tap, the per-cell lists are sorted by patch
+// index, and each pixel then visits the (at most) four cells that can reach it, in a fixed
+// cell order.  The result is deterministic; its summation order differs from the reference's
+// global patch order only by fp32 rounding.
+#include "dis_internal.h"
+
+namespace disb200 {
+
+namespace {
+
+// RGB pointer desync of the reference (patchgrid.cpp:243,255-258 and 320,333-334): the weight
+// pointer advances by one per patch pixel plus two more only for pixels that pass the
+// in-image test.  Returns the weight offset of patch pixel (r, c) given the rectangle
+// [c_lo, c_hi] x [r_lo, r_hi] of patch pixels that pass the test (empty if lo > hi).
+__device__ __forceinline__ int rgb_weight_offset(int r, int c, int psz, int c_lo, int c_hi, int r_lo, int r_hi) {
+  const int ncols = max(0, c_hi - c_lo + 1);
+  const int rows_before = max(0, min(r - 1, r_hi) - r_lo + 1);   // fully processed in-range rows above r
+  int inside_before = rows_before * ncols;
+  if (r >= r_lo && r <= r_hi) inside_before += max(0, min(c - 1, c_hi) - c_lo + 1);
+  return (r * psz + c) + 2 * inside_before;
+}
+
+template <int C, int NOP>
+__global__ void densify_kernel(DensifyArgs a, LevelGeom g, OptConst o) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, pair = blockIdx.z;
+  if (x >= g.w) return;
+  const int psz = o.psz, lb = -psz / 2, ub = psz / 2 - 1, nv = o.novals;
+  const float* P = a.p_iter + (size_t)pair * g.npatch * NOP;
+  const float* Wt = a.pweight + (size_t)pair * g.npatch * nv;
+  float we = 0.f, f0 = 0.f, f1 = 0.f;
+
+  // grid columns gx with  gx*steps + offw + lb <= x <= gx*steps + offw + ub
+  const int ax = x - g.offw, ay = y - g.offh;
+  int gx_lo = (ax - ub + g.steps - 1 >= 0) ? (ax - ub + g.steps - 1) / g.steps : 0;
+  int gx_hi = (ax - lb >= 0) ? (ax - lb) / g.steps : -1;
+  int gy_lo = (ay - ub + g.steps - 1 >= 0) ? (ay - ub + g.steps - 1) / g.steps : 0;
+  int gy_hi = (ay - lb >= 0) ? (ay - lb) / g.steps : -1;
+  gx_hi = min(gx_hi, g.nopw - 1);
+  gy_hi = min(gy_hi, g.noph - 1);
+  for (int gx = gx_lo; gx <= gx_hi; ++gx) {
+    const int px = gx * g.steps + g.offw;
+    const int c = x - px - lb;
+    for (int gy = gy_lo; gy <= gy_hi; ++gy) {
+      const int py = gy * g.steps + g.offh;
+      const int r = y - py - lb;
+      const int ip = gx * g.noph + gy;
+      const float* pw = Wt + (size_t)ip * nv;
+      float absw;
+      if (C == 1) {
+        absw = 1.0f / fmaxf(o.minerrval, __ldg(pw + r * psz + c));
+      } else {
+        const int c_lo = max(0, -(px + lb)), c_hi = min(psz - 1, g.w - 1 - (px + lb));
+        const int r_lo = max(0, -(py + lb)), r_hi = min(psz - 1, g.h - 1 - (py + lb));
+        const int off = rgb_weight_offset(r, c, psz, c_lo, c_hi, r_lo, r_hi);
+        absw = fmaxf(o.minerrval, __ldg(pw + off));
+        absw += fmaxf(o.minerrval, __ldg(pw + off + 1));
+        absw += fmaxf(o.minerrval, __ldg(pw + off + 2));
+        absw = 1.0f / absw;
+      }
+      we += absw;
+      f0 += __ldg(P + (size_t)ip * NOP) * absw;
+      if (NOP == 2) f1 += __ldg(P + (size_t)ip * NOP + 1) * absw;
+    }
+  }
+
+  if (a.cg_p_iter) {
+    // backward merge: gather from the binned complementary patches (patchgrid.cpp:278-375)
+    const float* CP = a.cg_p_iter + (size_t)pair * g.npatch * NOP;
+    const float* CT = a.cg_pt_iter + (size_t)pair * g.npatch * 2;
+    const float* CW = a.cg_pweight + (size_t)pair * g.npatch * nv;
+    const int ncx = (g.w + 2 * psz) / psz + 2, ncy = (g.h + 2 * psz) / psz + 2;
+    const int* cnt = a.cell_count + (size_t)pair * ncx * ncy;
+    const int* lst = a.cell_list + (size_t)pair * ncx * ncy * a.cell_cap;
+    // anchor (top-left tap) ax0 = pos0 + lb - 1 reaches pixels ax0 .. ax0 + psz
+    const int cx1 = (x + 2 * psz) / psz, cx0 = (x - psz + 2 * psz) / psz;
+    const int cy1 = (y + 2 * psz) / psz, cy0 = (y - psz + 2 * psz) / psz;
+    for (int cy = cy0; cy <= cy1; ++cy)
+      for (int cx = cx0; cx <= cx1; ++cx) {
+        if (cx < 0 || cy < 0 || cx >= ncx || cy >= ncy) continue;
+        const int cell = cy * ncx + cx;
+        const int m = min(cnt[cell], a.cell_cap);
+        for (int e = 0; e < m; ++e) {
+          const int ip = lst[(size_t)cell * a.cell_cap + e];
+          const float rx = __ldg(CT + 2 * ip), ry = __ldg(CT + 2 * ip + 1);
+          const int pos0 = (int)ceil((double)rx + .00001), pos1 = (int)ceil((double)ry + .00001);
+          const float fx = floorf(rx), fy = floorf(ry);
+          const float r0 = rx - fx, r1 = ry - fy;
+          const float wb[4] = {r0 * r1, (1.f - r0) * r1, r0 * (1.f - r1), (1.f - r0) * (1.f - r1)};
+          // the four taps of patch pixel (xt, yt): cc (xt,yt), fc (xt-1,yt), cf (xt,yt-1), ff (xt-1,yt-1)
+          const int c_lo = max(0, 1 - (pos0 + lb)), c_hi = min(psz - 1, g.w - 2 - (pos0 + lb));
+          const int r_lo = max(0, 1 - (pos1 + lb)), r_hi = min(psz - 1, g.h - 2 - (pos1 + lb));
+          const float* pw = CW + (size_t)ip * nv;
+          const float p0 = __ldg(CP + (size_t)ip * NOP), p1 = NOP == 2 ? __ldg(CP + (size_t)ip * NOP + 1) : 0.f;
+#pragma unroll
+          for (int tpi = 0; tpi < 4; ++tpi) {
+            const int xt = x + (tpi & 1), yt = y + (tpi >> 1);      // tap 0 cc, 1 fc, 2 cf, 3 ff
+            const int c = xt - pos0 - lb, r = yt - pos1 - lb;
+            if (c < c_lo || c > c_hi || r < r_lo || r > r_hi) continue;
+            float absw;
+            if (C == 1) {
+              absw = 1.0f / fmaxf(o.minerrval, __ldg(pw + r * psz + c));
+            } else {
+              const int off = rgb_weight_offset(r, c, psz, c_lo, c_hi, r_lo, r_hi);
+              absw = fmaxf(o.minerrval, __ldg(pw + off));
+              absw += fmaxf(o.minerrval, __ldg(pw + off + 1));
+              absw += fmaxf(o.minerrval, __ldg(pw + off + 2));
+              absw = 1.0f / absw;
+            }
+            we += wb[tpi] * absw;
+            f0 -= wb[tpi] * (p0 * absw);
+            if (NOP == 2) f1 -= wb[tpi] * (p1 * absw);
+          }
+        }
+      }
+  }
+
+  if (we > 0.f) { f0 /= we; f1 /= we; }
+  float* out = a.flow + ((size_t)pair * g.w * g.h + (size_t)y * g.w + x) * NOP;
+  out[0] = f0;
+  if (NOP == 2) out[1] = f1;
+}
+
+// ---- binning of the complementary grid's end positions ----------------------------------
+__global__ void bin_count_kernel(const float* __restrict__ pt_iter, int npatch, int psz, int w, int h, int* cell_count,
+                                 int* cell_list, int cap) {
+  const int ip = blockIdx.x * blockDim.x + threadIdx.x, pair = blockIdx.y;
+  if (ip >= npatch) return;
+  const float rx = pt_iter[((size_t)pair * npatch + ip) * 2], ry = pt_iter[((size_t)pair * npatch + ip) * 2 + 1];
+  const int ncx = (w + 2 * psz) / psz + 2, ncy = (h + 2 * psz) / psz + 2;
+  const int pos0 = (int)ceil((double)rx + .00001), pos1 = (int)ceil((double)ry + .00001);
+  const int ax = pos0 - psz / 2 - 1 + 2 * psz, ay = pos1 - psz / 2 - 1 + 2 * psz;
+  if (ax < 0 || ay < 0) return;   // cannot reach the image
+  const int cx = ax / psz, cy = ay / psz;
+  if (cx >= ncx || cy >= ncy) return;
+  const int cell = cy * ncx + cx;
+  const int slot = atomicAdd(cell_count + (size_t)pair * ncx * ncy + cell, 1);
+  if (slot < cap) cell_list[((size_t)pair * ncx * ncy + cell) * cap + slot] = ip;
+}
+
+__global__ void bin_sort_kernel(int* cell_count, int* cell_list, int ncell, int cap, int* overflow) {
+  const int cell = blockIdx.x * blockDim.x + threadIdx.x, pair = blockIdx.y;
+  if (cell >= ncell) return;
+  const int m_raw = cell_count[(size_t)pair * ncell + cell];
+  if (m_raw > cap) atomicMax(overflow, m_raw);
+  const int m = min(m_raw, cap);
+  int* l = cell_list + ((size_t)pair * ncell + cell) * cap;
+  for (int i = 1; i < m; ++i) {   // insertion sort, lists are a handful of entries
+    const int v = l[i];
+    int k = i - 1;
+    while (k >= 0 && l[k] > v) { l[k + 1] = l[k]; --k; }
+    l[k + 1] = v;
+  }
+}
+
+}  // namespace
+
+void launch_densify(const DensifyArgs& a, const LevelGeom& g, const OptConst& o, int n, cudaStream_t s,
+                    LaunchStats* st) {
+  if (a.cg_p_iter) {
+    const int ncx = (g.w + 2 * o.psz) / o.psz + 2, ncy = (g.h + 2 * o.psz) / o.psz + 2;
+    cudaMemsetAsync(a.cell_count, 0, sizeof(int) * (size_t)ncx * ncy * n, s);
+    bin_count_kernel<<<dim3((g.npatch + 127) / 128, n), 128, 0, s>>>(a.cg_pt_iter, g.npatch, o.psz, g.w, g.h,
+                                                                      a.cell_count, a.cell_list, a.cell_cap);
+    bin_sort_kernel<<<dim3((ncx * ncy + 127) / 128, n), 128, 0, s>>>(a.cell_count, a.cell_list, ncx * ncy, a.cell_cap,
+                                                                     a.overflow);
+    st->launches += 3;
+  }
+  dim3 blk(128), grd((g.w + 127) / 128, g.h, n);
+  if (o.noc == 1) {
+    if (o.nop == 2) densify_kernel<1, 2><<<grd, blk, 0, s>>>(a, g, o);
+    else densify_kernel<1, 1><<<grd, blk, 0, s>>>(a, g, o);
+  } else {
+    if (o.nop == 2) densify_kernel<3, 2><<<grd, blk, 0, s>>>(a, g, o);
+    else densify_kernel<3, 1><<<grd, blk, 0, s>>>(a, g, o);
+  }
+  st->launches++;
+}
+
+}  // namespace disb200

@@ -1,0 +1,112 @@
+// Internal declarations shared by the kernels and the engine.
+#ifndef DISB200_INTERNAL_H_
+#define DISB200_INTERNAL_H_
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/disb200.h"
+
+namespace disb200 {
+
+// Derived constants of one pyramid level: camparam (oflow.h:30-43, oflow.cpp:139-157) and the
+// patch grid of PatGridClass::PatGridClass (patchgrid.cpp:31-76).
+struct LevelGeom {
+  int level;
+  int w, h;          // level size (of the padded-to-divisible frame)
+  int pad;           // imgpadding == patch size
+  int tw, th;        // w + 2 pad, h + 2 pad
+  int nopw, noph, npatch;
+  int offw, offh;    // grid offsets
+  int steps;
+  float lb, ubw, ubh;
+  size_t img_elems;  // tw*th*C
+};
+
+// optparam (oflow.h:45-91, oflow.cpp:75-107)
+struct OptConst {
+  int psz, noc, nop, novals, steps;
+  int max_iter, min_iter, patnorm, costfct, mode;
+  float dp_thresh_sq, dr_thresh, res_thresh, outlierthresh;
+  float minerrval, normoutlier;
+};
+
+OptConst make_optconst(const DisParams& p);
+LevelGeom make_levelgeom(const DisParams& p, int W, int H, int level);
+
+// Launch bookkeeping (gpu_launches in bench.py is read from here).
+struct LaunchStats {
+  int launches;
+};
+
+// ---- stage 1: pyramid -------------------------------------------------------------------
+// u8 frames [n][h0][w0][C] -> padded level image of level `lvl` (2^lvl x 2^lvl box mean of
+// the replicate-padded frame), then Sobel/8 + border fill.  Exact for any lvl <= 8.
+void launch_downscale_u8(const uint8_t* frames, int n, int w0, int h0, int C, int padl, int padt, int lvl,
+                         const LevelGeom& g, float* img, cudaStream_t s, LaunchStats* st);
+// level image (padded array, interior valid) -> next coarser level image interior (2x2 mean)
+void launch_halve(const float* src, const LevelGeom& gs, float* dst, const LevelGeom& gd, int n, int C,
+                  cudaStream_t s, LaunchStats* st);
+// interior of img valid -> fill replicate border of img, write dx, dy (zero border)
+void launch_sobel_pad(float* img, float* dx, float* dy, const LevelGeom& g, int n, int C, cudaStream_t s,
+                      LaunchStats* st);
+
+// ---- stage 2: inverse search ------------------------------------------------------------
+struct PatchArgs {
+  const float* tmpl_img;   // template frame: padded level image / dx / dy   [n][th][tw][C]
+  const float* tmpl_dx;
+  const float* tmpl_dy;
+  const float* tgt_img;    // target frame padded level image
+  const float* flow_prev;  // coarser-level dense flow [n][h/2][w/2][nop] or null
+  size_t flow_prev_stride; // elements per pair
+  float* p_iter;           // [n][npatch][nop]
+  float* pt_iter;          // [n][npatch][2]   (may be null)
+  float* pweight;          // [n][npatch][novals]
+  int camlr;
+};
+// returns false if (psz, channels) has no kernel instantiation
+bool launch_patch_search(const PatchArgs& a, const LevelGeom& g, const OptConst& o, int n, cudaStream_t s,
+                         LaunchStats* st);
+
+// ---- stage 3: densification ---------------------------------------------------------------
+struct DensifyArgs {
+  const float* p_iter;     // own grid
+  const float* pweight;
+  const float* cg_p_iter;  // complementary grid (forward-backward merging) or null
+  const float* cg_pt_iter;
+  const float* cg_pweight;
+  float* flow;             // [n][h][w][nop]
+  // scratch for the backward merge (cell lists), may be null when cg is null
+  int* cell_count;         // [n][ncell]
+  int* cell_list;          // [n][ncell][cell_cap]
+  int cell_cap;
+  int* overflow;         // single int, set to the largest cell population that exceeded cell_cap
+};
+void launch_densify(const DensifyArgs& a, const LevelGeom& g, const OptConst& o, int n, cudaStream_t s,
+                    LaunchStats* st);
+
+// ---- stage 4: variational refinement ------------------------------------------------------
+struct VarRefBuffers {
+  // all planes are [n][h][w] (stride == w), sized for the largest level
+  float* avg;    // [C] planes
+  float* Iz;     // [C]
+  float* mask;
+  float* Ix; float* Iy; float* Ixx; float* Ixy; float* Iyy; float* Ixz; float* Iyz;   // [C] each
+  float* du;     // [nop] interleaved
+  float* smooth; // float2 {h, v}
+  float* coef;   // float4 {hl, h, vt, v}
+  float* inv;    // float4 {i11, i12, i22, 0}   (DE: {a11+sum,0,0,0})
+  float* rhs;    // float2 {b1, b2}            (DE: float)
+  size_t plane_cap;  // elements per pair per plane (>= w*h of the largest level)
+};
+void launch_varref_level(const float* im_a, const float* im_b, float* flow, const LevelGeom& g, const DisParams& p,
+                         int camlr, const VarRefBuffers& vb, int n, cudaStream_t s, LaunchStats* st);
+size_t varref_plane_count(int C, int nop);  // number of float planes VarRefBuffers needs
+
+// ---- stage 5: upsample + crop ---------------------------------------------------------------
+void launch_upsample_crop(const float* flow, const LevelGeom& g, int nop, int sc_l, int padl, int padt, int w0,
+                          int h0, float* out, int n, cudaStream_t s, LaunchStats* st);
+
+}  // namespace disb200
+
+#endif

@@ -1,0 +1,650 @@
+// Host orchestration: the scale loop of OFC::OFClass (oflow.cpp:31-338) and the driver steps of
+// run_dense.cpp:297-415 around it, for a batch of independent frame pairs, behind the C-ABI of
+// include/disb200.h.  Every stage is a CUDA kernel (pyramid.cu, patch.cu, densify.cu,
+// varref.cu, upsample.cu); there is no CPU implementation to fall back to.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "dis_internal.h"
+
+namespace disb200 {
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) {
+  g_err = msg;
+  return code;
+}
+#define CU(call)                                                                          \
+  do {                                                                                    \
+    cudaError_t e__ = (call);                                                             \
+    if (e__ != cudaSuccess)                                                               \
+      return fail(e__ == cudaErrorMemoryAllocation ? DISB200_ENOMEM : DISB200_ECUDA,      \
+                  std::string(#call) + ": " + cudaGetErrorString(e__));                   \
+  } while (0)
+
+OptConst make_optconst(const DisParams& p) {
+  OptConst o;
+  o.mode = p.mode;
+  o.nop = p.mode == DISB200_MODE_OF ? 2 : 1;                              // oflow.cpp:75-79
+  o.psz = p.patchsz;
+  o.outlierthresh = (float)p.patchsz / 2;                                 // oflow.cpp:81
+  o.max_iter = p.max_iter;
+  o.min_iter = p.min_iter;
+  o.dp_thresh_sq = p.dp_thresh * p.dp_thresh;                             // oflow.cpp:87
+  o.dr_thresh = p.dr_thresh;
+  o.res_thresh = p.res_thresh;
+  o.steps = std::max(1, (int)std::floor(p.patchsz * (1 - p.patove)));     // oflow.cpp:90
+  o.noc = p.channels;
+  o.novals = p.channels * p.patchsz * p.patchsz;                          // oflow.cpp:91
+  o.patnorm = p.patnorm;
+  o.costfct = p.costfct;
+  o.minerrval = 2.0f;                                                     // oflow.h:76
+  o.normoutlier = 5.0f;                                                   // oflow.h:77
+  return o;
+}
+
+LevelGeom make_levelgeom(const DisParams& p, int W, int H, int level) {
+  LevelGeom g;
+  const OptConst o = make_optconst(p);
+  const float sc = std::pow(2.0f, -level);                                // oflow.cpp:142-151
+  g.level = level;
+  g.h = (int)(H * sc);
+  g.w = (int)(W * sc);
+  g.pad = p.patchsz;
+  g.tw = g.w + 2 * g.pad;
+  g.th = g.h + 2 * g.pad;
+  g.lb = -(float)p.patchsz / 2;
+  g.ubw = (float)(g.w + p.patchsz / 2 - 2);
+  g.ubh = (float)(g.h + p.patchsz / 2 - 2);
+  g.steps = o.steps;
+  g.nopw = (int)std::ceil((float)g.w / (float)g.steps);                   // patchgrid.cpp:43-46
+  g.noph = (int)std::ceil((float)g.h / (float)g.steps);
+  g.offw = (g.w - (g.nopw - 1) * g.steps) / 2;
+  g.offh = (g.h - (g.noph - 1) * g.steps) / 2;
+  g.npatch = g.nopw * g.noph;
+  g.img_elems = (size_t)g.tw * g.th * p.channels;
+  return g;
+}
+
+static int validate(const DisParams& p) {
+  if (p.mode != DISB200_MODE_OF && p.mode != DISB200_MODE_DE) return fail(DISB200_EINVAL, "mode must be 1 (OF) or 2 (DE)");
+  if (p.channels != 1 && p.channels != 3) return fail(DISB200_EINVAL, "channels must be 1 or 3");
+  if (p.sc_l < 0 || p.sc_f < p.sc_l || p.sc_f > 8) return fail(DISB200_EINVAL, "need 0 <= sc_l <= sc_f <= 8");
+  if (p.patove < 0.f || p.patove >= 1.f) return fail(DISB200_EINVAL, "patove must be in [0,1)");
+  if (p.patchsz != 4 && p.patchsz != 8 && p.patchsz != 12 && p.patchsz != 16)
+    return fail(DISB200_EUNSUPPORTED, "patch size must be one of 4, 8, 12, 16");
+  if (p.costfct != 0 && p.costfct != 1 && p.costfct != 2)
+    return fail(DISB200_EUNSUPPORTED, "costfct must be 0 (L2), 1 (L1) or 2 (pseudo-Huber)");
+  if (p.max_iter < 0 || p.min_iter < 0) return fail(DISB200_EINVAL, "iteration counts must be >= 0");
+  if (p.usetvref && (p.tv_innerit < 0 || p.tv_solverit < 1)) return fail(DISB200_EINVAL, "tv_innerit >= 0 and tv_solverit >= 1 required");
+  return DISB200_OK;
+}
+
+// Device workspace + scale loop for n <= max_batch pairs of one geometry.
+struct Engine {
+  DisParams p;
+  OptConst o;
+  int W = 0, H = 0, C = 1, nop = 2, max_batch = 0, device = 0;
+  std::vector<LevelGeom> geom;                       // indexed by level
+  std::vector<float*> pyr[2][3];                     // [frame][img|dx|dy][level]
+  std::vector<float*> flow[2];                       // [dir][level]  [n][h][w][nop]
+  float* p_iter[2] = {nullptr, nullptr};
+  float* pt_iter[2] = {nullptr, nullptr};
+  float* pweight[2] = {nullptr, nullptr};
+  float* initflow = nullptr;                         // optional warm start (oflow.cpp:215-217)
+  bool has_initflow = false;
+  float* vpool = nullptr;
+  VarRefBuffers vb;
+  int* cell_count = nullptr;
+  int* cell_list = nullptr;
+  int cell_cap = 0;
+  int* overflow = nullptr;
+  size_t ncell_max = 0;
+  std::vector<void*> allocs;
+  cudaStream_t stream = nullptr;
+  LaunchStats stats{0};
+  // stage timing
+  bool stage_timing = false;
+  float stage_ms[5] = {0, 0, 0, 0, 0};
+  std::vector<cudaEvent_t> ev_pool;
+  struct Mark { int stage; cudaEvent_t a, b; };
+  std::vector<Mark> marks;
+  size_t ev_used = 0;
+
+  template <class T>
+  int dalloc(T** ptr, size_t count) {
+    void* q = nullptr;
+    CU(cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(T)));
+    allocs.push_back(q);
+    *ptr = static_cast<T*>(q);
+    return DISB200_OK;
+  }
+
+  int init(const DisParams& prm, int W_, int H_, int max_batch_, int device_) {
+    p = prm;
+    o = make_optconst(p);
+    W = W_; H = H_; C = p.channels; nop = o.nop; max_batch = max_batch_; device = device_;
+    if (W % (1 << p.sc_f) || H % (1 << p.sc_f)) return fail(DISB200_EINVAL, "W and H must be divisible by 2^sc_f (oflow.h:102)");
+    CU(cudaSetDevice(device));
+    CU(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    geom.resize(p.sc_f + 1);
+    for (int f = 0; f < 2; ++f)
+      for (int a = 0; a < 3; ++a) pyr[f][a].assign(p.sc_f + 1, nullptr);
+    flow[0].assign(p.sc_f + 1, nullptr);
+    flow[1].assign(p.sc_f + 1, nullptr);
+    size_t max_patch = 0, max_pix = 0;
+    for (int l = p.sc_l; l <= p.sc_f; ++l) {
+      geom[l] = make_levelgeom(p, W, H, l);
+      const LevelGeom& g = geom[l];
+      if (g.w < 2 || g.h < 2) return fail(DISB200_EUNSUPPORTED, "coarsest level smaller than 2x2 pixels");
+      for (int f = 0; f < 2; ++f)
+        for (int a = 0; a < 3; ++a) {
+          int rc = dalloc(&pyr[f][a][l], g.img_elems * max_batch);
+          if (rc) return rc;
+        }
+      for (int d = 0; d < (p.usefbcon ? 2 : 1); ++d) {
+        int rc = dalloc(&flow[d][l], (size_t)g.w * g.h * nop * max_batch);
+        if (rc) return rc;
+      }
+      max_patch = std::max(max_patch, (size_t)g.npatch);
+      max_pix = std::max(max_pix, (size_t)g.w * g.h);
+      ncell_max = std::max(ncell_max, (size_t)((g.w + 2 * o.psz) / o.psz + 2) * ((g.h + 2 * o.psz) / o.psz + 2));
+    }
+    for (int d = 0; d < (p.usefbcon ? 2 : 1); ++d) {
+      int rc = dalloc(&p_iter[d], max_patch * nop * max_batch);
+      if (!rc) rc = dalloc(&pt_iter[d], max_patch * 2 * max_batch);
+      if (!rc) rc = dalloc(&pweight[d], max_patch * o.novals * max_batch);
+      if (rc) return rc;
+    }
+    if (p.usefbcon) {
+      const int per_axis = (o.psz + o.steps - 1) / o.steps + 1;
+      cell_cap = std::max(16, 4 * per_axis * per_axis);
+      int rc = dalloc(&cell_count, ncell_max * max_batch);
+      if (!rc) rc = dalloc(&overflow, 1);
+      if (!rc) CU(cudaMemset(overflow, 0, sizeof(int)));
+      if (!rc) rc = dalloc(&cell_list, ncell_max * cell_cap * max_batch);
+      if (rc) return rc;
+    }
+    {
+      const LevelGeom& gc = geom[p.sc_f];
+      int rc = dalloc(&initflow, (size_t)(gc.w / 2) * (gc.h / 2) * nop * max_batch);
+      if (rc) return rc;
+    }
+    if (p.usetvref) {
+      const size_t plane = (max_pix + 3) & ~(size_t)3;   // keeps float4 planes 16-byte aligned
+      const size_t nplanes = varref_plane_count(C, nop);
+      int rc = dalloc(&vpool, plane * nplanes * max_batch);
+      if (rc) return rc;
+      float* q = vpool;
+      auto take = [&](size_t k) { float* r = q; q += plane * k * max_batch; return r; };
+      vb.plane_cap = plane;
+      vb.coef = take(4); vb.inv = take(4);          // float4 planes first (alignment)
+      vb.du = take(nop); vb.rhs = take(nop);
+      vb.avg = take(C); vb.Iz = take(C); vb.Ix = take(C); vb.Iy = take(C);
+      vb.Ixx = take(C); vb.Ixy = take(C); vb.Iyy = take(C); vb.Ixz = take(C); vb.Iyz = take(C);
+      vb.mask = take(1); vb.smooth = take(1);
+    }
+    return DISB200_OK;
+  }
+
+  void destroy() {
+    if (stream) cudaStreamSynchronize(stream);
+    for (void* q : allocs) cudaFree(q);
+    allocs.clear();
+    for (cudaEvent_t e : ev_pool) cudaEventDestroy(e);
+    ev_pool.clear();
+    if (stream) cudaStreamDestroy(stream);
+    stream = nullptr;
+  }
+
+  cudaEvent_t next_event() {
+    if (ev_used == ev_pool.size()) {
+      cudaEvent_t e;
+      cudaEventCreate(&e);
+      ev_pool.push_back(e);
+    }
+    return ev_pool[ev_used++];
+  }
+  struct StageScope {
+    Engine* e; int stage; cudaEvent_t a;
+    StageScope(Engine* e_, int s) : e(e_), stage(s), a(nullptr) {
+      if (e->stage_timing) { a = e->next_event(); cudaEventRecord(a, e->stream); }
+    }
+    ~StageScope() {
+      if (e->stage_timing) { cudaEvent_t b = e->next_event(); cudaEventRecord(b, e->stream); e->marks.push_back({stage, a, b}); }
+    }
+  };
+  void begin_run() {
+    stats.launches = 0;
+    ev_used = 0;
+    marks.clear();
+  }
+  void collect_stage_times() {
+    if (!stage_timing) return;
+    cudaStreamSynchronize(stream);
+    for (float& v : stage_ms) v = 0.f;
+    for (const Mark& m : marks) {
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, m.a, m.b);
+      stage_ms[m.stage] += ms;
+    }
+  }
+
+  // a1 + a2: u8 frames (device) -> padded pyramids of both frames
+  void build_pyramids(const uint8_t* dA, const uint8_t* dB, int n, int w0, int h0, int padl, int padt) {
+    StageScope sc(this, 0);
+    const uint8_t* fr[2] = {dA, dB};
+    for (int f = 0; f < 2; ++f) {
+      launch_downscale_u8(fr[f], n, w0, h0, C, padl, padt, p.sc_l, geom[p.sc_l], pyr[f][0][p.sc_l], stream, &stats);
+      for (int l = p.sc_l + 1; l <= p.sc_f; ++l)
+        launch_halve(pyr[f][0][l - 1], geom[l - 1], pyr[f][0][l], geom[l], n, C, stream, &stats);
+      for (int l = p.sc_l; l <= p.sc_f; ++l)
+        launch_sobel_pad(pyr[f][0][l], pyr[f][1][l], pyr[f][2][l], geom[l], n, C, stream, &stats);
+    }
+  }
+
+  // The scale loop, oflow.cpp:182-330.  Result: flow[0][sc_l].
+  int run_levels(int n) {
+    for (int sl = p.sc_f; sl >= p.sc_l; --sl) {
+      const LevelGeom& g = geom[sl];
+      const int ndir = p.usefbcon ? 2 : 1;
+      {
+        StageScope sc(this, 1);
+        for (int d = 0; d < ndir; ++d) {                               // oflow.cpp:191-232
+          PatchArgs a;
+          a.tmpl_img = pyr[d][0][sl]; a.tmpl_dx = pyr[d][1][sl]; a.tmpl_dy = pyr[d][2][sl];
+          a.tgt_img = pyr[1 - d][0][sl];
+          a.flow_prev = nullptr; a.flow_prev_stride = 0;
+          if (sl < p.sc_f) {
+            a.flow_prev = flow[d][sl + 1];
+            a.flow_prev_stride = (size_t)geom[sl + 1].w * geom[sl + 1].h * nop;
+          } else if (d == 0 && has_initflow) {
+            a.flow_prev = initflow;
+            a.flow_prev_stride = (size_t)(g.w / 2) * (g.h / 2) * nop;
+          }
+          a.p_iter = p_iter[d]; a.pt_iter = pt_iter[d]; a.pweight = pweight[d];
+          a.camlr = d;
+          if (!launch_patch_search(a, g, o, n, stream, &stats))
+            return fail(DISB200_EUNSUPPORTED, "no inverse-search kernel for this patch size / channel count");
+        }
+      }
+      {
+        StageScope sc(this, 2);
+        for (int d = 0; d < ndir; ++d) {                               // oflow.cpp:259-267
+          if (d == 1 && sl == p.sc_l) break;
+          DensifyArgs a;
+          a.p_iter = p_iter[d]; a.pweight = pweight[d];
+          a.cg_p_iter = p.usefbcon ? p_iter[1 - d] : nullptr;
+          a.cg_pt_iter = p.usefbcon ? pt_iter[1 - d] : nullptr;
+          a.cg_pweight = p.usefbcon ? pweight[1 - d] : nullptr;
+          a.flow = flow[d][sl];
+          a.cell_count = cell_count; a.cell_list = cell_list; a.cell_cap = cell_cap; a.overflow = overflow;
+          launch_densify(a, g, o, n, stream, &stats);
+        }
+      }
+      if (p.usetvref) {                                                // oflow.cpp:281-290
+        StageScope sc(this, 3);
+        launch_varref_level(pyr[0][0][sl], pyr[1][0][sl], flow[0][sl], g, p, 0, vb, n, stream, &stats);
+        if (p.usefbcon && sl > p.sc_l)
+          launch_varref_level(pyr[1][0][sl], pyr[0][0][sl], flow[1][sl], g, p, 1, vb, n, stream, &stats);
+      }
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(DISB200_ECUDA, std::string("kernel launch: ") + cudaGetErrorString(e));
+    return DISB200_OK;
+  }
+};
+
+}  // namespace disb200
+
+// ===========================================================================================
+// C-ABI
+// ===========================================================================================
+using namespace disb200;
+
+struct DisHandle {
+  Engine e;
+  int w0 = 0, h0 = 0, padl = 0, padt = 0;
+  // double-buffered device staging for the host-pointer entry points
+  uint8_t* dA[2] = {nullptr, nullptr};
+  uint8_t* dB[2] = {nullptr, nullptr};
+  float* dOut[2] = {nullptr, nullptr};
+  cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
+  cudaEvent_t ev_h2d[2], ev_comp[2], ev_d2h[2];
+  cudaEvent_t t0 = nullptr, t1 = nullptr;
+  bool staging = false;
+  size_t in_bytes = 0, out_bytes = 0;   // per pair
+
+  int ensure_staging() {
+    if (staging) return DISB200_OK;
+    for (int k = 0; k < 2; ++k) {
+      int rc = e.dalloc(&dA[k], in_bytes * e.max_batch);
+      if (!rc) rc = e.dalloc(&dB[k], in_bytes * e.max_batch);
+      if (!rc) rc = e.dalloc(&dOut[k], out_bytes / sizeof(float) * e.max_batch);
+      if (rc) return rc;
+      CU(cudaEventCreateWithFlags(&ev_h2d[k], cudaEventDisableTiming));
+      CU(cudaEventCreateWithFlags(&ev_comp[k], cudaEventDisableTiming));
+      CU(cudaEventCreateWithFlags(&ev_d2h[k], cudaEventDisableTiming));
+    }
+    CU(cudaStreamCreateWithFlags(&s_h2d, cudaStreamNonBlocking));
+    CU(cudaStreamCreateWithFlags(&s_d2h, cudaStreamNonBlocking));
+    staging = true;
+    return DISB200_OK;
+  }
+
+  // enqueue the whole per-batch pipeline on e.stream
+  int enqueue(const uint8_t* a, const uint8_t* b, int n, float* out) {
+    e.build_pyramids(a, b, n, w0, h0, padl, padt);
+    int rc = e.run_levels(n);
+    if (rc) return rc;
+    {
+      Engine::StageScope sc(&e, 4);
+      launch_upsample_crop(e.flow[0][e.p.sc_l], e.geom[e.p.sc_l], e.nop, e.p.sc_l, padl, padt, w0, h0, out, n, e.stream, &e.stats);
+    }
+    cudaError_t ce = cudaGetLastError();
+    if (ce != cudaSuccess) return fail(DISB200_ECUDA, std::string("kernel launch: ") + cudaGetErrorString(ce));
+    return DISB200_OK;
+  }
+
+  int check_overflow() {
+    if (!e.overflow) return DISB200_OK;
+    int v = 0;
+    CU(cudaMemcpy(&v, e.overflow, sizeof(int), cudaMemcpyDeviceToHost));
+    if (v > 0) {
+      cudaMemset(e.overflow, 0, sizeof(int));
+      return fail(DISB200_EUNSUPPORTED, "forward-backward merge: " + std::to_string(v) + " patches ended in one cell, capacity " + std::to_string(e.cell_cap));
+    }
+    return DISB200_OK;
+  }
+};
+
+extern "C" {
+
+const char* disb200_last_error(void) { return g_err.c_str(); }
+const char* disb200_version(void) { return "disb200 0.1 (sm_100a)"; }
+
+int disb200_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+int disb200_operating_point(int op, int width, int mode, int channels, DisParams* p) {
+  if (!p) return fail(DISB200_EINVAL, "null params");
+  std::memset(p, 0, sizeof(*p));
+  p->dp_thresh = 0.05f; p->dr_thresh = 0.95f; p->res_thresh = 0.0f;      // run_dense.cpp:228-232
+  p->usefbcon = 0; p->patnorm = 1; p->costfct = 0;
+  p->tv_alpha = 10.0f; p->tv_gamma = 10.0f; p->tv_delta = 5.0f;
+  p->tv_innerit = 1; p->tv_solverit = 3; p->tv_sor = 1.6f;
+  p->verbosity = 2; p->mode = mode; p->channels = channels; p->sor_mode = DISB200_SOR_LEXICOGRAPHIC;
+  const int fratio = 5;
+  auto first_scale = [&](int psz) {                                       // run_dense.cpp:181-184
+    return std::max(0, (int)std::floor(log2((2.0f * (float)width) / ((float)fratio * (float)psz))));
+  };
+  switch (op) {                                                           // run_dense.cpp:238-268
+    case 1: p->patchsz = 8; p->patove = 0.3f; p->sc_f = first_scale(8); p->sc_l = std::max(p->sc_f - 2, 0); p->max_iter = p->min_iter = 16; p->usetvref = 0; break;
+    case 3: p->patchsz = 12; p->patove = 0.75f; p->sc_f = first_scale(12); p->sc_l = std::max(p->sc_f - 4, 0); p->max_iter = p->min_iter = 16; p->usetvref = 1; break;
+    case 4: p->patchsz = 12; p->patove = 0.75f; p->sc_f = first_scale(12); p->sc_l = std::max(p->sc_f - 5, 0); p->max_iter = p->min_iter = 128; p->usetvref = 1; break;
+    default: p->patchsz = 8; p->patove = 0.4f; p->sc_f = first_scale(8); p->sc_l = std::max(p->sc_f - 2, 0); p->max_iter = p->min_iter = 12; p->usetvref = 1; break;
+  }
+  return DISB200_OK;
+}
+
+int disb200_padded_dims(int w0, int h0, int sc_f, int* W, int* H, int* padl, int* padt) {
+  if (w0 <= 0 || h0 <= 0 || sc_f < 0 || sc_f > 16) return fail(DISB200_EINVAL, "bad dimensions");
+  const int scfct = 1 << sc_f;                                            // run_dense.cpp:299-305
+  int padw = 0, padh = 0;
+  if (w0 % scfct) padw = scfct - w0 % scfct;
+  if (h0 % scfct) padh = scfct - h0 % scfct;
+  if (W) *W = w0 + padw;
+  if (H) *H = h0 + padh;
+  if (padl) *padl = padw / 2;
+  if (padt) *padt = padh / 2;
+  return DISB200_OK;
+}
+
+int disb200_create(const DisParams* params, int w0, int h0, int max_batch, int device, DisHandle** out) {
+  if (!params || !out) return fail(DISB200_EINVAL, "null argument");
+  if (max_batch < 1) return fail(DISB200_EINVAL, "max_batch must be >= 1");
+  int rc = validate(*params);
+  if (rc) return rc;
+  if (disb200_device_count() <= device) return fail(DISB200_ECUDA, "no CUDA device " + std::to_string(device) + " (this library has no CPU path)");
+  DisHandle* h = new DisHandle();
+  int W, H;
+  rc = disb200_padded_dims(w0, h0, params->sc_f, &W, &H, &h->padl, &h->padt);
+  if (!rc) rc = h->e.init(*params, W, H, max_batch, device);
+  if (!rc) {
+    h->w0 = w0; h->h0 = h0;
+    h->in_bytes = (size_t)w0 * h0 * params->channels;
+    h->out_bytes = (size_t)w0 * h0 * h->e.nop * sizeof(float);
+    if (cudaEventCreate(&h->t0) != cudaSuccess || cudaEventCreate(&h->t1) != cudaSuccess) rc = fail(DISB200_ECUDA, "cudaEventCreate failed");
+  }
+  if (rc) { h->e.destroy(); delete h; return rc; }
+  *out = h;
+  return DISB200_OK;
+}
+
+int disb200_destroy(DisHandle* h) {
+  if (!h) return DISB200_OK;
+  cudaSetDevice(h->e.device);
+  if (h->s_h2d) { cudaStreamSynchronize(h->s_h2d); cudaStreamDestroy(h->s_h2d); }
+  if (h->s_d2h) { cudaStreamSynchronize(h->s_d2h); cudaStreamDestroy(h->s_d2h); }
+  if (h->staging)
+    for (int k = 0; k < 2; ++k) { cudaEventDestroy(h->ev_h2d[k]); cudaEventDestroy(h->ev_comp[k]); cudaEventDestroy(h->ev_d2h[k]); }
+  if (h->t0) cudaEventDestroy(h->t0);
+  if (h->t1) cudaEventDestroy(h->t1);
+  h->e.destroy();
+  delete h;
+  return DISB200_OK;
+}
+
+int disb200_run_batch_device(DisHandle* h, const uint8_t* dA, const uint8_t* dB, int n, float* dOut) {
+  if (!h || !dA || !dB || !dOut) return fail(DISB200_EINVAL, "null argument");
+  if (n < 1 || n > h->e.max_batch) return fail(DISB200_EINVAL, "n must be in 1..max_batch");
+  CU(cudaSetDevice(h->e.device));
+  h->e.begin_run();
+  return h->enqueue(dA, dB, n, dOut);
+}
+
+int disb200_sync(DisHandle* h) {
+  if (!h) return fail(DISB200_EINVAL, "null handle");
+  CU(cudaSetDevice(h->e.device));
+  CU(cudaStreamSynchronize(h->e.stream));
+  h->e.collect_stage_times();
+  return h->check_overflow();
+}
+
+int disb200_run_batch_host(DisHandle* h, const uint8_t* A, const uint8_t* B, int n, float* out) {
+  if (!h || !A || !B || !out) return fail(DISB200_EINVAL, "null argument");
+  if (n < 1) return fail(DISB200_EINVAL, "n must be >= 1");
+  CU(cudaSetDevice(h->e.device));
+  int rc = h->ensure_staging();
+  if (rc) return rc;
+  h->e.begin_run();
+  const int mb = h->e.max_batch;
+  int k = 0;
+  for (int i0 = 0; i0 < n; i0 += mb, ++k) {
+    const int m = std::min(mb, n - i0), b = k & 1;
+    // input buffer b is free once the compute of chunk k-2 is done
+    if (k >= 2) CU(cudaStreamWaitEvent(h->s_h2d, h->ev_comp[b], 0));
+    CU(cudaMemcpyAsync(h->dA[b], A + (size_t)i0 * h->in_bytes, h->in_bytes * m, cudaMemcpyHostToDevice, h->s_h2d));
+    CU(cudaMemcpyAsync(h->dB[b], B + (size_t)i0 * h->in_bytes, h->in_bytes * m, cudaMemcpyHostToDevice, h->s_h2d));
+    CU(cudaEventRecord(h->ev_h2d[b], h->s_h2d));
+    CU(cudaStreamWaitEvent(h->e.stream, h->ev_h2d[b], 0));
+    // output buffer b is free once the download of chunk k-2 is done
+    if (k >= 2) CU(cudaStreamWaitEvent(h->e.stream, h->ev_d2h[b], 0));
+    rc = h->enqueue(h->dA[b], h->dB[b], m, h->dOut[b]);
+    if (rc) return rc;
+    CU(cudaEventRecord(h->ev_comp[b], h->e.stream));
+    CU(cudaStreamWaitEvent(h->s_d2h, h->ev_comp[b], 0));
+    CU(cudaMemcpyAsync(out + (size_t)i0 * (h->out_bytes / sizeof(float)), h->dOut[b], h->out_bytes * m, cudaMemcpyDeviceToHost, h->s_d2h));
+    CU(cudaEventRecord(h->ev_d2h[b], h->s_d2h));
+  }
+  CU(cudaStreamSynchronize(h->s_d2h));
+  CU(cudaStreamSynchronize(h->e.stream));
+  h->e.collect_stage_times();
+  return h->check_overflow();
+}
+
+int disb200_run_batch(DisHandle* h, const uint8_t* const* imgA, const uint8_t* const* imgB, int n, float* const* out) {
+  if (!h || !imgA || !imgB || !out) return fail(DISB200_EINVAL, "null argument");
+  if (n < 1) return fail(DISB200_EINVAL, "n must be >= 1");
+  CU(cudaSetDevice(h->e.device));
+  int rc = h->ensure_staging();
+  if (rc) return rc;
+  h->e.begin_run();
+  const int mb = h->e.max_batch;
+  for (int i0 = 0; i0 < n; i0 += mb) {
+    const int m = std::min(mb, n - i0);
+    for (int i = 0; i < m; ++i) {
+      CU(cudaMemcpyAsync(h->dA[0] + (size_t)i * h->in_bytes, imgA[i0 + i], h->in_bytes, cudaMemcpyHostToDevice, h->e.stream));
+      CU(cudaMemcpyAsync(h->dB[0] + (size_t)i * h->in_bytes, imgB[i0 + i], h->in_bytes, cudaMemcpyHostToDevice, h->e.stream));
+    }
+    rc = h->enqueue(h->dA[0], h->dB[0], m, h->dOut[0]);
+    if (rc) return rc;
+    for (int i = 0; i < m; ++i)
+      CU(cudaMemcpyAsync(out[i0 + i], h->dOut[0] + (size_t)i * (h->out_bytes / sizeof(float)), h->out_bytes, cudaMemcpyDeviceToHost, h->e.stream));
+    CU(cudaStreamSynchronize(h->e.stream));
+  }
+  h->e.collect_stage_times();
+  return h->check_overflow();
+}
+
+int disb200_timer_begin(DisHandle* h) {
+  if (!h) return fail(DISB200_EINVAL, "null handle");
+  CU(cudaSetDevice(h->e.device));
+  CU(cudaEventRecord(h->t0, h->e.stream));
+  return DISB200_OK;
+}
+int disb200_timer_end(DisHandle* h, float* ms) {
+  if (!h || !ms) return fail(DISB200_EINVAL, "null argument");
+  CU(cudaSetDevice(h->e.device));
+  CU(cudaEventRecord(h->t1, h->e.stream));
+  CU(cudaEventSynchronize(h->t1));
+  CU(cudaEventElapsedTime(ms, h->t0, h->t1));
+  return DISB200_OK;
+}
+int disb200_last_launch_count(const DisHandle* h) { return h ? h->e.stats.launches : 0; }
+int disb200_set_stage_timing(DisHandle* h, int on) {
+  if (!h) return fail(DISB200_EINVAL, "null handle");
+  h->e.stage_timing = on != 0;
+  return DISB200_OK;
+}
+int disb200_stage_ms(const DisHandle* h, int stage, float* ms) {
+  if (!h || !ms || stage < 0 || stage > 4) return fail(DISB200_EINVAL, "bad argument");
+  *ms = h->e.stage_ms[stage];
+  return DISB200_OK;
+}
+
+int disb200_fetch(DisHandle* h, int kind, int which, int level, int pair, void* dst, size_t nbytes) {
+  if (!h || !dst) return fail(DISB200_EINVAL, "null argument");
+  Engine& e = h->e;
+  if (pair < 0 || pair >= e.max_batch || which < 0 || which > 1) return fail(DISB200_EINVAL, "bad pair / which");
+  CU(cudaSetDevice(e.device));
+  CU(cudaStreamSynchronize(e.stream));
+  const void* src = nullptr;
+  size_t bytes = 0;
+  if (kind >= 0 && kind <= 3) {
+    if (level < e.p.sc_l || level > e.p.sc_f) return fail(DISB200_EINVAL, "level outside sc_l..sc_f");
+    const LevelGeom& g = e.geom[level];
+    if (kind <= 2) {
+      bytes = g.img_elems * sizeof(float);
+      src = e.pyr[which][kind][level] + (size_t)pair * g.img_elems;
+    } else {
+      if (!e.flow[which][level]) return fail(DISB200_EINVAL, "no backward flow (usefbcon = 0)");
+      bytes = (size_t)g.w * g.h * e.nop * sizeof(float);
+      src = e.flow[which][level] + (size_t)pair * g.w * g.h * e.nop;
+    }
+  } else if (kind >= 4 && kind <= 6) {
+    const LevelGeom& g = e.geom[e.p.sc_l];
+    if (!e.p_iter[which]) return fail(DISB200_EINVAL, "no backward grid (usefbcon = 0)");
+    if (kind == 4) { bytes = (size_t)g.npatch * e.nop * sizeof(float); src = e.p_iter[which] + (size_t)pair * g.npatch * e.nop; }
+    if (kind == 5) { bytes = (size_t)g.npatch * 2 * sizeof(float); src = e.pt_iter[which] + (size_t)pair * g.npatch * 2; }
+    if (kind == 6) { bytes = (size_t)g.npatch * e.o.novals * sizeof(float); src = e.pweight[which] + (size_t)pair * g.npatch * e.o.novals; }
+  } else {
+    return fail(DISB200_EINVAL, "unknown kind");
+  }
+  if (bytes != nbytes) return fail(DISB200_EINVAL, "nbytes is " + std::to_string(nbytes) + ", object has " + std::to_string(bytes));
+  CU(cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost));
+  return DISB200_OK;
+}
+
+int disb200_ofclass(const DisParams* params, const float* const* im_ao, const float* const* im_ao_dx,
+                    const float* const* im_ao_dy, const float* const* im_bo, const float* const* im_bo_dx,
+                    const float* const* im_bo_dy, int W, int H, float* outflow, const float* initflow) {
+  if (!params || !im_ao || !im_ao_dx || !im_ao_dy || !im_bo || !im_bo_dx || !im_bo_dy || !outflow)
+    return fail(DISB200_EINVAL, "null argument");
+  int rc = validate(*params);
+  if (rc) return rc;
+  if (disb200_device_count() < 1) return fail(DISB200_ECUDA, "no CUDA device (this library has no CPU path)");
+  Engine e;
+  rc = e.init(*params, W, H, 1, 0);
+  const float* const* src[2][3] = {{im_ao, im_ao_dx, im_ao_dy}, {im_bo, im_bo_dx, im_bo_dy}};
+  for (int l = params->sc_l; !rc && l <= params->sc_f; ++l)
+    for (int f = 0; f < 2 && !rc; ++f)
+      for (int a = 0; a < 3 && !rc; ++a) {
+        if (!src[f][a][l]) { rc = fail(DISB200_EINVAL, "pyramid level " + std::to_string(l) + " is null"); break; }
+        if (cudaMemcpyAsync(e.pyr[f][a][l], src[f][a][l], e.geom[l].img_elems * sizeof(float), cudaMemcpyHostToDevice, e.stream) != cudaSuccess)
+          rc = fail(DISB200_ECUDA, "pyramid upload failed");
+      }
+  if (!rc && initflow) {
+    const LevelGeom& gc = e.geom[params->sc_f];
+    if (cudaMemcpyAsync(e.initflow, initflow, (size_t)(gc.w / 2) * (gc.h / 2) * e.nop * sizeof(float), cudaMemcpyHostToDevice, e.stream) != cudaSuccess)
+      rc = fail(DISB200_ECUDA, "initflow upload failed");
+    e.has_initflow = true;
+  }
+  if (!rc) { e.begin_run(); rc = e.run_levels(1); }
+  if (!rc) {
+    const LevelGeom& g = e.geom[params->sc_l];
+    cudaError_t ce = cudaMemcpyAsync(outflow, e.flow[0][params->sc_l], (size_t)g.w * g.h * e.nop * sizeof(float), cudaMemcpyDeviceToHost, e.stream);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(e.stream);
+    if (ce != cudaSuccess) rc = fail(DISB200_ECUDA, std::string("ofclass: ") + cudaGetErrorString(ce));
+  }
+  if (!rc && e.overflow) {
+    int v = 0;
+    cudaMemcpy(&v, e.overflow, sizeof(int), cudaMemcpyDeviceToHost);
+    if (v > 0) rc = fail(DISB200_EUNSUPPORTED, "forward-backward merge cell overflow");
+  }
+  e.destroy();
+  return rc;
+}
+
+int disb200_varref_level(const DisParams* params, const float* im_a, const float* im_b, int w_l, int h_l, int level,
+                         int camlr, float* flow) {
+  if (!params || !im_a || !im_b || !flow) return fail(DISB200_EINVAL, "null argument");
+  int rc = validate(*params);
+  if (rc) return rc;
+  if (disb200_device_count() < 1) return fail(DISB200_ECUDA, "no CUDA device (this library has no CPU path)");
+  if (w_l < 2 || h_l < 2) return fail(DISB200_EUNSUPPORTED, "level smaller than 2x2 pixels");
+  // an engine whose only level is `level`-like: reuse the allocator with sc_f = sc_l = 0 on a w_l x h_l frame
+  DisParams q = *params;
+  q.sc_f = q.sc_l = 0;
+  q.usefbcon = 0;
+  q.usetvref = 1;
+  Engine e;
+  rc = e.init(q, w_l, h_l, 1, 0);
+  if (!rc) {
+    LevelGeom g = e.geom[0];
+    g.level = level;
+    const size_t fb = (size_t)w_l * h_l * e.nop * sizeof(float);
+    cudaError_t ce = cudaMemcpyAsync(e.pyr[0][0][0], im_a, g.img_elems * sizeof(float), cudaMemcpyHostToDevice, e.stream);
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(e.pyr[1][0][0], im_b, g.img_elems * sizeof(float), cudaMemcpyHostToDevice, e.stream);
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(e.flow[0][0], flow, fb, cudaMemcpyHostToDevice, e.stream);
+    if (ce == cudaSuccess) {
+      e.begin_run();
+      launch_varref_level(e.pyr[0][0][0], e.pyr[1][0][0], e.flow[0][0], g, *params, camlr, e.vb, 1, e.stream, &e.stats);
+      ce = cudaGetLastError();
+    }
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(flow, e.flow[0][0], fb, cudaMemcpyDeviceToHost, e.stream);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(e.stream);
+    if (ce != cudaSuccess) rc = fail(DISB200_ECUDA, std::string("varref_level: ") + cudaGetErrorString(ce));
+  }
+  e.destroy();
+  return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,271 @@
+// Stage 2 — per-patch inverse-compositional Gauss-Newton search.
+//
+// One kernel does, per patch, what the reference spreads over
+//   PatClass::InitializePatch / getPatchStaticNNGrad / ComputeHessian   (patch.cpp:55-86,298-343)
+//   PatGridClass::InitializeFromCoarserOF                               (patchgrid.cpp:195-211)
+//   PatClass::OptimizeStart / OptimizeIter / OptimizeComputeErrImg      (patch.cpp:118-210,275-295)
+//   getPatchStaticBil / LossComputeErrorImage                           (patch.cpp:221-273,346-413)
+// A sub-warp of G lanes owns one patch; value n of the patch (row-major, channels
+// interleaved) lives in lane n % G, slot n / G, so that a load instruction of the group
+// touches consecutive floats of the target image.  Template, gradients, the residual and
+// its weight stay in registers; reductions are xor-butterflies, which leave every lane with
+// the bit-identical sum, so all scalar state (p_iter, convergence flags) is replicated and
+// the loop is uniform inside a group.  Groups of one warp may need different trip counts
+// (min_iter < max_iter): the loop runs until every group of the warp has converged and
+// finished groups stop committing state.
+#include "dis_internal.h"
+
+namespace disb200 {
+
+template <int G>
+__device__ __forceinline__ float gsum(float v) {
+#pragma unroll
+  for (int m = G / 2; m > 0; m >>= 1) v += __shfl_xor_sync(0xffffffffu, v, m);
+  return v;
+}
+
+template <int PSZ, int C, int G, bool OF>
+__global__ void __launch_bounds__(128)
+patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
+  constexpr int NV = PSZ * PSZ * C;
+  constexpr int VPL = (NV + G - 1) / G;
+  constexpr int ROWLEN = PSZ * C;
+  constexpr int LB = -PSZ / 2;
+  constexpr int NOP = OF ? 2 : 1;
+
+  const int lane = threadIdx.x % G;
+  const int ip_raw = blockIdx.x * (blockDim.x / G) + threadIdx.x / G;
+  const bool active = ip_raw < g.npatch;
+  const int ip = active ? ip_raw : g.npatch - 1;
+  const int pair = blockIdx.y;
+  const int rowstride = g.tw * C;
+
+  const float* timg = a.tmpl_img + (size_t)pair * g.img_elems;
+  const float* tdxp = a.tmpl_dx + (size_t)pair * g.img_elems;
+  const float* tdyp = a.tmpl_dy + (size_t)pair * g.img_elems;
+  const float* qimg = a.tgt_img + (size_t)pair * g.img_elems;
+
+  // patch index is column-major: ip = x * noph + y (patchgrid.cpp:64)
+  const int gx = ip / g.noph, gy = ip - gx * g.noph;
+  const float ptrx = (float)(gx * g.steps + g.offw);
+  const float ptry = (float)(gy * g.steps + g.offh);
+
+  int off[VPL];
+  bool val[VPL];
+#pragma unroll
+  for (int k = 0; k < VPL; ++k) {
+    const int n = k * G + lane;
+    val[k] = n < NV;
+    const int nn = val[k] ? n : 0;
+    const int row = nn / ROWLEN;
+    off[k] = row * rowstride + (nn - row * ROWLEN);
+  }
+
+  // ---- template, gradients, Hessian (patch.cpp:298-343, 69-86) ----
+  float t[VPL], dx[VPL], dy[VPL];
+  {
+    const int px = (int)ptrx + g.pad + LB, py = (int)ptry + g.pad + LB;
+    const int base = (py * g.tw + px) * C;
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) {
+      t[k] = val[k] ? __ldg(timg + base + off[k]) : 0.f;
+      dx[k] = val[k] ? __ldg(tdxp + base + off[k]) : 0.f;
+      dy[k] = (OF && val[k]) ? __ldg(tdyp + base + off[k]) : 0.f;
+      s += t[k];
+    }
+    if (o.patnorm > 0) {
+      const float m = gsum<G>(s) / (float)NV;
+#pragma unroll
+      for (int k = 0; k < VPL; ++k) t[k] = val[k] ? t[k] - m : 0.f;
+    }
+  }
+  float H00 = 0.f, H01 = 0.f, H11 = 0.f;
+#pragma unroll
+  for (int k = 0; k < VPL; ++k) {
+    H00 += dx[k] * dx[k];
+    if (OF) { H01 += dx[k] * dy[k]; H11 += dy[k] * dy[k]; }
+  }
+  H00 = gsum<G>(H00);
+  float l00, l10 = 0.f, l11 = 1.f;
+  if (OF) {
+    H01 = gsum<G>(H01);
+    H11 = gsum<G>(H11);
+    if (H00 * H11 - H01 * H01 == 0.f) { H00 = (float)((double)H00 + 1e-10); H11 = (float)((double)H11 + 1e-10); }
+    // Eigen LLT, unblocked: stop at the first non-positive pivot, rest left unfactored
+    l00 = H00; l10 = H01; l11 = H11;
+    if (l00 > 0.f) {
+      l00 = sqrtf(l00);
+      l10 = l10 / l00;
+      const float x = l11 - l10 * l10;
+      if (x > 0.f) l11 = sqrtf(x);
+    }
+  } else {
+    if (H00 == 0.f) H00 = (float)((double)H00 + 1e-10);
+    l00 = H00;
+    if (l00 > 0.f) l00 = sqrtf(l00);
+  }
+
+  // ---- start (patchgrid.cpp:195-211, patch.cpp:97-154) ----
+  float p_in0 = 0.f, p_in1 = 0.f;
+  if (a.flow_prev) {
+    const int x = (int)floorf(ptrx / 2), y = (int)floorf(ptry / 2);
+    const float* fp = a.flow_prev + (size_t)pair * a.flow_prev_stride + (size_t)(y * (g.w / 2) + x) * NOP;
+    p_in0 = fp[0] * 2;
+    if (OF) p_in1 = fp[1] * 2;
+  }
+  float p0 = p_in0, p1 = p_in1;
+  float ptx = ptrx + p0, pty = OF ? ptry + p1 : ptry;
+  const float stx = ptx, sty = pty;
+  float dp0 = 0.f, dp1 = 0.f;          // delta_p
+  float dpsq_init = 1e-10f, mares = 1e5f;
+  int cnt = 0;
+  const bool start_ok = !(ptx < g.lb || pty < g.lb || ptx > g.ubw || pty > g.ubh);
+  bool conv = !start_ok;
+
+  float pd[VPL], pw[VPL];
+#pragma unroll
+  for (int k = 0; k < VPL; ++k) { pd[k] = 0.f; pw[k] = 0.f; }
+  float s0 = 0.f, s1 = 0.f;            // projections of the current residual on the sd images
+
+  const float bsq = o.normoutlier * o.normoutlier, bsq2 = bsq * 2.0f;
+
+  // One evaluation of OptimizeComputeErrImg at (ex, ey); `commit` selects whether this group
+  // still updates its state.  Returns through the captured variables.
+  bool first = true;
+  while (true) {
+    const bool upd = first ? start_ok : !conv;
+    float np0 = p0, np1 = p1, nptx = ptx, npty = pty, ndp0 = dp0, ndp1 = dp1;
+    bool nconv = conv;
+    int ncnt = cnt;
+    if (!first) {
+      ncnt = cnt + 1;
+      // delta_p = Hes.llt().solve(delta_p) (patch.cpp:175-182)
+      if (OF) {
+        const float y0 = s0 / l00;
+        const float y1 = (s1 - l10 * y0) / l11;
+        const float x1 = y1 / l11;
+        const float x0 = (y0 - l10 * x1) / l00;
+        ndp0 = x0; ndp1 = x1;
+        np0 = p0 - ndp0; np1 = p1 - ndp1;
+      } else {
+        ndp0 = (s0 / l00) / l00;
+        np0 = p0 - ndp0;
+        np0 = (a.camlr == 0) ? fminf(np0, 0.f) : fmaxf(np0, 0.f);      // patch.cpp:186-191
+      }
+      nptx = ptrx + np0;
+      if (OF) npty = ptry + np1;
+      const float ddx = stx - nptx, ddy = sty - npty;
+      if (sqrtf(ddx * ddx + ddy * ddy) > o.outlierthresh || nptx < g.lb || npty < g.lb || nptx > g.ubw || npty > g.ubh) {
+        np0 = p_in0; np1 = p_in1;                                    // patch.cpp:202-205
+        nptx = ptrx + np0;
+        if (OF) npty = ptry + np1;
+        nconv = true;
+      }
+    }
+    // sample position: finished / invalid groups sample their reference position (always in range)
+    const float ex = upd ? nptx : ptrx, ey = upd ? npty : ptry;
+    // getPatchStaticBil (patch.cpp:346-413)
+    const int ix1 = (int)ceilf(ex + .00001f), iy1 = (int)ceilf(ey + .00001f);
+    const float rx = ex - floorf(ex), ry = ey - floorf(ey);
+    const float w0 = rx * ry, w1 = (1.f - rx) * ry, w2 = rx * (1.f - ry), w3 = (1.f - rx) * (1.f - ry);
+    const float* qb = qimg + ((iy1 + g.pad + LB) * g.tw + (ix1 + g.pad + LB)) * C;
+    float q[VPL];
+    float qs = 0.f;
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) {
+      const float* p = qb + off[k];
+      const float va = __ldg(p), vb = __ldg(p - C), vc = __ldg(p - rowstride), vd = __ldg(p - rowstride - C);
+      q[k] = val[k] ? w0 * va + w1 * vb + w2 * vc + w3 * vd : 0.f;
+      qs += q[k];
+    }
+    float m = 0.f;
+    if (o.patnorm > 0) m = gsum<G>(qs) / (float)NV;
+    float ns0 = 0.f, ns1 = 0.f, wsum = 0.f;
+    float npd[VPL], npw[VPL];
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) {
+      const float d = (q[k] - m) - t[k];
+      float vpd, vpw;
+      if (o.costfct == 0) {                                         // patch.cpp:228-241
+        vpd = d; vpw = fabsf(d);
+      } else if (o.costfct == 1) {                                  // :242-257
+        vpw = sqrtf(fabsf(d));
+        vpd = copysignf(vpw, d);
+      } else {                                                      // :258-272
+        vpw = sqrtf((sqrtf(1.0f + (d * d) / bsq) - 1.0f) * bsq2);
+        vpd = copysignf(vpw, d);
+      }
+      if (!val[k]) { vpd = 0.f; vpw = 0.f; }
+      npd[k] = vpd; npw[k] = vpw;
+      ns0 += dx[k] * vpd;
+      if (OF) ns1 += dy[k] * vpd;
+      wsum += fabsf(vpw);
+    }
+    ns0 = gsum<G>(ns0);
+    if (OF) ns1 = gsum<G>(ns1);
+    wsum = gsum<G>(wsum);
+    if (upd) {
+      // OptimizeComputeErrImg bookkeeping (patch.cpp:283-293)
+      const float dpsq = OF ? ndp0 * ndp0 + ndp1 * ndp1 : ndp0 * ndp0;
+      if (ncnt == 1) dpsq_init = dpsq;
+      const float mares_old = mares;
+      const float nmares = wsum / (float)NV;
+      if (!((ncnt < o.max_iter) & (nmares > o.res_thresh) &
+            ((ncnt < o.min_iter) | (dpsq / dpsq_init >= o.dp_thresh_sq)) &
+            ((ncnt < o.min_iter) | (nmares / mares_old <= o.dr_thresh))))
+        nconv = true;
+      mares = nmares;
+      p0 = np0; p1 = np1; ptx = nptx; pty = npty; dp0 = ndp0; dp1 = ndp1; cnt = ncnt; conv = nconv;
+      s0 = ns0; s1 = ns1;
+#pragma unroll
+      for (int k = 0; k < VPL; ++k) { pd[k] = npd[k]; pw[k] = npw[k]; }
+    }
+    first = false;
+    if (!__any_sync(0xffffffffu, !conv)) break;
+  }
+
+  if (active) {
+    const size_t pi = (size_t)pair * g.npatch + ip;
+    if (lane == 0) {
+      a.p_iter[pi * NOP] = p0;
+      if (OF) a.p_iter[pi * NOP + 1] = p1;
+      if (a.pt_iter) { a.pt_iter[pi * 2] = ptx; a.pt_iter[pi * 2 + 1] = pty; }
+    }
+    float* wout = a.pweight + pi * NV;
+#pragma unroll
+    for (int k = 0; k < VPL; ++k)
+      if (val[k]) wout[k * G + lane] = pw[k];
+  }
+  (void)pd;
+}
+
+template <int PSZ, int C, int G>
+static void launch_one(const PatchArgs& a, const LevelGeom& g, const OptConst& o, int n, cudaStream_t s) {
+  const int threads = 128, per_block = threads / G;
+  dim3 grd((g.npatch + per_block - 1) / per_block, n);
+  if (o.mode == DISB200_MODE_OF)
+    patch_search_kernel<PSZ, C, G, true><<<grd, threads, 0, s>>>(a, g, o);
+  else
+    patch_search_kernel<PSZ, C, G, false><<<grd, threads, 0, s>>>(a, g, o);
+}
+
+bool launch_patch_search(const PatchArgs& a, const LevelGeom& g, const OptConst& o, int n, cudaStream_t s,
+                         LaunchStats* st) {
+  const int key = o.psz * 10 + o.noc;
+  switch (key) {
+    case 41: launch_one<4, 1, 8>(a, g, o, n, s); break;
+    case 81: launch_one<8, 1, 8>(a, g, o, n, s); break;
+    case 121: launch_one<12, 1, 16>(a, g, o, n, s); break;
+    case 161: launch_one<16, 1, 32>(a, g, o, n, s); break;
+    case 43: launch_one<4, 3, 8>(a, g, o, n, s); break;
+    case 83: launch_one<8, 3, 32>(a, g, o, n, s); break;
+    case 123: launch_one<12, 3, 32>(a, g, o, n, s); break;
+    case 163: launch_one<16, 3, 32>(a, g, o, n, s); break;
+    default: return false;
+  }
+  st->launches++;
+  return true;
+}
+
+}  // namespace disb200

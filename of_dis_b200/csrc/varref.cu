@@ -1,0 +1,561 @@
+// Stage 4 — variational refinement of one level (VarRefClass, refine_variational.cpp:25-342
+// and the FDF1.0.1 routines it drives).  All arithmetic is fp32 in the reference's operation
+// order and this file is compiled with -fmad=false, so on identical inputs the lexicographic
+// mode reproduces the reference bit for bit.
+//
+// Kernels (all batched over frame pairs through blockIdx.z / blockIdx.y):
+//   warp_kernel     image_warp + the avg/Iz part of get_derivatives   (opticalflow_aux.c:33-99)
+//   deriv1_kernel   Ix Iy Ixz Iyz   (5-tap [1,-8,0,8,-1]/12, replicate border; image.cpp:467-640)
+//   deriv2_kernel   Ixx Ixy Iyy
+//   smooth_kernel   per-pixel diffusivity s of compute_smoothness     (opticalflow_aux.c:138-159)
+//   system_kernel   compute_data / compute_data_DE + sub_laplacian + the 2x2 block inverse of
+//                   sor_coupled's first sweep                          (opticalflow_aux.c:194-223,
+//                   409-747; solver.c:122-128)
+//   sor_*_kernel    lexicographic SOR as an anti-diagonal wavefront    (solver.c:83-471)
+//   finish_kernel   flow += increment (with the DE sign clamp)         (refine_variational.cpp:208-227,301-323)
+// The planes read by the refinement are the unpadded interiors of the padded pyramid arrays,
+// addressed in place (the reference copies them out first, refine_variational.cpp:120-149).
+#include "dis_internal.h"
+
+namespace disb200 {
+
+namespace {
+
+__device__ __forceinline__ int clampi(int v, int lo, int hi) { return min(max(v, lo), hi); }
+
+// coefficients of convolution_new(2, {0,-8/12,1/12}, 0): {1/12, -8/12, -0, 8/12, -1/12}
+__device__ __forceinline__ float tap5(float s0, float s1, float s2, float s3, float s4) {
+  const float h1 = -8.0f / 12.0f, h2 = 1.0f / 12.0f;
+  return h2 * s0 + ((h1 * s1 + (-0.0f) * s2) + ((-h1) * s3 + (-h2) * s4));
+}
+// convolution_new(1, {0,-0.5}, 0): {-0.5, -0, 0.5}
+__device__ __forceinline__ float tap3(float s0, float s1, float s2) { return -0.5f * s0 + ((-0.0f) * s1 + 0.5f * s2); }
+
+__device__ __forceinline__ float mla(float a, float b, float c) { return a + b * c; }
+__device__ __forceinline__ float mls(float a, float b, float c) { return a - b * c; }
+
+struct Dims {
+  int w, h, pad, tw;
+  size_t img_elems;   // padded array elements per pair
+  size_t plane;       // plane capacity per pair (elements)
+};
+
+// ---------------------------------------------------------------------------------------
+template <int C, bool OF>
+__global__ void warp_kernel(const float* __restrict__ im_a, const float* __restrict__ im_b,
+                            const float* __restrict__ flow, Dims d, float* __restrict__ avg,
+                            float* __restrict__ Iz, float* __restrict__ mask) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y, pair = blockIdx.z;
+  if (i >= d.w) return;
+  constexpr int NOP = OF ? 2 : 1;
+  const size_t pix = (size_t)j * d.w + i;
+  const float* fl = flow + ((size_t)pair * d.w * d.h + pix) * NOP;
+  const float wx = fl[0], wy = OF ? fl[1] : 0.f;
+  const float xx = (float)i + wx, yy = (float)j + wy;
+  const float fx = floorf(xx), fy = floorf(yy);
+  const int x = (int)fx, y = (int)fy;
+  const float dx = xx - fx, dy = yy - fy;
+  mask[(size_t)pair * d.plane + pix] = (xx >= 0.f && xx <= (float)(d.w - 1) && yy >= 0.f && yy <= (float)(d.h - 1)) ? 1.f : 0.f;
+  const int x1 = clampi(x, 0, d.w - 1) + d.pad, x2 = clampi(x + 1, 0, d.w - 1) + d.pad;
+  const int y1 = clampi(y, 0, d.h - 1) + d.pad, y2 = clampi(y + 1, 0, d.h - 1) + d.pad;
+  const float* A = im_a + (size_t)pair * d.img_elems;
+  const float* B = im_b + (size_t)pair * d.img_elems;
+#pragma unroll
+  for (int c = 0; c < C; ++c) {
+    const float s11 = __ldg(B + ((size_t)y1 * d.tw + x1) * C + c), s21 = __ldg(B + ((size_t)y1 * d.tw + x2) * C + c);
+    const float s12 = __ldg(B + ((size_t)y2 * d.tw + x1) * C + c), s22 = __ldg(B + ((size_t)y2 * d.tw + x2) * C + c);
+    const float w2 = s11 * (1.0f - dx) * (1.0f - dy) + s21 * dx * (1.0f - dy) + s12 * (1.0f - dx) * dy + s22 * dx * dy;
+    const float i1 = __ldg(A + ((size_t)(j + d.pad) * d.tw + (i + d.pad)) * C + c);
+    const size_t o = ((size_t)pair * C + c) * d.plane + pix;
+    avg[o] = 0.5f * (w2 + i1);
+    Iz[o] = w2 - i1;
+  }
+}
+
+__device__ __forceinline__ float conv5h(const float* p, int i, int j, int w) {
+  const float* r = p + (size_t)j * w;
+  return tap5(r[clampi(i - 2, 0, w - 1)], r[clampi(i - 1, 0, w - 1)], r[i], r[clampi(i + 1, 0, w - 1)], r[clampi(i + 2, 0, w - 1)]);
+}
+__device__ __forceinline__ float conv5v(const float* p, int i, int j, int w, int h) {
+  return tap5(p[(size_t)clampi(j - 2, 0, h - 1) * w + i], p[(size_t)clampi(j - 1, 0, h - 1) * w + i], p[(size_t)j * w + i],
+              p[(size_t)clampi(j + 1, 0, h - 1) * w + i], p[(size_t)clampi(j + 2, 0, h - 1) * w + i]);
+}
+
+// blockIdx.z enumerates (pair, channel) planes
+__global__ void deriv1_kernel(const float* __restrict__ avg, const float* __restrict__ Iz, Dims d,
+                              float* __restrict__ Ix, float* __restrict__ Iy, float* __restrict__ Ixz,
+                              float* __restrict__ Iyz) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
+  if (i >= d.w) return;
+  const size_t po = (size_t)blockIdx.z * d.plane, pix = (size_t)j * d.w + i;
+  Ix[po + pix] = conv5h(avg + po, i, j, d.w);
+  Iy[po + pix] = conv5v(avg + po, i, j, d.w, d.h);
+  Ixz[po + pix] = conv5h(Iz + po, i, j, d.w);
+  Iyz[po + pix] = conv5v(Iz + po, i, j, d.w, d.h);
+}
+__global__ void deriv2_kernel(const float* __restrict__ Ix, const float* __restrict__ Iy, Dims d,
+                              float* __restrict__ Ixx, float* __restrict__ Ixy, float* __restrict__ Iyy) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
+  if (i >= d.w) return;
+  const size_t po = (size_t)blockIdx.z * d.plane, pix = (size_t)j * d.w + i;
+  Ixx[po + pix] = conv5h(Ix + po, i, j, d.w);
+  Ixy[po + pix] = conv5v(Ix + po, i, j, d.w, d.h);
+  Iyy[po + pix] = conv5v(Iy + po, i, j, d.w, d.h);
+}
+
+// uu = wx + du (DE: clamped), read on the fly
+template <bool OF>
+__device__ __forceinline__ void load_uv(const float* flow, const float* du, size_t pix, int camlr, float& u, float& v) {
+  if (OF) {
+    const float2 f = *reinterpret_cast<const float2*>(flow + pix * 2);
+    const float2 q = *reinterpret_cast<const float2*>(du + pix * 2);
+    u = f.x + q.x;
+    v = f.y + q.y;
+  } else {
+    const float t = flow[pix] + du[pix];
+    u = camlr == 0 ? fminf(t, 0.f) : fmaxf(t, 0.f);
+    v = 0.f;
+  }
+}
+
+// compute_smoothness, first half: s = (alpha/4) / sqrt(ux^2+uy^2+vx^2+vy^2 + eps)
+template <bool OF>
+__global__ void smooth_kernel(const float* __restrict__ flow, const float* __restrict__ du, Dims d, int camlr,
+                              float quarter_alpha, int first_iter, float* __restrict__ s) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y, pair = blockIdx.z;
+  if (i >= d.w) return;
+  constexpr int NOP = OF ? 2 : 1;
+  const float* fl = flow + (size_t)pair * d.w * d.h * NOP;
+  const float* q = du + (size_t)pair * d.plane * NOP;
+  const int xm = clampi(i - 1, 0, d.w - 1), xp = clampi(i + 1, 0, d.w - 1), ym = clampi(j - 1, 0, d.h - 1), yp = clampi(j + 1, 0, d.h - 1);
+  float ul, vl, uc, vc, ur, vr, ut, vt, ub, vb;
+  // first_iter: uu = wx exactly (memcpy in the reference, no clamp: refine_variational.cpp:189,288)
+  auto ld = [&](int x, int y, float& u, float& v) {
+    const size_t pix = (size_t)y * d.w + x;
+    if (first_iter) {
+      u = fl[pix * NOP];
+      v = OF ? fl[pix * NOP + 1] : 0.f;
+    } else {
+      load_uv<OF>(fl, q, pix, camlr, u, v);
+    }
+  };
+  ld(xm, j, ul, vl); ld(i, j, uc, vc); ld(xp, j, ur, vr); ld(i, ym, ut, vt); ld(i, yp, ub, vb);
+  const float ux = tap3(ul, uc, ur), vx = tap3(vl, vc, vr), uy = tap3(ut, uc, ub), vy = tap3(vt, vc, vb);
+  const float eps = 0.001f * 0.001f;
+  const float t = eps + ((ux * ux + uy * uy) + (vx * vx + vy * vy));
+  s[(size_t)pair * d.plane + (size_t)j * d.w + i] = quarter_alpha / sqrtf(t);
+}
+
+}  // namespace
+}  // namespace disb200
+
+namespace disb200 {
+namespace {
+
+struct DerivPtrs {
+  const float *Ix, *Iy, *Iz, *Ixx, *Ixy, *Iyy, *Ixz, *Iyz;
+};
+
+#define DNORM (0.1f * 0.1f)
+#define EPSC (0.001f * 0.001f)
+#define EPSG (0.001f * 0.001f)
+
+// compute_data (opticalflow_aux.c:409-594), one pixel.  P(plane, c) reads channel c.
+template <int C>
+__device__ __forceinline__ void data_term_of(const DerivPtrs& D, size_t o, size_t cstride, float m, float u, float v,
+                                             float hd3, float hg3, float& A11, float& A12, float& A22, float& B1,
+                                             float& B2) {
+#define P(p, c) __ldg(D.p + o + (size_t)(c)*cstride)
+  A11 = 0.f; A12 = 0.f; A22 = 0.f; B1 = 0.f; B2 = 0.f;
+  float tmp, tmp2, tmp3, tmpx, tmpy, tmpxy, n1, n2, n3 = 0.f, n4 = 0.f, n5 = 0.f, n6 = 0.f;
+  if (hd3 != 0.f) {
+    tmpx = P(Ix, 0); tmpy = P(Iy, 0);
+    tmp2 = mla(mla(P(Iz, 0), tmpx, u), tmpy, v);
+    n1 = mla(mla(DNORM, tmpx, tmpx), tmpy, tmpy);
+    tmp = (tmp2 * tmp2) / n1;
+    if (C == 3) {
+      tmpx = P(Ix, 1); tmpy = P(Iy, 1);
+      tmp2 = mla(mla(P(Iz, 1), tmpx, u), tmpy, v);
+      n2 = mla(mla(DNORM, tmpx, tmpx), tmpy, tmpy);
+      tmp = tmp + (tmp2 * tmp2) / n2;
+      tmpx = P(Ix, 2); tmpy = P(Iy, 2);
+      tmp2 = mla(mla(P(Iz, 2), tmpx, u), tmpy, v);
+      n3 = mla(mla(DNORM, tmpx, tmpx), tmpy, tmpy);
+      tmp = tmp + (tmp2 * tmp2) / n3;
+      tmp = (m * hd3) / sqrtf(EPSC + tmp);
+      tmp3 = tmp / n3; tmp2 = tmp3 * tmpx; tmp3 = tmp3 * tmpy;
+      A11 = mla(A11, tmp2, tmpx); A12 = mla(A12, tmp2, tmpy); A22 = mla(A22, tmp3, tmpy);
+      B1 = mls(B1, tmp2, P(Iz, 2)); B2 = mls(B2, tmp3, P(Iz, 2));
+      tmpx = P(Ix, 1); tmpy = P(Iy, 1);
+      tmp3 = tmp / n2; tmp2 = tmp3 * tmpx; tmp3 = tmp3 * tmpy;
+      A11 = mla(A11, tmp2, tmpx); A12 = mla(A12, tmp2, tmpy); A22 = mla(A22, tmp3, tmpy);
+      B1 = mls(B1, tmp2, P(Iz, 1)); B2 = mls(B2, tmp3, P(Iz, 1));
+      tmpx = P(Ix, 0); tmpy = P(Iy, 1);   // sic: Iy of channel 2 (opticalflow_aux.c:496)
+    } else {
+      tmp = (m * hd3) / sqrtf(mla(EPSC, 3.f, tmp));
+    }
+    tmp3 = tmp / n1; tmp2 = tmp3 * tmpx; tmp3 = tmp3 * tmpy;
+    A11 = mla(A11, tmp2, tmpx); A12 = mla(A12, tmp2, tmpy); A22 = mla(A22, tmp3, tmpy);
+    B1 = mls(B1, tmp2, P(Iz, 0)); B2 = mls(B2, tmp3, P(Iz, 0));
+  }
+  tmpx = P(Ixx, 0); tmpy = P(Iyy, 0); tmpxy = P(Ixy, 0);
+  tmp2 = mla(mla(P(Ixz, 0), tmpx, u), tmpxy, v);
+  tmp3 = mla(mla(P(Iyz, 0), tmpxy, u), tmpy, v);
+  tmpxy = tmpxy * tmpxy;
+  n1 = mla(tmpxy + DNORM, tmpx, tmpx);
+  n2 = mla(tmpxy + DNORM, tmpy, tmpy);
+  tmp = (tmp2 * tmp2) / n1 + (tmp3 * tmp3) / n2;
+  if (C == 3) {
+    tmpx = P(Ixx, 1); tmpy = P(Iyy, 1); tmpxy = P(Ixy, 1);
+    tmp2 = mla(mla(P(Ixz, 1), tmpx, u), tmpxy, v);
+    tmp3 = mla(mla(P(Iyz, 1), tmpxy, u), tmpy, v);
+    tmpxy = tmpxy * tmpxy;
+    n3 = mla(tmpxy + DNORM, tmpx, tmpx);
+    n4 = mla(tmpxy + DNORM, tmpy, tmpy);
+    // sic: the channel sums are assigned, not accumulated (opticalflow_aux.c:529,538)
+    tmpx = P(Ixx, 2); tmpy = P(Iyy, 2); tmpxy = P(Ixy, 2);
+    tmp2 = mla(mla(P(Ixz, 2), tmpx, u), tmpxy, v);
+    tmp3 = mla(mla(P(Iyz, 2), tmpxy, u), tmpy, v);
+    tmpxy = tmpxy * tmpxy;
+    n5 = mla(tmpxy + DNORM, tmpx, tmpx);
+    n6 = mla(tmpxy + DNORM, tmpy, tmpy);
+    tmp = (tmp2 * tmp2) / n5 + (tmp3 * tmp3) / n6;
+    tmp = (m * hg3) / sqrtf(EPSG + tmp);
+    tmp2 = tmp / n6; tmp3 = tmp / n5;
+    A11 = mla(mla(A11, tmp3, tmpx * tmpx), tmp2, tmpxy);
+    A22 = mla(mla(A22, tmp2, tmpy * tmpy), tmp3, tmpxy);
+    tmpxy = P(Ixy, 2);
+    A12 = mla(A12, mla(tmp3 * tmpx, tmp2, tmpy), tmpxy);
+    B1 = mls(mls(B1, tmp3 * tmpx, P(Ixz, 2)), tmp2 * tmpxy, P(Iyz, 2));
+    B2 = mls(mls(B2, tmp2 * tmpy, P(Iyz, 2)), tmp3 * tmpxy, P(Ixz, 2));
+    tmp2 = tmp / n4; tmp3 = tmp / n3;
+    tmpx = P(Ixx, 1); tmpy = P(Iyy, 1); tmpxy = P(Ixy, 1);
+    A12 = mla(A12, mla(tmp3 * tmpx, tmp2, tmpy), tmpxy);
+    B1 = mls(mls(B1, tmp3 * tmpx, P(Ixz, 1)), tmp2 * tmpxy, P(Iyz, 1));
+    B2 = mls(mls(B2, tmp2 * tmpy, P(Iyz, 1)), tmp3 * tmpxy, P(Ixz, 1));
+    tmpxy = tmpxy * tmpxy;
+    A11 = mla(mla(A11, tmp3, tmpx * tmpx), tmp2, tmpxy);
+    A22 = mla(mla(A22, tmp2, tmpy * tmpy), tmp3, tmpxy);
+    tmpx = P(Ixx, 0); tmpy = P(Iyy, 0);
+  } else {
+    tmp = (m * hg3) / sqrtf(mla(EPSG, 3.f, tmp));
+  }
+  tmp2 = tmp / n2; tmp3 = tmp / n1;
+  tmpxy = P(Ixy, 0);
+  A12 = mla(A12, mla(tmp3 * tmpx, tmp2, tmpy), tmpxy);
+  B1 = mls(mls(B1, tmp3 * tmpx, P(Ixz, 0)), tmp2 * tmpxy, P(Iyz, 0));
+  B2 = mls(mls(B2, tmp2 * tmpy, P(Iyz, 0)), tmp3 * tmpxy, P(Ixz, 0));
+  tmpxy = tmpxy * tmpxy;
+  A11 = mla(mla(A11, tmp3, tmpx * tmpx), tmp2, tmpxy);
+  A22 = mla(mla(A22, tmp2, tmpy * tmpy), tmp3, tmpxy);
+  if (C == 1) { A11 *= 3.f; A12 *= 3.f; A22 *= 3.f; B1 *= 3.f; B2 *= 3.f; }
+  (void)n4;
+#undef P
+}
+
+// compute_data_DE (opticalflow_aux.c:602-747), one pixel
+template <int C>
+__device__ __forceinline__ void data_term_de(const DerivPtrs& D, size_t o, size_t cstride, float m, float u,
+                                             float hd3, float hg3, float& A11, float& B1) {
+#define P(p, c) __ldg(D.p + o + (size_t)(c)*cstride)
+  A11 = 0.f; B1 = 0.f;
+  float tmp, tmp2, tmp3, tmpx, tmpy, tmpxy, n1, n2, n3 = 0.f, n4 = 0.f, n5 = 0.f, n6 = 0.f;
+  if (hd3 != 0.f) {
+    tmpx = P(Ix, 0); tmpy = P(Iy, 0);
+    tmp2 = mla(P(Iz, 0), tmpx, u);
+    n1 = mla(mla(DNORM, tmpy, tmpy), tmpx, tmpx);
+    tmp = (tmp2 * tmp2) / n1;
+    if (C == 3) {
+      tmpx = P(Ix, 1); tmpy = P(Iy, 1);
+      tmp2 = mla(P(Iz, 1), tmpx, u);
+      n2 = mla(mla(DNORM, tmpy, tmpy), tmpx, tmpx);
+      tmp = tmp + (tmp2 * tmp2) / n2;
+      tmpx = P(Ix, 2); tmpy = P(Iy, 2);
+      tmp2 = mla(P(Iz, 2), tmpx, u);
+      n3 = mla(mla(DNORM, tmpy, tmpy), tmpx, tmpx);
+      tmp = tmp + (tmp2 * tmp2) / n3;
+      tmp = (m * hd3) / sqrtf(EPSC + tmp);
+      tmp2 = (tmp / n3) * tmpx;
+      A11 = mla(A11, tmp2, tmpx); B1 = mls(B1, tmp2, P(Iz, 2));
+      tmpx = P(Ix, 1);
+      tmp2 = (tmp / n2) * tmpx;
+      A11 = mla(A11, tmp2, tmpx); B1 = mls(B1, tmp2, P(Iz, 1));
+      tmpx = P(Ix, 0);
+    } else {
+      tmp = (m * hd3) / sqrtf(mla(EPSC, 3.f, tmp));
+    }
+    tmp2 = (tmp / n1) * tmpx;
+    A11 = mla(A11, tmp2, tmpx); B1 = mls(B1, tmp2, P(Iz, 0));
+  }
+  tmpx = P(Ixx, 0); tmpy = P(Iyy, 0); tmpxy = P(Ixy, 0);
+  tmp2 = mla(P(Iyz, 0), tmpxy, u);
+  tmpxy = mla(DNORM, tmpxy, tmpxy);
+  n1 = mla(tmpxy, tmpx, tmpx);
+  n2 = mla(tmpxy, tmpy, tmpy);
+  tmp = (tmp2 * tmp2) / n2;
+  tmp2 = mla(P(Ixz, 0), tmpx, u);
+  tmp = tmp + (tmp2 * tmp2) / n1;
+  if (C == 3) {
+    tmpx = P(Ixx, 1); tmpy = P(Iyy, 1); tmpxy = P(Ixy, 1);
+    tmp2 = mla(P(Iyz, 1), tmpxy, u);
+    tmpxy = mla(DNORM, tmpxy, tmpxy);
+    n3 = mla(tmpxy, tmpx, tmpx);
+    n4 = mla(tmpxy, tmpy, tmpy);
+    tmp = tmp + (tmp2 * tmp2) / n4;
+    tmp2 = mla(P(Ixz, 1), tmpx, u);
+    tmp = tmp + (tmp2 * tmp2) / n3;
+    tmpx = P(Ixx, 2); tmpy = P(Iyy, 2); tmpxy = P(Ixy, 2);
+    tmp2 = mla(P(Iyz, 2), tmpxy, u);
+    tmpxy = mla(DNORM, tmpxy, tmpxy);
+    n5 = mla(tmpxy, tmpx, tmpx);
+    n6 = mla(tmpxy, tmpy, tmpy);
+    tmp = tmp + (tmp2 * tmp2) / n6;
+    tmp2 = mla(P(Ixz, 2), tmpx, u);
+    tmp = tmp + (tmp2 * tmp2) / n5;
+    tmp = (m * hg3) / sqrtf(EPSG + tmp);
+    tmpxy = P(Ixy, 2);
+    tmp2 = (tmp / n6) * tmpxy; tmp3 = (tmp / n5) * tmpx;
+    A11 = mla(mla(A11, tmp3, tmpx), tmp2, tmpxy);
+    B1 = mls(mls(B1, tmp3, P(Ixz, 2)), tmp2, P(Iyz, 2));
+    tmpx = P(Ixx, 1); tmpy = P(Iyy, 1); tmpxy = P(Ixy, 1);
+    tmp2 = (tmp / n4) * tmpxy; tmp3 = (tmp / n3) * tmpx;
+    A11 = mla(mla(A11, tmp3, tmpx), tmp2, tmpxy);
+    B1 = mls(mls(B1, tmp3, P(Ixz, 1)), tmp2, P(Iyz, 1));
+    tmpx = P(Ixx, 0); tmpy = P(Iyy, 0);
+  } else {
+    tmp = (m * hg3) / sqrtf(mla(EPSG, 3.f, tmp));
+  }
+  tmpxy = P(Ixy, 0);
+  tmp2 = (tmp / n2) * tmpxy; tmp3 = (tmp / n1) * tmpx;
+  A11 = mla(mla(A11, tmp3, tmpx), tmp2, tmpxy);
+  B1 = mls(mls(B1, tmp3, P(Ixz, 0)), tmp2, P(Iyz, 0));
+  if (C == 1) { A11 *= 3.f; B1 *= 3.f; }
+  (void)tmpy;
+#undef P
+}
+
+// Data term + laplacian of the current flow into the right-hand side + (OF) inverse of the
+// 2x2 diagonal block.  Outputs per pixel: coef {hl, h, vt, v}; OF: inv {i11, i12, i22, 0},
+// rhs {b1, b2}; DE: inv {a11 + sum(psi)}, rhs {b1}.
+template <int C, bool OF>
+__global__ void system_kernel(DerivPtrs D, const float* __restrict__ mask, const float* __restrict__ s,
+                              const float* __restrict__ flow, const float* __restrict__ du, Dims d, float hd3,
+                              float hg3, float4* __restrict__ coef, float* __restrict__ inv, float* __restrict__ rhs) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y, pair = blockIdx.z;
+  if (i >= d.w) return;
+  constexpr int NOP = OF ? 2 : 1;
+  const int w = d.w, h = d.h;
+  const size_t pix = (size_t)j * w + i;
+  const size_t po = (size_t)pair * d.plane;
+  const float* sp = s + po;
+  const float sc = sp[pix];
+  // smooth_horiz / smooth_vert (opticalflow_aux.c:161-184): h(i) = s(i)+s(i+1), 0 in the last column
+  const float hh = i < w - 1 ? sc + sp[pix + 1] : 0.f;
+  const float hl = i > 0 ? sp[pix - 1] + sc : 0.f;
+  const float vv = j < h - 1 ? sc + sp[pix + w] : 0.f;
+  const float vt = j > 0 ? sp[pix - w] + sc : 0.f;
+  const float* fl = flow + (size_t)pair * w * h * NOP;
+  const float* q = du + po * NOP;
+  const float m = mask[po + pix];
+  const size_t o = (size_t)pair * C * d.plane + pix;
+  float b[NOP];
+  float A11, A12 = 0.f, A22 = 0.f;
+  if (OF) {
+    const float2 dd = *reinterpret_cast<const float2*>(q + pix * 2);
+    data_term_of<C>(D, o, d.plane, m, dd.x, dd.y, hd3, hg3, A11, A12, A22, b[0], b[NOP - 1]);
+  } else {
+    data_term_de<C>(D, o, d.plane, m, q[pix], hd3, hg3, A11, b[0]);
+  }
+  // sub_laplacian (opticalflow_aux.c:194-223): b = (((b - t(i-1)) + t(i)) - tv(j-1)) + tv(j)
+#pragma unroll
+  for (int k = 0; k < NOP; ++k) {
+    const float wc = fl[pix * NOP + k];
+    float bb = b[k];
+    if (i > 0) bb -= hl * (wc - fl[(pix - 1) * NOP + k]);
+    if (i < w - 1) bb += hh * (fl[(pix + 1) * NOP + k] - wc);
+    if (j > 0) bb -= vt * (wc - fl[(pix - w) * NOP + k]);
+    if (j < h - 1) bb += vv * (fl[(pix + w) * NOP + k] - wc);
+    b[k] = bb;
+  }
+  coef[po + pix] = make_float4(hl, hh, vt, vv);
+  if (OF) {
+    // solver.c:122-128,184,244
+    float dpsis;
+    if (j == 0) dpsis = hl + (hh + vv);
+    else if (j < h - 1) dpsis = (hl + hh) + (vt + vv);
+    else dpsis = hl + (hh + vt);
+    const float I11 = A22 + dpsis, I22 = A11 + dpsis;
+    const float det = I11 * I22 - A12 * A12;
+    reinterpret_cast<float4*>(inv)[po + pix] = make_float4(I11 / det, A12 / (0.f - det), I22 / det, 0.f);
+    reinterpret_cast<float2*>(rhs)[po + pix] = make_float2(b[0], b[NOP - 1]);
+  } else {
+    // solver.c:447-465: sum_dpsis accumulates top, left, bottom, right
+    float sum = 0.f;
+    if (j > 0) sum += vt;
+    if (i > 0) sum += hl;
+    if (j < h - 1) sum += vv;
+    if (i < w - 1) sum += hh;
+    inv[po + pix] = A11 + sum;
+    rhs[po + pix] = b[0];
+  }
+}
+
+}  // namespace
+}  // namespace disb200
+
+namespace disb200 {
+namespace {
+
+// One lexicographic SOR update of pixel (i, j) (solver.c:129-141,191-203,251-262 for OF;
+// solver.c:446-467 for DE).  `left` carries the value just written at (i-1, j).
+template <bool OF>
+__device__ __forceinline__ void sor_pixel(float* du, const float4* __restrict__ coef, const float* __restrict__ inv,
+                                          const float* __restrict__ rhs, int i, int j, int w, int h, float omega,
+                                          float2& left) {
+  const size_t pix = (size_t)j * w + i;
+  const float4 c = __ldg(coef + pix);   // {hl, h, vt, v}
+  if (OF) {
+    float2* q = reinterpret_cast<float2*>(du);
+    const float4 iv = __ldg(reinterpret_cast<const float4*>(inv) + pix);
+    const float2 b = __ldg(reinterpret_cast<const float2*>(rhs) + pix);
+    const float2 cur = q[pix];
+    float2 r = make_float2(0.f, 0.f), t = r, bt = r;
+    if (i < w - 1) r = q[pix + 1];
+    if (j > 0) t = q[pix - w];
+    if (j < h - 1) bt = q[pix + w];
+    float s1, s2;
+    if (j == 0) {
+      s1 = mla(mla(b.x, c.y, r.x), c.w, bt.x);
+      s2 = mla(mla(b.y, c.y, r.y), c.w, bt.y);
+    } else if (j < h - 1) {
+      s1 = mla(c.y * r.x, c.z, t.x) + mla(b.x, c.w, bt.x);
+      s2 = mla(c.y * r.y, c.z, t.y) + mla(b.y, c.w, bt.y);
+    } else {
+      s1 = mla(mla(b.x, c.y, r.x), c.z, t.x);
+      s2 = mla(mla(b.y, c.y, r.y), c.z, t.y);
+    }
+    float B1 = s1, B2 = s2;
+    if (i > 0) { B1 = c.x * left.x + s1; B2 = c.x * left.y + s2; }
+    float2 nw;
+    nw.x = cur.x + omega * (iv.x * B1 + iv.y * B2 - cur.x);
+    nw.y = cur.y + omega * (iv.y * B1 + iv.z * B2 - cur.y);
+    q[pix] = nw;
+    left = nw;
+  } else {
+    float sigma = 0.f;
+    if (j > 0) sigma -= c.z * du[pix - w];
+    if (i > 0) sigma -= c.x * left.x;
+    if (j < h - 1) sigma -= c.w * du[pix + w];
+    if (i < w - 1) sigma -= c.y * du[pix + 1];
+    const float A11 = __ldg(inv + pix), B1 = __ldg(rhs + pix) - sigma;
+    const float nw = (1.0f - omega) * du[pix] + omega * (B1 / A11);
+    du[pix] = nw;
+    left.x = nw;
+  }
+}
+
+// One CTA per frame pair.  Pixel (i, j) of sweep s needs (i-1, j) and (i, j-1) of sweep s and
+// (i+1, j), (i, j+1) of sweep s-1, so with one thread per (sweep, row) and thread (s, j)
+// working on column  step - j - 2 s  every dependency was produced at least one barrier
+// earlier: all sweeps of the call run as one skewed wavefront of  w + h - 1 + 2 (iters-1)
+// steps.  When rows x sweeps exceed the CTA, sweeps run one after another over row bands,
+// which is the same lexicographic order.
+template <bool OF>
+__global__ void __launch_bounds__(1024)
+sor_wavefront_kernel(float* du_all, const float4* __restrict__ coef_all, const float* __restrict__ inv_all,
+                     const float* __restrict__ rhs_all, Dims d, int iters, float omega, int pipelined) {
+  constexpr int NOP = OF ? 2 : 1;
+  const int pair = blockIdx.x, w = d.w, h = d.h;
+  float* du = du_all + (size_t)pair * d.plane * NOP;
+  const float4* coef = coef_all + (size_t)pair * d.plane;
+  const float* inv = inv_all + (size_t)pair * d.plane * (OF ? 4 : 1);
+  const float* rhs = rhs_all + (size_t)pair * d.plane * NOP;
+  const int tid = threadIdx.x;
+  float2 left = make_float2(0.f, 0.f);
+  if (pipelined) {
+    const int s = tid / h, j = tid - s * h;
+    const bool act = s < iters;
+    const int nsteps = w + h - 1 + 2 * (iters - 1);
+    for (int step = 0; step < nsteps; ++step) {
+      const int i = step - j - 2 * s;
+      if (act && i >= 0 && i < w) sor_pixel<OF>(du, coef, inv, rhs, i, j, w, h, omega, left);
+      __syncthreads();
+    }
+  } else {
+    const int R = blockDim.x;
+    for (int it = 0; it < iters; ++it)
+      for (int j0 = 0; j0 < h; j0 += R) {
+        const int j = j0 + tid, rows = min(R, h - j0);
+        const int nsteps = w + rows - 1;
+        for (int step = 0; step < nsteps; ++step) {
+          const int i = step - tid;
+          if (j < h && i >= 0 && i < w) sor_pixel<OF>(du, coef, inv, rhs, i, j, w, h, omega, left);
+          __syncthreads();
+        }
+      }
+  }
+}
+
+template <bool OF>
+__global__ void finish_kernel(float* __restrict__ flow, const float* __restrict__ du, Dims d, int camlr) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y, pair = blockIdx.z;
+  if (i >= d.w) return;
+  constexpr int NOP = OF ? 2 : 1;
+  const size_t pix = (size_t)j * d.w + i;
+  float u, v;
+  load_uv<OF>(flow + (size_t)pair * d.w * d.h * NOP, du + (size_t)pair * d.plane * NOP, pix, camlr, u, v);
+  float* o = flow + ((size_t)pair * d.w * d.h + pix) * NOP;
+  o[0] = u;
+  if (OF) o[1] = v;
+}
+
+template <int C, bool OF>
+void varref_level_impl(const float* im_a, const float* im_b, float* flow, const LevelGeom& g, const DisParams& p,
+                       int camlr, const VarRefBuffers& vb, int n, cudaStream_t st, LaunchStats* ls) {
+  constexpr int NOP = OF ? 2 : 1;
+  Dims d{g.w, g.h, g.pad, g.tw, g.img_elems, vb.plane_cap};
+  const int n_inner = p.tv_innerit * (g.level + 1);                       // refine_variational.cpp:36
+  if (n_inner <= 0) return;
+  const float qa = 0.25f * p.tv_alpha, hg3 = p.tv_gamma * 0.5f / 3.0f, hd3 = p.tv_delta * 0.5f / 3.0f;
+  dim3 blk(128), grd((g.w + 127) / 128, g.h, n), grdc((g.w + 127) / 128, g.h, n * C);
+  warp_kernel<C, OF><<<grd, blk, 0, st>>>(im_a, im_b, flow, d, vb.avg, vb.Iz, vb.mask);
+  deriv1_kernel<<<grdc, blk, 0, st>>>(vb.avg, vb.Iz, d, vb.Ix, vb.Iy, vb.Ixz, vb.Iyz);
+  deriv2_kernel<<<grdc, blk, 0, st>>>(vb.Ix, vb.Iy, d, vb.Ixx, vb.Ixy, vb.Iyy);
+  cudaMemsetAsync(vb.du, 0, sizeof(float) * vb.plane_cap * NOP * n, st);
+  ls->launches += 4;
+  DerivPtrs D{vb.Ix, vb.Iy, vb.Iz, vb.Ixx, vb.Ixy, vb.Iyy, vb.Ixz, vb.Iyz};
+  const bool pipelined = g.h * p.tv_solverit <= 1024;
+  int threads = pipelined ? g.h * p.tv_solverit : (g.h < 1024 ? g.h : 1024);
+  threads = ((threads + 31) / 32) * 32;
+  for (int it = 0; it < n_inner; ++it) {
+    smooth_kernel<OF><<<grd, blk, 0, st>>>(flow, vb.du, d, camlr, qa, it == 0, vb.smooth);
+    system_kernel<C, OF><<<grd, blk, 0, st>>>(D, vb.mask, vb.smooth, flow, vb.du, d, hd3, hg3,
+                                              reinterpret_cast<float4*>(vb.coef), vb.inv, vb.rhs);
+    sor_wavefront_kernel<OF><<<n, threads, 0, st>>>(vb.du, reinterpret_cast<const float4*>(vb.coef), vb.inv, vb.rhs, d,
+                                                    p.tv_solverit, p.tv_sor, pipelined ? 1 : 0);
+    ls->launches += 3;
+  }
+  finish_kernel<OF><<<grd, blk, 0, st>>>(flow, vb.du, d, camlr);
+  ls->launches++;
+}
+
+}  // namespace
+
+size_t varref_plane_count(int C, int nop) {
+  // avg, Iz, Ix, Iy, Ixx, Ixy, Iyy, Ixz, Iyz (C each) + mask + s + du (nop) + coef (4) + inv (4) + rhs (nop)
+  return (size_t)9 * C + 2 + nop + 4 + 4 + nop;
+}
+
+void launch_varref_level(const float* im_a, const float* im_b, float* flow, const LevelGeom& g, const DisParams& p,
+                         int camlr, const VarRefBuffers& vb, int n, cudaStream_t s, LaunchStats* st) {
+  const bool of = p.mode == DISB200_MODE_OF;
+  if (p.channels == 1) {
+    if (of) varref_level_impl<1, true>(im_a, im_b, flow, g, p, camlr, vb, n, s, st);
+    else varref_level_impl<1, false>(im_a, im_b, flow, g, p, camlr, vb, n, s, st);
+  } else {
+    if (of) varref_level_impl<3, true>(im_a, im_b, flow, g, p, camlr, vb, n, s, st);
+    else varref_level_impl<3, false>(im_a, im_b, flow, g, p, camlr, vb, n, s, st);
+  }
+}
+
+}  // namespace disb200
