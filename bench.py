@@ -1,0 +1,335 @@
+#!/usr/bin/env python
+"""bench.py - DIS optical flow hot path, frame pairs/s on B200 (contract: see DESIGN.md "Measurement").
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--batch B] [--workload C1|C2|C3|op1..op4]
+  python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+  python bench.py --impl reference ...      # the reference's CPU code on the host cores
+
+A step is one pass of the whole per-pair path (pyramid -> inverse search -> densification ->
+variational refinement -> upsample) over one batch of B synthetic frame pairs per GPU.
+`value` is device-resident throughput (frames already in HBM, result left in HBM), `e2e` is the
+same metric through disb200_run_batch_host with pinned HOST buffers (H2D + D2H inside the timed
+region).  Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (mode, channels, op, w0, h0, description)
+    "C1": (1, 1, 2, 1024, 436, "run_OF_INT op2 1024x436 grey"),
+    "C2": (1, 3, 4, 1024, 436, "run_OF_RGB op4 1024x436 BGR"),
+    "C3": (2, 1, 2, 1280, 720, "run_DE_INT op2 1280x720 grey stereo"),
+    "op1": (1, 1, 1, 1024, 436, "run_OF_INT op1 1024x436 grey"),
+    "op3": (1, 1, 3, 1024, 436, "run_OF_INT op3 1024x436 grey"),
+    "op4": (1, 1, 4, 1024, 436, "run_OF_INT op4 1024x436 grey"),
+    "C5": (1, 1, 2, 1920, 1080, "run_OF_INT op2 1920x1080 grey video pairs"),
+}
+N_DISTINCT = 4  # distinct synthetic pairs, tiled over the batch
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def make_inputs(mode, ch, w0, h0, n_distinct=N_DISTINCT):
+    from of_dis_b200.synth import make_pair
+    As, Bs = [], []
+    for s in range(n_distinct):
+        A, B, _ = make_pair(h0, w0, channels=ch, mode="OF" if mode == 1 else "DE", seed=s)
+        As.append(A)
+        Bs.append(B)
+    return np.stack(As), np.stack(Bs)
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons through NVML while the timed region runs."""
+
+    def __init__(self, device):
+        super().__init__(daemon=True)
+        self.device, self.samples, self.reasons, self.stop_flag, self.max_mhz = device, [], set(), False, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(device)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {
+            nv.nvmlClocksEventReasonHwSlowdown if hasattr(nv, "nvmlClocksEventReasonHwSlowdown") else 0x8: "hw_slowdown",
+            getattr(nv, "nvmlClocksEventReasonHwThermalSlowdown", 0x40): "hw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwThermalSlowdown", 0x20): "sw_thermal_slowdown",
+            getattr(nv, "nvmlClocksEventReasonSwPowerCap", 0x4): "sw_power_cap",
+            getattr(nv, "nvmlClocksEventReasonHwPowerBrakeSlowdown", 0x80): "hw_power_brake",
+        }
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def result(self):
+        self.stop_flag = True
+        self.join(timeout=1.0)
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["nvml unavailable"]}
+        return {"sm_mhz": statistics.median(self.samples), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
+
+
+def to_orc(p):
+    from oracle.bindings import OrcParams
+    q = OrcParams()
+    for f, _ in OrcParams._fields_:
+        setattr(q, f, getattr(p, {"psz": "patchsz", "noc": "channels"}.get(f, f)))
+    return q
+
+
+def cpu_reference_throughput(p, A, B, seconds_budget, threads):
+    """pairs/s of the reference's CPU code for the same path on `threads` host threads.
+
+    OFClass comes from oracle/_ref (the reference's own sources) when that library travelled
+    with the snapshot, else from the restatement; pyramid and final upsample are the OpenCV
+    restatement in both cases (OpenCV itself is unavailable).  ctypes releases the GIL, so
+    plain Python threads run the C code in parallel.
+    """
+    from concurrent.futures import ThreadPoolExecutor
+    from oracle import bindings as ob
+    port = ob.Port()
+    q = to_orc(p)
+    kind = "port"
+    ref = None
+    if ob.have_ref(p.mode, p.channels):
+        try:
+            ref = ob.Ref(p.mode, p.channels)
+            kind = "reference"
+        except Exception:
+            ref = None
+    h0, w0 = A.shape[1:3]
+    W, H, padl, padt = port.pad_dims(w0, h0, p.sc_f)
+
+    def one(i):
+        a, b = A[i % len(A)], B[i % len(B)]
+        if ref is None:
+            return port.run_dense(q, a, b)
+        PA = port.pyramid(a, p.sc_f, p.sc_l, p.patchsz)
+        PB = port.pyramid(b, p.sc_f, p.sc_l, p.patchsz)
+        low = ref.ofclass(q, PA, PB, W, H)
+        return port.upsample_crop(low, p.sc_l, padl, padt, w0, h0)
+
+    t = time.perf_counter()
+    one(0)
+    t1 = time.perf_counter() - t
+    per_thread = max(2, min(64, int(seconds_budget / max(t1, 1e-4))))
+    n = per_thread * threads
+    with ThreadPoolExecutor(threads) as ex:
+        list(ex.map(one, range(threads)))  # warm-up
+        t = time.perf_counter()
+        list(ex.map(one, range(n)))
+        dt = time.perf_counter() - t
+    return n / dt, kind, "%d pairs on %d threads, %.1f s wall (1 pair single-thread %.1f ms)" % (n, threads, dt, t1 * 1e3)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--batch", type=int, default=256, help="frame pairs per step per GPU")
+    ap.add_argument("--workload", default="C1", choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU baseline sample budget per thread")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    W_ = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    mode, ch, op, w0, h0, desc = WORKLOADS[args.workload]
+    nop = 2 if mode == 1 else 1
+
+    import of_dis_b200 as dis   # raises if libdisb200.so is missing: there is no fallback
+    p = dis.operating_point(op, w0, mode, ch).copy(verbosity=0)
+    A, B = make_inputs(mode, ch, w0, h0)
+    bytes_per_pair = 2 * w0 * h0 * ch + 4 * w0 * h0 * nop     # compulsory traffic of the whole path
+    config = {"workload": "%s: %s, params %s" % (args.workload, desc, " ".join("%g" % v for v in p.cli_args())),
+              "pairs_per_step_per_gpu": args.batch, "frame": [w0, h0, ch], "l2_policy": "inputs+outputs per step (%.0f MB) exceed the 126 MB L2" % (args.batch * bytes_per_pair / 1e6),
+              "sor": "lexicographic wavefront (parity mode)"}
+
+    # ------------------------------------------------------------------ reference arm (CPU)
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        threads = os.cpu_count() or 1
+        vals = []
+        sample = ""
+        kind = "port"
+        for s in range(max(args.warmup, 0) + max(args.steps, 1)):
+            v, kind, sample = cpu_reference_throughput(p, A, B, max(0.5, 60.0 / max(args.steps + args.warmup, 1) / 4), threads)
+            if s >= args.warmup:
+                vals.append(v)
+        v = statistics.median(vals)
+        line = {"impl": "reference", "metric": "frame_pairs_per_s", "value": v, "unit": "pairs/s", "mpix_per_s": v * w0 * h0 / 1e6,
+                "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / v,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": config,
+                "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": threads, "kind": kind, "sample": sample},
+                "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return 0
+
+    # ------------------------------------------------------------------ our arm (GPU)
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    nb = args.batch
+    reps = -(-nb // len(A))
+    hA = torch.from_numpy(np.ascontiguousarray(np.concatenate([A] * reps)[:nb])).pin_memory()
+    hB = torch.from_numpy(np.ascontiguousarray(np.concatenate([B] * reps)[:nb])).pin_memory()
+    hOut = torch.empty((nb, h0, w0, nop), dtype=torch.float32).pin_memory()
+    dA, dB = hA.cuda(non_blocking=False), hB.cuda(non_blocking=False)
+    dOut = torch.empty((nb, h0, w0, nop), dtype=torch.float32, device="cuda")
+    torch.cuda.synchronize()
+    hd = dis.Handle(p, w0, h0, max_batch=nb, device=local_rank)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        hd.run_device(dA.data_ptr(), dB.data_ptr(), nb, dOut.data_ptr())
+
+    for _ in range(W_):
+        step()
+    hd.sync()
+    launches_per_step = hd.launch_count()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    barrier()
+    hd.timer_begin()
+    for _ in range(args.steps):
+        step()
+    ms = hd.timer_end()
+    barrier()
+    clocks = sampler.result()
+    if world > 1:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    pairs = nb * args.steps * world
+    value = pairs / (ms / 1e3)
+
+    # per-stage device time (CUDA events on the launching stream) -> roofline of the dominant stage
+    hd.set_stage_timing(True)
+    acc = {}
+    for _ in range(3):
+        step()
+        hd.sync()
+        for k, v in hd.stage_ms().items():
+            acc[k] = acc.get(k, 0.0) + v / 3
+    hd.set_stage_timing(False)
+    acc["varref_other"] = acc.get("varref", 0.0) - acc.get("sor", 0.0)
+    stage_share = {k: acc[k] for k in ("pyramid", "inverse_search", "densify", "varref_other", "sor", "upsample")}
+    step_ms = sum(stage_share.values())
+    peak, peak_src = peaks()
+    # algorithmic bytes of each stage per pair (DESIGN.md "Kernels and their rooflines")
+    W, H = hd.W, hd.H
+    lv = [(W >> l, H >> l, l) for l in range(p.sc_l, p.sc_f + 1)]
+    pad = p.patchsz
+    alg = {
+        "pyramid": 2 * w0 * h0 * ch + sum(2 * 3 * 4 * ch * (w + 2 * pad) * (h + 2 * pad) for w, h, _ in lv),
+        "upsample": 4 * nop * lv[0][0] * lv[0][1] + 4 * nop * w0 * h0,
+        # per sweep read 9 planes (a11 a12 a22 b1 b2 h v du dv), write 2 (DE: 5 + 1)
+        "sor": sum(p.tv_innerit * (l + 1) * p.tv_solverit * (4 * w * h) * (11 if nop == 2 else 6) for w, h, l in lv) if p.usetvref else 0,
+    }
+    dom = max(stage_share, key=stage_share.get)
+    dom_ms = stage_share[dom]
+    dom_bytes = alg.get(dom)
+    roof = {"bound": "hbm", "kernel": dom, "unit": "GB/s", "peak": peak, "peak_source": peak_src,
+            "share_of_step": dom_ms / step_ms if step_ms else None, "traffic": None}
+    if dom_bytes:
+        roof["achieved"] = dom_bytes * nb / (dom_ms / 1e3) / 1e9
+        roof["frac"] = roof["achieved"] / peak
+        roof["algorithmic_bytes_per_launch_set"] = dom_bytes * nb
+    else:
+        roof["achieved"] = None
+        roof["frac"] = None
+    path_gbs = value / world * bytes_per_pair / 1e9
+    roof["whole_path"] = {"algorithmic_bytes_per_pair": bytes_per_pair, "achieved": path_gbs, "frac": path_gbs / peak}
+    roof["stage_ms_per_step"] = {k: round(v, 4) for k, v in stage_share.items()}
+
+    # ---- end to end through the host-pointer C-ABI entry (pinned host buffers) ----
+    e2e = None
+    if not args.no_e2e:
+        for _ in range(2):
+            hd.run_host_ptr(hA.data_ptr(), hB.data_ptr(), nb, hOut.data_ptr())
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            hd.run_host_ptr(hA.data_ptr(), hB.data_ptr(), nb, hOut.data_ptr())
+        barrier()
+        dt = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([dt], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        e2e = {"value": pairs / dt, "unit": "pairs/s", "h2d_bytes_per_step": 2 * nb * w0 * h0 * ch,
+               "d2h_bytes_per_step": nb * w0 * h0 * nop * 4, "checksum": float(hOut[0].double().abs().mean())}
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        v, kind, sample = cpu_reference_throughput(p, A, B, args.cpu_seconds / 4, threads)
+        cpu = {"value": v, "unit": "pairs/s", "cores": threads, "kind": kind, "sample": sample}
+
+    if rank == 0:
+        line = {"metric": "frame_pairs_per_s", "value": value, "unit": "pairs/s", "mpix_per_s": value * w0 * h0 / 1e6,
+                "n_gpus": world, "steps": args.steps, "warmup": W_, "ms_per_step": ms / args.steps,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic warped-texture pairs (%d distinct seeds tiled over the batch)" % len(A),
+                "config": config, "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * args.steps,
+                "roofline": roof, "cpu_baseline": cpu}
+        print(json.dumps(line))
+    hd.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

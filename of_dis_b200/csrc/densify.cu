@@ -173,7 +173,7 @@ void launch_densify(const DensifyArgs& a, const LevelGeom& g, const OptConst& o,
                                                                       a.cell_count, a.cell_list, a.cell_cap);
     bin_sort_kernel<<<dim3((ncx * ncy + 127) / 128, n), 128, 0, s>>>(a.cell_count, a.cell_list, ncx * ncy, a.cell_cap,
                                                                      a.overflow);
-    st->launches += 3;
+    st->launches += 2;
   }
   dim3 blk(128), grd((g.w + 127) / 128, g.h, n);
   if (o.noc == 1) {

@@ -37,6 +37,9 @@ LevelGeom make_levelgeom(const DisParams& p, int W, int H, int level);
 // Launch bookkeeping (gpu_launches in bench.py is read from here).
 struct LaunchStats {
   int launches;
+  // optional stage marks for the CUDA-event stopwatch (begin = 1 / end = 0)
+  void (*mark)(void* ctx, int stage, int begin);
+  void* ctx;
 };
 
 // ---- stage 1: pyramid -------------------------------------------------------------------

@@ -106,10 +106,10 @@ struct Engine {
   size_t ncell_max = 0;
   std::vector<void*> allocs;
   cudaStream_t stream = nullptr;
-  LaunchStats stats{0};
+  LaunchStats stats{0, nullptr, nullptr};
   // stage timing
   bool stage_timing = false;
-  float stage_ms[5] = {0, 0, 0, 0, 0};
+  float stage_ms[6] = {0, 0, 0, 0, 0, 0};
   std::vector<cudaEvent_t> ev_pool;
   struct Mark { int stage; cudaEvent_t a, b; };
   std::vector<Mark> marks;
@@ -218,8 +218,18 @@ struct Engine {
       if (e->stage_timing) { cudaEvent_t b = e->next_event(); cudaEventRecord(b, e->stream); e->marks.push_back({stage, a, b}); }
     }
   };
+  cudaEvent_t open_mark[8] = {nullptr};
+  static void mark_cb(void* ctx, int stage, int begin) {
+    Engine* e = static_cast<Engine*>(ctx);
+    cudaEvent_t ev = e->next_event();
+    cudaEventRecord(ev, e->stream);
+    if (begin) e->open_mark[stage] = ev;
+    else e->marks.push_back({stage, e->open_mark[stage], ev});
+  }
   void begin_run() {
     stats.launches = 0;
+    stats.mark = stage_timing ? &Engine::mark_cb : nullptr;
+    stats.ctx = this;
     ev_used = 0;
     marks.clear();
   }
@@ -535,7 +545,7 @@ int disb200_set_stage_timing(DisHandle* h, int on) {
   return DISB200_OK;
 }
 int disb200_stage_ms(const DisHandle* h, int stage, float* ms) {
-  if (!h || !ms || stage < 0 || stage > 4) return fail(DISB200_EINVAL, "bad argument");
+  if (!h || !ms || stage < 0 || stage > 5) return fail(DISB200_EINVAL, "bad argument");
   *ms = h->e.stage_ms[stage];
   return DISB200_OK;
 }

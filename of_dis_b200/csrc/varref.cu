@@ -522,7 +522,7 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
   deriv1_kernel<<<grdc, blk, 0, st>>>(vb.avg, vb.Iz, d, vb.Ix, vb.Iy, vb.Ixz, vb.Iyz);
   deriv2_kernel<<<grdc, blk, 0, st>>>(vb.Ix, vb.Iy, d, vb.Ixx, vb.Ixy, vb.Iyy);
   cudaMemsetAsync(vb.du, 0, sizeof(float) * vb.plane_cap * NOP * n, st);
-  ls->launches += 4;
+  ls->launches += 3;
   DerivPtrs D{vb.Ix, vb.Iy, vb.Iz, vb.Ixx, vb.Ixy, vb.Iyy, vb.Ixz, vb.Iyz};
   const bool pipelined = g.h * p.tv_solverit <= 1024;
   int threads = pipelined ? g.h * p.tv_solverit : (g.h < 1024 ? g.h : 1024);
@@ -531,8 +531,10 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
     smooth_kernel<OF><<<grd, blk, 0, st>>>(flow, vb.du, d, camlr, qa, it == 0, vb.smooth);
     system_kernel<C, OF><<<grd, blk, 0, st>>>(D, vb.mask, vb.smooth, flow, vb.du, d, hd3, hg3,
                                               reinterpret_cast<float4*>(vb.coef), vb.inv, vb.rhs);
+    if (ls->mark) ls->mark(ls->ctx, 5, 1);
     sor_wavefront_kernel<OF><<<n, threads, 0, st>>>(vb.du, reinterpret_cast<const float4*>(vb.coef), vb.inv, vb.rhs, d,
                                                     p.tv_solverit, p.tv_sor, pipelined ? 1 : 0);
+    if (ls->mark) ls->mark(ls->ctx, 5, 0);
     ls->launches += 3;
   }
   finish_kernel<OF><<<grd, blk, 0, st>>>(flow, vb.du, d, camlr);

@@ -1,0 +1,261 @@
+"""CPU suite (-m "not gpu"): the oracle against its golden vectors, host logic, C-ABI exports."""
+import ctypes
+import importlib.util
+import os
+import re
+import struct
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from oracle import bindings as ob
+from tests.helpers import base_orc, epe
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _ref_cases():
+    spec = importlib.util.spec_from_file_location("make_golden", os.path.join(ROOT, "tests", "golden", "make_golden.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m.REF_CASES
+
+
+REF_CASES = _ref_cases()
+
+
+# ---------------------------------------------------------------- OpenCV steps vs python-cv2 golden
+@pytest.mark.parametrize("tag", ["g", "c"])
+def test_pyramid_steps_match_cv2(port, cv2_golden, tag):
+    g = cv2_golden
+    lv = g[tag + "_l0"]
+    for l in (1, 2, 3):
+        lv = port.halve(lv)
+        assert np.array_equal(lv, g["%s_l%d" % (tag, l)]), "2x2 box mean differs from cv2.resize at level %d" % l
+        dx, dy = port.sobel(lv)
+        assert np.array_equal(dx, g["%s_dx%d" % (tag, l)])
+        assert np.array_equal(dy, g["%s_dy%d" % (tag, l)])
+
+
+@pytest.mark.parametrize("tag", ["g", "c"])
+def test_pyramid_level_from_u8_matches_cv2(port, cv2_golden, tag):
+    """a1 + a2 end to end: u8 frame -> replicate pad to /16 -> level 2 -> Sobel -> border pads."""
+    g = cv2_golden
+    u8 = g[tag + "_u8"]
+    img, dx, dy = port.pyramid_level(u8, sc_f=4, level=2, pad=8)
+    want_img = g[tag + "_pad2_rep"].reshape(img.shape)
+    want_dx = g[tag + "_pad2_zero"].reshape(dx.shape)
+    assert np.array_equal(img, want_img)
+    assert np.array_equal(dx, want_dx)
+    assert port.pad_dims(72, 44, 4) == (80, 48, 4, 2)
+
+
+@pytest.mark.parametrize("nop", [1, 2])
+@pytest.mark.parametrize("sc_l", [1, 2, 3])
+def test_upsample_crop_matches_cv2(port, cv2_golden, nop, sc_l):
+    fl = cv2_golden["up_in_%d_%d" % (nop, sc_l)]
+    want = cv2_golden["up_out_%d_%d" % (nop, sc_l)]
+    h0, w0 = want.shape[:2]
+    got = port.upsample_crop(fl, sc_l, 1, 2, w0, h0)
+    assert np.abs(got - want).max() <= 1e-5   # cv2 differs by fp32 rounding at most
+
+
+def test_upsample_sc_l_zero_is_a_crop(port):
+    fl = np.arange(6 * 8 * 2, dtype=np.float32).reshape(6, 8, 2)
+    got = port.upsample_crop(fl, 0, 1, 2, 5, 3)
+    assert np.array_equal(got, fl[2:5, 1:6])
+
+
+# ---------------------------------------------------------------- oracle vs the reference's own code
+@pytest.mark.parametrize("name", sorted(REF_CASES))
+def test_port_matches_reference_golden(port, ref_golden, name):
+    mode, noc, h0, w0, kw = REF_CASES[name]
+    A, B = ref_golden[name + "_A"], ref_golden[name + "_B"]
+    p = base_orc(mode, noc, **kw)
+    W, H, _, _ = port.pad_dims(w0, h0, p.sc_f)
+    PA = port.pyramid(A, p.sc_f, p.sc_l, p.psz)
+    PB = port.pyramid(B, p.sc_f, p.sc_l, p.psz)
+    got = port.ofclass(p, PA, PB, W, H)
+    want = ref_golden[name + "_low"]
+    assert np.array_equal(got, want), "restatement differs from the reference build: EPE mean %g max %g" % epe(got, want)
+
+
+@pytest.mark.parametrize("mode,noc", [(1, 1), (1, 3), (2, 1), (2, 3)])
+def test_port_matches_reference_live(port, mode, noc):
+    if not ob.have_ref(mode, noc):
+        pytest.skip("oracle/_ref not built on this machine")
+    from of_dis_b200.synth import make_pair
+    ref = ob.Ref(mode, noc)
+    A, B, _ = make_pair(70, 110, channels=noc, mode="OF" if mode == 1 else "DE", seed=5)
+    for kw in (dict(), dict(usefbcon=1), dict(costfct=2, min_iter=3, max_iter=20, res_thresh=.3), dict(sc_f=2, sc_l=0, usetvref=0)):
+        p = base_orc(mode, noc, **kw)
+        W, H, _, _ = port.pad_dims(110, 70, p.sc_f)
+        PA = port.pyramid(A, p.sc_f, p.sc_l, p.psz)
+        PB = port.pyramid(B, p.sc_f, p.sc_l, p.psz)
+        assert np.array_equal(port.ofclass(p, PA, PB, W, H), ref.ofclass(p, PA, PB, W, H)), kw
+        # per-stage: patch state and densified flow on the finest level, refinement alone
+        wl, hl = W >> p.sc_l, H >> p.sc_l
+        a = (PA[0][p.sc_l], PA[1][p.sc_l], PA[2][p.sc_l])
+        b = (PB[0][p.sc_l], PB[1][p.sc_l], PB[2][p.sc_l])
+        ro, rr = port.patchgrid_level(p, a, b, wl, hl, p.sc_l), ref.patchgrid_level(p, a, b, wl, hl, p.sc_l)
+        for k in ("p_iter_fw", "pt_iter_fw", "pweight_fw", "cnt_fw", "dense_fw"):
+            assert np.array_equal(ro[k], rr[k]), (kw, k)
+        fl = ro["dense_fw"]
+        assert np.array_equal(port.varref_level(p, a[0], b[0], wl, hl, p.sc_l, 0, fl),
+                              ref.varref_level(p, a[0], b[0], wl, hl, p.sc_l, 0, fl)), kw
+
+
+def test_port_flow_is_sane(port):
+    """EPE against the synthetic ground truth (not a parity check, a sanity check of the generator + oracle)."""
+    from of_dis_b200.synth import make_pair
+    A, B, gt = make_pair(218, 512, channels=1, mode="OF", seed=2)
+    p = port.operating_point(2, 512, 1, 1).copy(verbosity=0)
+    out = port.run_dense(p, A, B)
+    assert out.shape == (218, 512, 2)
+    assert epe(out, gt)[0] < 0.8
+
+
+def test_identical_frames_give_zero_flow(port):
+    from of_dis_b200.synth import make_pair
+    A, _, _ = make_pair(100, 160, channels=1, mode="OF", seed=1)
+    p = base_orc(1, 1)
+    out = port.run_dense(p, A, A)
+    assert np.all(out == 0)
+
+
+# ---------------------------------------------------------------- host logic of the product (no GPU needed)
+def test_operating_points_match_oracle(dis, port):
+    for op in (1, 2, 3, 4, 7):
+        for width in (320, 640, 1024, 1280, 1920, 3840):
+            for mode, ch in ((1, 1), (1, 3), (2, 1)):
+                p = dis.operating_point(op, width, mode, ch)
+                q = port.operating_point(op, width, mode, ch)
+                for f, _ in ob.OrcParams._fields_:
+                    assert getattr(p, {"psz": "patchsz", "noc": "channels"}.get(f, f)) == getattr(q, f), (op, width, f)
+    p = dis.operating_point(2, 1024)
+    # run_dense.cpp:260-266 + README: op2 on a 1024 wide frame = 5 3 12 12 .05 .95 0 8 .4 0 1 0 1 10 10 5 1 3 1.6
+    assert p.cli_args()[:19] == pytest.approx([5, 3, 12, 12, .05, .95, 0, 8, .4, 0, 1, 0, 1, 10, 10, 5, 1, 3, 1.6])
+
+
+def test_padded_dims_match_oracle(dis, port):
+    for (w0, h0, sc_f) in ((1024, 436, 5), (1280, 720, 6), (3840, 2160, 7), (1920, 1080, 6), (33, 17, 3), (64, 64, 4)):
+        assert dis.padded_dims(w0, h0, sc_f) == port.pad_dims(w0, h0, sc_f)
+    assert dis.padded_dims(1024, 436, 5) == (1024, 448, 0, 6)
+
+
+def test_cabi_exports_every_declared_symbol(dis):
+    hdr = open(os.path.join(ROOT, "include", "disb200.h")).read()
+    names = sorted(set(re.findall(r"\b(disb200_[a-z0-9_]+)\s*\(", hdr)))
+    assert len(names) >= 20
+    L = dis.lib()
+    for n in names:
+        assert hasattr(L, n), "libdisb200.so does not export " + n
+    assert b"sm_100a" in L.disb200_version()
+
+
+def test_struct_layout_matches_header(dis):
+    # 23 four-byte fields in CLI order + mode, channels, sor_mode
+    assert ctypes.sizeof(dis.DisParams) == 23 * 4
+    hdr = open(os.path.join(ROOT, "include", "disb200.h")).read()
+    body = hdr[hdr.index("typedef struct DisParams {"):hdr.index("} DisParams;")]
+    fields = re.findall(r"^\s*(?:int|float)\s+([a-z_]+);", body, re.M)
+    assert fields == [f for f, _ in dis.DisParams._fields_]
+
+
+def test_compute_entry_points_fail_loudly_without_gpu(dis):
+    if dis.device_count() > 0:
+        pytest.skip("a GPU is present")
+    p = dis.operating_point(2, 256)
+    with pytest.raises(dis.DisError) as e:
+        dis.Handle(p, 256, 128, 1)
+    assert e.value.code == 2 and "no CPU path" in str(e.value)
+
+
+def test_invalid_parameters_are_rejected(dis):
+    p = dis.operating_point(2, 256)
+    for kw in (dict(mode=3), dict(channels=2), dict(sc_l=4, sc_f=3), dict(patove=1.0), dict(patchsz=7), dict(costfct=10)):
+        with pytest.raises(dis.DisError) as e:
+            dis.Handle(p.copy(**kw), 256, 128, 1)
+        assert e.value.code in (1, 4), kw
+
+
+def test_flo_and_pfm_writers_use_the_reference_framing(dis, tmp_path):
+    fl = np.arange(3 * 5 * 2, dtype=np.float32).reshape(3, 5, 2) - 7
+    f = str(tmp_path / "a.flo")
+    dis.save_flo(f, fl)
+    raw = open(f, "rb").read()
+    assert raw[:4] == b"PIEH" and struct.unpack("<ii", raw[4:12]) == (5, 3)          # run_dense.cpp:29-32
+    assert np.array_equal(np.frombuffer(raw[12:], np.float32).reshape(3, 5, 2), fl)
+    d = fl[..., 0]
+    f = str(tmp_path / "a.pfm")
+    dis.save_pfm(f, d)
+    raw = open(f, "rb").read()
+    head = b"Pf\n5 3\n-1.000000\n"                                                     # run_dense.cpp:70
+    assert raw.startswith(head)
+    body = np.frombuffer(raw[len(head):], np.float32).reshape(3, 5)
+    assert np.array_equal(body, -d[::-1])                                              # bottom-up, negated (:72-79)
+
+
+def test_pnm_reader(dis, tmp_path):
+    rng = np.random.default_rng(0)
+    g = rng.integers(0, 256, (7, 9), dtype=np.uint8)
+    c = rng.integers(0, 256, (7, 9, 3), dtype=np.uint8)   # RGB on disk
+    pg, pc = str(tmp_path / "g.pgm"), str(tmp_path / "c.ppm")
+    open(pg, "wb").write(b"P5\n# comment\n9 7\n255\n" + g.tobytes())
+    open(pc, "wb").write(b"P6 9 7 255\n" + c.tobytes())
+    assert np.array_equal(dis.read_pnm(pg, 1), g)
+    assert np.array_equal(dis.read_pnm(pc, 3), c[..., ::-1])                          # BGR like cv::imread
+    assert np.array_equal(dis.read_pnm(pg, 3), np.repeat(g[..., None], 3, -1))
+    grey = dis.read_pnm(pc, 1).astype(int)
+    want = (c[..., 0].astype(int) * 4899 + c[..., 1].astype(int) * 9617 + c[..., 2].astype(int) * 1868 + 8192) >> 14
+    assert np.array_equal(grey, want)
+
+
+# ---------------------------------------------------------------- multi-GPU host logic on CPU (gloo, world 2)
+def test_shard_range_covers_everything():
+    from of_dis_b200.sharding import frames_for_pairs, shard_range
+    for n in (0, 1, 7, 256, 257):
+        for world in (1, 2, 3, 8):
+            blocks = [shard_range(n, r, world) for r in range(world)]
+            assert blocks[0][0] == 0 and blocks[-1][1] == n
+            assert all(blocks[i][1] == blocks[i + 1][0] for i in range(world - 1))
+            assert max(b[1] - b[0] for b in blocks) - min(b[1] - b[0] for b in blocks) <= 1
+    assert frames_for_pairs(32, 64) == (32, 65)
+
+
+_GLOO_WORKER = r"""
+import os, sys
+sys.path.insert(0, sys.argv[1])
+import numpy as np, torch, torch.distributed as dist
+from of_dis_b200.sharding import shard_range
+from of_dis_b200.synth import make_pair
+from oracle import bindings as ob
+dist.init_process_group("gloo")
+rank, world = dist.get_rank(), dist.get_world_size()
+port = ob.Port()
+n = 5
+lo, hi = shard_range(n, rank, world)
+p = port.operating_point(2, 160, 1, 1).copy(verbosity=0)
+sums = torch.zeros(n, dtype=torch.float64)
+for i in range(lo, hi):                      # each rank processes only its own block: no data-path collective
+    A, B, _ = make_pair(64, 160, seed=i)
+    sums[i] = float(np.abs(port.run_dense(p, A, B)).sum())
+cnt = torch.tensor([hi - lo])
+dist.all_reduce(sums); dist.all_reduce(cnt)   # bookkeeping only (what bench.py does with the timings)
+if rank == 0:
+    full = [float(np.abs(port.run_dense(p, *make_pair(64, 160, seed=i)[:2])).sum()) for i in range(n)]
+    assert int(cnt) == n and np.allclose(sums.numpy(), full, rtol=0, atol=0), (sums, full)
+    print("OK")
+dist.destroy_process_group()
+"""
+
+
+def test_pair_sharding_world2_gloo(tmp_path, port):
+    script = tmp_path / "w.py"
+    script.write_text(_GLOO_WORKER)
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                        "--master-addr", "127.0.0.1", "--master-port", "29741", str(script), ROOT],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]

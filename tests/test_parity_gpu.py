@@ -1,0 +1,239 @@
+"""GPU suite (-m gpu): the CUDA path, called through the C-ABI, against the CPU oracle.
+
+Tolerances (north_star): mean EPE(GPU, CPU) <= 0.01 px for every operating point; max-pixel
+bound 0.01 px at op1/op2-like settings and 1.0 px at op3/op4-like settings (rare outlier-test
+flips).  Stages whose arithmetic order is reproduced exactly are held to
+bit-equality: pyramid, variational refinement (lexicographic SOR), upsample.
+"""
+import importlib.util
+import os
+
+import numpy as np
+import pytest
+
+from oracle import bindings as ob
+from of_dis_b200.synth import make_pair
+from tests.helpers import base_orc, epe, to_dis, to_orc
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+MEAN_TOL = 0.01
+MAX_TOL_FINE = 0.01   # op1 / op2
+MAX_TOL_DENSE = 1.0   # op3 / op4 (and other high-overlap settings)
+
+
+def _ref_cases():
+    spec = importlib.util.spec_from_file_location("make_golden", os.path.join(ROOT, "tests", "golden", "make_golden.py"))
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m.REF_CASES
+
+
+REF_CASES = _ref_cases()
+
+
+# ------------------------------------------------------------------------------ stage 1
+@pytest.mark.parametrize("ch", [1, 3])
+@pytest.mark.parametrize("w0,h0,sc_f,sc_l", [(150, 90, 3, 1), (1024, 436, 5, 3), (96, 64, 2, 0), (333, 217, 4, 2)])
+def test_pyramid_bit_exact(gpu, port, ch, w0, h0, sc_f, sc_l):
+    A, B, _ = make_pair(h0, w0, channels=ch, seed=4)
+    p = to_dis(gpu, base_orc(1, ch, sc_f=sc_f, sc_l=sc_l))
+    with gpu.Handle(p, w0, h0, max_batch=2) as hd:
+        hd.run_host(np.stack([A, B]), np.stack([B, A]))
+        for l in range(sc_l, sc_f + 1):
+            want_a, want_b = port.pyramid_level(A, sc_f, l, 8), port.pyramid_level(B, sc_f, l, 8)
+            for which, pair, want in ((0, 0, want_a), (1, 0, want_b), (0, 1, want_b), (1, 1, want_a)):
+                got = hd.fetch_pyramid(which, l, pair)
+                for k in range(3):
+                    assert np.array_equal(got[k], want[k]), (l, which, pair, k)
+
+
+# ------------------------------------------------------------------------------ stage 4 alone
+@pytest.mark.parametrize("mode,ch", [(1, 1), (1, 3), (2, 1), (2, 3)])
+@pytest.mark.parametrize("w0,h0,level", [(1024, 436, 3), (500, 218, 1), (130, 70, 0)])
+def test_varref_level_bit_exact(gpu, port, mode, ch, w0, h0, level):
+    """Covers widths that are not multiples of 4 (FDF stride padding) and both cameras."""
+    A, B, _ = make_pair(h0, w0, channels=ch, mode="OF" if mode == 1 else "DE", seed=1)
+    q = base_orc(mode, ch, sc_f=level, sc_l=level)
+    p = to_dis(gpu, q)
+    W, H, _, _ = port.pad_dims(w0, h0, level)
+    a, b = port.pyramid_level(A, level, level, 8)[0], port.pyramid_level(B, level, level, 8)[0]
+    wl, hl = W >> level, H >> level
+    nop = 2 if mode == 1 else 1
+    rng = np.random.default_rng(0)
+    fl = (rng.standard_normal((hl, wl, nop)) * 0.7).astype(np.float32)
+    for camlr in ((0,) if mode == 1 else (0, 1)):
+        f = fl if mode == 1 else (-np.abs(fl) if camlr == 0 else np.abs(fl))
+        want = port.varref_level(q, a, b, wl, hl, level, camlr, f)
+        got = gpu.varref_level(p, a, b, wl, hl, level, camlr, f)
+        assert np.abs(want - f).max() > 0.1          # the refinement did something
+        assert np.array_equal(got, want), "max diff %g" % np.abs(got - want).max()
+
+
+@pytest.mark.parametrize("solverit,innerit,omega", [(1, 1, 1.0), (5, 2, 1.9), (3, 1, 1.6)])
+def test_varref_sweep_counts(gpu, port, solverit, innerit, omega):
+    A, B, _ = make_pair(120, 200, seed=6)
+    q = base_orc(1, 1, sc_f=1, sc_l=1, tv_solverit=solverit, tv_innerit=innerit, tv_sor=omega)
+    a, b = port.pyramid_level(A, 1, 1, 8)[0], port.pyramid_level(B, 1, 1, 8)[0]
+    fl = np.full((60, 100, 2), 0.3, np.float32)
+    assert np.array_equal(gpu.varref_level(to_dis(gpu, q), a, b, 100, 60, 1, 0, fl), port.varref_level(q, a, b, 100, 60, 1, 0, fl))
+
+
+def test_varref_tall_level_uses_band_mode(gpu, port):
+    """h * solverit > 1024 threads: sweeps run band by band, still the lexicographic order."""
+    A, B, _ = make_pair(400, 96, seed=8)
+    q = base_orc(1, 1, sc_f=0, sc_l=0, tv_solverit=3)
+    a, b = port.pyramid_level(A, 0, 0, 8)[0], port.pyramid_level(B, 0, 0, 8)[0]
+    fl = np.zeros((400, 96, 2), np.float32)
+    fl[..., 0] = 1.5
+    assert np.array_equal(gpu.varref_level(to_dis(gpu, q), a, b, 96, 400, 0, 0, fl), port.varref_level(q, a, b, 96, 400, 0, 0, fl))
+
+
+# ------------------------------------------------------------------------------ OFClass level (drop-in boundary)
+@pytest.mark.parametrize("name", sorted(REF_CASES))
+def test_ofclass_against_reference_golden(gpu, port, ref_golden, name):
+    """Same padded host pyramids in, low-resolution flow out, against outputs of the reference's own build."""
+    mode, noc, h0, w0, kw = REF_CASES[name]
+    A, B = ref_golden[name + "_A"], ref_golden[name + "_B"]
+    q = base_orc(mode, noc, **kw)
+    W, H, _, _ = port.pad_dims(w0, h0, q.sc_f)
+    PA, PB = port.pyramid(A, q.sc_f, q.sc_l, q.psz), port.pyramid(B, q.sc_f, q.sc_l, q.psz)
+    got = gpu.ofclass(to_dis(gpu, q), PA, PB, W, H)
+    m, mx = epe(got, ref_golden[name + "_low"])
+    assert m <= MEAN_TOL and mx <= (MAX_TOL_DENSE if q.psz == 12 else 0.05), (m, mx)
+
+
+def test_ofclass_initflow(gpu, port):
+    A, B, _ = make_pair(90, 150, seed=11)
+    q = base_orc(1, 1, sc_f=2, sc_l=1)
+    W, H, _, _ = port.pad_dims(150, 90, 2)
+    PA, PB = port.pyramid(A, 2, 1, 8), port.pyramid(B, 2, 1, 8)
+    init = np.zeros((H >> 3, W >> 3, 2), np.float32)
+    init[..., 0] = 0.4
+    init[..., 1] = -0.2
+    want = port.ofclass(q, PA, PB, W, H, initflow=init)
+    got = gpu.ofclass(to_dis(gpu, q), PA, PB, W, H, initflow=init)
+    assert not np.array_equal(want, port.ofclass(q, PA, PB, W, H))
+    m, mx = epe(got, want)
+    assert m <= MEAN_TOL and mx <= 0.05
+
+
+# ------------------------------------------------------------------------------ whole driver path, host buffers
+CONFIGS = [
+    # id, mode, ch, op, w0, h0, overrides, max tolerance
+    ("C1_of_int_op2", 1, 1, 2, 1024, 436, {}, MAX_TOL_FINE),
+    ("of_int_op1", 1, 1, 1, 1024, 436, {}, MAX_TOL_FINE),
+    ("of_int_op3", 1, 1, 3, 1024, 436, {}, MAX_TOL_DENSE),
+    ("of_rgb_op2", 1, 3, 2, 1024, 436, {}, MAX_TOL_FINE),
+    ("of_rgb_op3", 1, 3, 3, 640, 272, {}, MAX_TOL_DENSE),
+    ("C3_de_int_op2", 2, 1, 2, 1280, 720, {}, MAX_TOL_FINE),
+    ("de_rgb_op2", 2, 3, 2, 1280, 720, {}, MAX_TOL_FINE),
+    ("of_int_l1", 1, 1, 2, 1024, 436, dict(costfct=1), MAX_TOL_FINE),
+    ("of_int_huber", 1, 1, 2, 1024, 436, dict(costfct=2), MAX_TOL_FINE),
+    ("of_int_fb", 1, 1, 2, 1024, 436, dict(usefbcon=1), MAX_TOL_FINE),
+    ("de_int_fb_op3", 2, 1, 3, 640, 360, dict(usefbcon=1), MAX_TOL_DENSE),
+    ("of_int_early_stop", 1, 1, 2, 1024, 436, dict(min_iter=2, max_iter=30, res_thresh=0.4), 0.05),
+    ("of_int_nonorm", 1, 1, 2, 1024, 436, dict(patnorm=0), MAX_TOL_FINE),
+    ("of_int_psz16", 1, 1, 2, 640, 272, dict(patchsz=16, patove=0.5, sc_f=3, sc_l=1), 0.05),
+    ("of_int_psz4", 1, 1, 2, 320, 136, dict(patchsz=4, patove=0.5, sc_f=3, sc_l=2), 0.05),
+]
+
+
+@pytest.mark.parametrize("cfg", CONFIGS, ids=[c[0] for c in CONFIGS])
+def test_run_dense_parity(gpu, port, cfg):
+    _, mode, ch, op, w0, h0, kw, max_tol = cfg
+    A, B, gt = make_pair(h0, w0, channels=ch, mode="OF" if mode == 1 else "DE", seed=0)
+    p = gpu.operating_point(op, w0, mode, ch).copy(verbosity=0, **kw)
+    want, want_low = port.run_dense(to_orc(p), A, B, want_lowres=True)
+    with gpu.Handle(p, w0, h0, max_batch=3) as hd:
+        out = hd.run_host(np.stack([A, B, A]), np.stack([B, A, B]))
+        low = hd.fetch_flow(0, p.sc_l, pair=2)
+        assert hd.launch_count() > 0
+    m, mx = epe(out[0], want)
+    assert m <= MEAN_TOL and mx <= max_tol, "EPE(GPU,CPU) mean %g max %g" % (m, mx)
+    assert np.array_equal(out[0], out[2])                     # batch position does not matter
+    assert epe(low, want_low)[0] <= MEAN_TOL
+    # the flow is a flow: error against the synthetic ground truth is what the CPU reference gets
+    assert abs(epe(out[0], gt)[0] - epe(want, gt)[0]) < 5e-3
+    # swapped pair (B -> A) is a different problem and must not leak from its neighbours
+    want_swapped = port.run_dense(to_orc(p), B, A)
+    assert epe(out[1], want_swapped)[0] <= MEAN_TOL
+
+
+def test_run_list_and_chunking(gpu, port):
+    """disb200_run_batch (pointer lists) and n > max_batch chunking give the same answers."""
+    pairs = [make_pair(100, 180, seed=s)[:2] for s in range(5)]
+    p = gpu.operating_point(2, 180).copy(verbosity=0, sc_f=2, sc_l=1)
+    As, Bs = [a for a, _ in pairs], [b for _, b in pairs]
+    with gpu.Handle(p, 180, 100, max_batch=2) as hd:
+        outs = hd.run_list(As, Bs)
+        outs2 = hd.run_host(np.stack(As), np.stack(Bs))
+    for i in range(5):
+        assert np.array_equal(outs[i], outs2[i])
+        assert epe(outs[i], port.run_dense(to_orc(p), As[i], Bs[i]))[0] <= MEAN_TOL
+
+
+def test_identical_frames_give_exactly_zero(gpu):
+    A, _, _ = make_pair(218, 512, seed=1)
+    p = gpu.operating_point(2, 512).copy(verbosity=0)
+    with gpu.Handle(p, 512, 218, 1) as hd:
+        assert np.all(hd.run_host(A[None], A[None]) == 0)
+
+
+def test_constant_frames(gpu, port):
+    """Zero-texture patches: mares == 0 -> immediate convergence; Hessian regulariser (patch.cpp:76-84)."""
+    A = np.full((96, 160), 77, np.uint8)
+    B = A.copy()
+    B[:, 80:] = 90
+    p = gpu.operating_point(2, 160).copy(verbosity=0, sc_f=2, sc_l=1)
+    with gpu.Handle(p, 160, 96, 1) as hd:
+        out = hd.run_host(A[None], B[None])[0]
+    want = port.run_dense(to_orc(p), A, B)
+    assert np.isfinite(out).all()
+    assert epe(out, want)[0] <= MEAN_TOL
+
+
+def test_large_motion_outliers_and_borders(gpu, port):
+    """Patches that start or move outside the valid box are reset (patch.cpp:133-139,197-206)."""
+    A, B, _ = make_pair(120, 200, seed=9)
+    B = np.roll(B, 37, axis=1)        # far beyond the search range at the fine levels
+    p = gpu.operating_point(2, 200).copy(verbosity=0, sc_f=3, sc_l=1)
+    with gpu.Handle(p, 200, 120, 1) as hd:
+        out = hd.run_host(A[None], B[None])[0]
+    want = port.run_dense(to_orc(p), A, B)
+    m, mx = epe(out, want)
+    assert np.isfinite(out).all() and m <= MEAN_TOL, (m, mx)
+
+
+def test_deterministic(gpu):
+    A, B, _ = make_pair(436, 1024, seed=2)
+    p = gpu.operating_point(2, 1024).copy(verbosity=0, usefbcon=1)
+    with gpu.Handle(p, 1024, 436, 2) as hd:
+        o1 = hd.run_host(np.stack([A, A]), np.stack([B, B])).copy()
+        o2 = hd.run_host(np.stack([A, A]), np.stack([B, B]))
+    assert np.array_equal(o1, o2) and np.array_equal(o1[0], o1[1])
+
+
+# ------------------------------------------------------------------------------ full bench size, properties only
+def test_full_batch_properties(gpu, port):
+    """BASELINE.json configs[0] at the bench batch size: every copy of a pair gives the same bits,
+    distinct pairs match the oracle, device-pointer and host-pointer entry points agree."""
+    import torch
+    w0, h0, nb = 1024, 436, 256
+    p = gpu.operating_point(2, w0).copy(verbosity=0)
+    pairs = [make_pair(h0, w0, seed=s)[:2] for s in range(2)]
+    A = np.stack([pairs[i % 2][0] for i in range(nb)])
+    B = np.stack([pairs[i % 2][1] for i in range(nb)])
+    with gpu.Handle(p, w0, h0, nb) as hd:
+        dA, dB = torch.from_numpy(A).cuda(), torch.from_numpy(B).cuda()
+        dOut = torch.empty((nb, h0, w0, 2), dtype=torch.float32, device="cuda")
+        torch.cuda.synchronize()
+        hd.run_device(dA.data_ptr(), dB.data_ptr(), nb, dOut.data_ptr())
+        hd.sync()
+        out = dOut.cpu().numpy()
+        host = hd.run_host(A[:6], B[:6])
+    for s in range(2):
+        assert all(np.array_equal(out[s], out[i]) for i in range(s, nb, 2))
+        assert epe(out[s], port.run_dense(to_orc(p), *pairs[s]))[0] <= MEAN_TOL
+    assert np.array_equal(host, out[:6])
