@@ -335,36 +335,31 @@ __device__ __forceinline__ void data_term_de(const DerivPtrs& D, size_t o, size_
 }
 
 // Data term + laplacian of the current flow into the right-hand side + (OF) inverse of the
-// 2x2 diagonal block.  Outputs per pixel: coef {hl, h, vt, v}; OF: inv {i11, i12, i22, 0},
-// rhs {b1, b2}; DE: inv {a11 + sum(psi)}, rhs {b1}.
+// 2x2 diagonal block, for one pixel.  `sp` (diffusivity plane) and `q` (flow increment) may
+// point to shared or global memory.  Output pack, two float4 per pixel:
+//   OF: cA = {h, v, vt, i12}   cB = {i11, i22, b1, b2}
+//   DE: cA = {h, v, vt, a11 + sum(psi)}   cB = {b1, 0, 0, 0}
+// (hl of pixel i is h of pixel i-1, which the solver already holds.)
 template <int C, bool OF>
-__global__ void system_kernel(DerivPtrs D, const float* __restrict__ mask, const float* __restrict__ s,
-                              const float* __restrict__ flow, const float* __restrict__ du, Dims d, float hd3,
-                              float hg3, float4* __restrict__ coef, float* __restrict__ inv, float* __restrict__ rhs) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y, pair = blockIdx.z;
-  if (i >= d.w) return;
+__device__ __forceinline__ void system_pixel(const DerivPtrs& D, const float* __restrict__ mask, const float* sp,
+                                             const float* __restrict__ fl, const float* q, int i, int j, int w,
+                                             int h, size_t cstride, size_t o, float hd3, float hg3, float4& cA,
+                                             float4& cB) {
   constexpr int NOP = OF ? 2 : 1;
-  const int w = d.w, h = d.h;
-  const size_t pix = (size_t)j * w + i;
-  const size_t po = (size_t)pair * d.plane;
-  const float* sp = s + po;
+  const int pix = j * w + i;
   const float sc = sp[pix];
   // smooth_horiz / smooth_vert (opticalflow_aux.c:161-184): h(i) = s(i)+s(i+1), 0 in the last column
   const float hh = i < w - 1 ? sc + sp[pix + 1] : 0.f;
   const float hl = i > 0 ? sp[pix - 1] + sc : 0.f;
   const float vv = j < h - 1 ? sc + sp[pix + w] : 0.f;
   const float vt = j > 0 ? sp[pix - w] + sc : 0.f;
-  const float* fl = flow + (size_t)pair * w * h * NOP;
-  const float* q = du + po * NOP;
-  const float m = mask[po + pix];
-  const size_t o = (size_t)pair * C * d.plane + pix;
+  const float m = mask[pix];
   float b[NOP];
   float A11, A12 = 0.f, A22 = 0.f;
   if (OF) {
-    const float2 dd = *reinterpret_cast<const float2*>(q + pix * 2);
-    data_term_of<C>(D, o, d.plane, m, dd.x, dd.y, hd3, hg3, A11, A12, A22, b[0], b[NOP - 1]);
+    data_term_of<C>(D, o + pix, cstride, m, q[pix * NOP], q[pix * NOP + NOP - 1], hd3, hg3, A11, A12, A22, b[0], b[NOP - 1]);
   } else {
-    data_term_de<C>(D, o, d.plane, m, q[pix], hd3, hg3, A11, b[0]);
+    data_term_de<C>(D, o + pix, cstride, m, q[pix], hd3, hg3, A11, b[0]);
   }
   // sub_laplacian (opticalflow_aux.c:194-223): b = (((b - t(i-1)) + t(i)) - tv(j-1)) + tv(j)
 #pragma unroll
@@ -377,7 +372,6 @@ __global__ void system_kernel(DerivPtrs D, const float* __restrict__ mask, const
     if (j < h - 1) bb += vv * (fl[(pix + w) * NOP + k] - wc);
     b[k] = bb;
   }
-  coef[po + pix] = make_float4(hl, hh, vt, vv);
   if (OF) {
     // solver.c:122-128,184,244
     float dpsis;
@@ -386,8 +380,8 @@ __global__ void system_kernel(DerivPtrs D, const float* __restrict__ mask, const
     else dpsis = hl + (hh + vt);
     const float I11 = A22 + dpsis, I22 = A11 + dpsis;
     const float det = I11 * I22 - A12 * A12;
-    reinterpret_cast<float4*>(inv)[po + pix] = make_float4(I11 / det, A12 / (0.f - det), I22 / det, 0.f);
-    reinterpret_cast<float2*>(rhs)[po + pix] = make_float2(b[0], b[NOP - 1]);
+    cA = make_float4(hh, vv, vt, A12 / (0.f - det));
+    cB = make_float4(I11 / det, I22 / det, b[0], b[NOP - 1]);
   } else {
     // solver.c:447-465: sum_dpsis accumulates top, left, bottom, right
     float sum = 0.f;
@@ -395,105 +389,206 @@ __global__ void system_kernel(DerivPtrs D, const float* __restrict__ mask, const
     if (i > 0) sum += hl;
     if (j < h - 1) sum += vv;
     if (i < w - 1) sum += hh;
-    inv[po + pix] = A11 + sum;
-    rhs[po + pix] = b[0];
+    cA = make_float4(hh, vv, vt, A11 + sum);
+    cB = make_float4(b[0], 0.f, 0.f, 0.f);
   }
 }
 
-}  // namespace
-}  // namespace disb200
+template <int C, bool OF>
+__global__ void system_kernel(DerivPtrs D, const float* __restrict__ mask, const float* __restrict__ s,
+                              const float* __restrict__ flow, const float* __restrict__ du, Dims d, float hd3,
+                              float hg3, float4* __restrict__ cA, float4* __restrict__ cB) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y, pair = blockIdx.z;
+  if (i >= d.w) return;
+  constexpr int NOP = OF ? 2 : 1;
+  const size_t po = (size_t)pair * d.plane;
+  float4 a, b;
+  system_pixel<C, OF>(D, mask + po, s + po, flow + (size_t)pair * d.w * d.h * NOP, du + po * NOP, i, j, d.w, d.h, d.plane,
+                      (size_t)pair * C * d.plane, hd3, hg3, a, b);
+  cA[po + (size_t)j * d.w + i] = a;
+  cB[po + (size_t)j * d.w + i] = b;
+}
 
-namespace disb200 {
-namespace {
-
-// One lexicographic SOR update of pixel (i, j) (solver.c:129-141,191-203,251-262 for OF;
-// solver.c:446-467 for DE).  `left` carries the value just written at (i-1, j).
+// compute_smoothness, first half, for one pixel (uu = wx + du; DE: clamped; first iteration: uu = wx)
 template <bool OF>
-__device__ __forceinline__ void sor_pixel(float* du, const float4* __restrict__ coef, const float* __restrict__ inv,
-                                          const float* __restrict__ rhs, int i, int j, int w, int h, float omega,
-                                          float2& left) {
-  const size_t pix = (size_t)j * w + i;
-  const float4 c = __ldg(coef + pix);   // {hl, h, vt, v}
-  if (OF) {
-    float2* q = reinterpret_cast<float2*>(du);
-    const float4 iv = __ldg(reinterpret_cast<const float4*>(inv) + pix);
-    const float2 b = __ldg(reinterpret_cast<const float2*>(rhs) + pix);
-    const float2 cur = q[pix];
-    float2 r = make_float2(0.f, 0.f), t = r, bt = r;
-    if (i < w - 1) r = q[pix + 1];
-    if (j > 0) t = q[pix - w];
-    if (j < h - 1) bt = q[pix + w];
-    float s1, s2;
-    if (j == 0) {
-      s1 = mla(mla(b.x, c.y, r.x), c.w, bt.x);
-      s2 = mla(mla(b.y, c.y, r.y), c.w, bt.y);
-    } else if (j < h - 1) {
-      s1 = mla(c.y * r.x, c.z, t.x) + mla(b.x, c.w, bt.x);
-      s2 = mla(c.y * r.y, c.z, t.y) + mla(b.y, c.w, bt.y);
+__device__ __forceinline__ float smooth_pixel(const float* __restrict__ fl, const float* q, int i, int j, int w, int h,
+                                              int camlr, float quarter_alpha, bool first_iter) {
+  constexpr int NOP = OF ? 2 : 1;
+  const int xm = max(i - 1, 0), xp = min(i + 1, w - 1), ym = max(j - 1, 0), yp = min(j + 1, h - 1);
+  float ul, vl, uc, vc, ur, vr, ut, vt, ub, vb;
+  auto ld = [&](int x, int y, float& u, float& v) {
+    const int pix = y * w + x;
+    if (OF) {
+      u = fl[pix * NOP];
+      v = fl[pix * NOP + NOP - 1];
+      if (!first_iter) { u = u + q[pix * NOP]; v = v + q[pix * NOP + NOP - 1]; }
     } else {
-      s1 = mla(mla(b.x, c.y, r.x), c.z, t.x);
-      s2 = mla(mla(b.y, c.y, r.y), c.z, t.y);
+      u = fl[pix];
+      if (!first_iter) { const float t = u + q[pix]; u = camlr == 0 ? fminf(t, 0.f) : fmaxf(t, 0.f); }
+      v = 0.f;
+    }
+  };
+  ld(xm, j, ul, vl); ld(i, j, uc, vc); ld(xp, j, ur, vr); ld(i, ym, ut, vt); ld(i, yp, ub, vb);
+  const float ux = tap3(ul, uc, ur), vx = tap3(vl, vc, vr), uy = tap3(ut, uc, ub), vy = tap3(vt, vc, vb);
+  const float eps = 0.001f * 0.001f;
+  const float t = eps + ((ux * ux + uy * uy) + (vx * vx + vy * vy));
+  return quarter_alpha / sqrtf(t);
+}
+
+// One lexicographic SOR update (solver.c:129-141,191-203,251-262 for OF; solver.c:446-467 for
+// DE) from values already in registers: cur = current value of the pixel, r / t / bt = right,
+// top, bottom neighbours (zero where there is none), left = value just written at (i-1, j),
+// hl = h(i-1, j).  Returns the new value.
+template <bool OF>
+__device__ __forceinline__ float2 sor_update(const float4 cA, const float4 cB, float hl, bool has_left, int rowtype,
+                                             float omega, float2 left, float2 cur, float2 r, float2 t, float2 bt) {
+  float2 nw = make_float2(0.f, 0.f);
+  if (OF) {
+    const float hh = cA.x, vv = cA.y, vt = cA.z, i12 = cA.w, i11 = cB.x, i22 = cB.y, b1 = cB.z, b2 = cB.w;
+    float s1, s2;
+    if (rowtype == 0) {
+      s1 = mla(mla(b1, hh, r.x), vv, bt.x);
+      s2 = mla(mla(b2, hh, r.y), vv, bt.y);
+    } else if (rowtype == 1) {
+      s1 = mla(hh * r.x, vt, t.x) + mla(b1, vv, bt.x);
+      s2 = mla(hh * r.y, vt, t.y) + mla(b2, vv, bt.y);
+    } else {
+      s1 = mla(mla(b1, hh, r.x), vt, t.x);
+      s2 = mla(mla(b2, hh, r.y), vt, t.y);
     }
     float B1 = s1, B2 = s2;
-    if (i > 0) { B1 = c.x * left.x + s1; B2 = c.x * left.y + s2; }
-    float2 nw;
-    nw.x = cur.x + omega * (iv.x * B1 + iv.y * B2 - cur.x);
-    nw.y = cur.y + omega * (iv.y * B1 + iv.z * B2 - cur.y);
-    q[pix] = nw;
-    left = nw;
+    if (has_left) { B1 = hl * left.x + s1; B2 = hl * left.y + s2; }
+    nw.x = cur.x + omega * (i11 * B1 + i12 * B2 - cur.x);
+    nw.y = cur.y + omega * (i12 * B1 + i22 * B2 - cur.y);
   } else {
     float sigma = 0.f;
-    if (j > 0) sigma -= c.z * du[pix - w];
-    if (i > 0) sigma -= c.x * left.x;
-    if (j < h - 1) sigma -= c.w * du[pix + w];
-    if (i < w - 1) sigma -= c.y * du[pix + 1];
-    const float A11 = __ldg(inv + pix), B1 = __ldg(rhs + pix) - sigma;
-    const float nw = (1.0f - omega) * du[pix] + omega * (B1 / A11);
-    du[pix] = nw;
-    left.x = nw;
+    if (rowtype != 0) sigma -= cA.z * t.x;
+    if (has_left) sigma -= hl * left.x;
+    if (rowtype != 2) sigma -= cA.y * bt.x;
+    sigma -= cA.x * r.x;   // h is 0 in the last column, r is 0 there too: adds -0 like the skipped branch adds nothing
+    const float B1 = cB.x - sigma;
+    nw.x = (1.0f - omega) * cur.x + omega * (B1 / cA.w);
+  }
+  return nw;
+}
+
+template <bool OF>
+__device__ __forceinline__ float2 ld_du(const float* du, int pix) {
+  if (OF) return reinterpret_cast<const float2*>(du)[pix];
+  return make_float2(du[pix], 0.f);
+}
+template <bool OF>
+__device__ __forceinline__ void st_du(float* du, int pix, float2 v) {
+  if (OF) reinterpret_cast<float2*>(du)[pix] = v;
+  else du[pix] = v.x;
+}
+
+// Skewed wavefront over rows [j0, j0 + rows) for `nsweeps` pipelined sweeps (nsweeps > 1 only
+// when the band is the whole image).  Pixel (i, j) of sweep s needs (i-1, j) and (i, j-1) of
+// sweep s and (i+1, j), (i, j+1) of sweep s-1.  Thread (s, r) owns row r of sweep s and, at
+// macro-step m, updates the K columns of chunk  m - r - 2 s  left to right, so every dependency
+// (including column i+1 of the next chunk in sweep s-1) was produced at least one barrier
+// earlier, and no value is overwritten before its last reader of the previous sweep.  K columns
+// per barrier amortise the barrier and let the neighbour loads of a chunk issue together.
+// The per-pixel coefficients do not depend on neighbours: they are loaded two chunks ahead
+// into a register ring whose slot is m % 2 (static after unrolling), which takes the L2 round
+// trip off the critical path.  Plain (coherent) loads, because in the fused kernel the
+// coefficients were written by this CTA.  All threads of the CTA must call this.
+template <bool OF>
+__device__ __forceinline__ void sor_wavefront(float* du, const float4* cA, const float4* cB, int w, int h, int j0,
+                                              int rows, int nsweeps, float omega) {
+  constexpr int K = 4;
+  const int tid = threadIdx.x;
+  const int s = tid / rows, r = tid - s * rows, j = j0 + r;
+  const bool act = s < nsweeps;
+  const int off = r + 2 * s;
+  const int nchunks = (w + K - 1) / K;
+  const int nsteps = nchunks + rows - 1 + 2 * (nsweeps - 1);
+  const int rowtype = j == 0 ? 0 : (j < h - 1 ? 1 : 2);
+  const int rowbase = (act ? j : 0) * w;
+  const float4* pa = cA + rowbase;
+  const float4* pb = cB + rowbase;
+  float4 ra[2][K], rb[2][K];
+#pragma unroll
+  for (int u = 0; u < 2; ++u) {
+    const int c = ((u - off % 2) + 2) % 2;   // the one chunk in {0, 1} that is consumed from slot u
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      ra[u][k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      rb[u][k] = ra[u][k];
+      const int i = c * K + k;
+      if (act && i < w) { ra[u][k] = pa[i]; rb[u][k] = pb[i]; }
+    }
+  }
+  const float2 zero2 = make_float2(0.f, 0.f);
+  float2 left = zero2;
+  float hprev = 0.f;
+  for (int m0 = 0; m0 < nsteps; m0 += 2) {
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int c = m0 + u - off;
+      if (act && c >= 0 && c < nchunks) {
+        const int i0 = c * K;
+        float2 own[K + 1], top[K], bot[K];
+#pragma unroll
+        for (int k = 0; k <= K; ++k) own[k] = (i0 + k < w) ? ld_du<OF>(du, rowbase + i0 + k) : zero2;
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+          const bool in = i0 + k < w;
+          top[k] = (in && rowtype != 0) ? ld_du<OF>(du, rowbase + i0 + k - w) : zero2;
+          bot[k] = (in && rowtype != 2) ? ld_du<OF>(du, rowbase + i0 + k + w) : zero2;
+        }
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+          if (i0 + k < w) {
+            const float2 nw = sor_update<OF>(ra[u][k], rb[u][k], hprev, i0 + k > 0, rowtype, omega, left, own[k],
+                                             own[k + 1], top[k], bot[k]);
+            st_du<OF>(du, rowbase + i0 + k, nw);
+            left = nw;
+            hprev = ra[u][k].x;
+          }
+        }
+        // refill the slot only after its last use, so the loads target the ring registers directly
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+          const int i = i0 + 2 * K + k;
+          if (i < w) { ra[u][k] = pa[i]; rb[u][k] = pb[i]; }
+        }
+      }
+      __syncthreads();
+    }
   }
 }
 
-// One CTA per frame pair.  Pixel (i, j) of sweep s needs (i-1, j) and (i, j-1) of sweep s and
-// (i+1, j), (i, j+1) of sweep s-1, so with one thread per (sweep, row) and thread (s, j)
-// working on column  step - j - 2 s  every dependency was produced at least one barrier
-// earlier: all sweeps of the call run as one skewed wavefront of  w + h - 1 + 2 (iters-1)
-// steps.  When rows x sweeps exceed the CTA, sweeps run one after another over row bands,
-// which is the same lexicographic order.
+// General path: one CTA per frame pair, increment du in global memory.  When rows x sweeps
+// exceed the CTA, sweeps run one after another over row bands (same lexicographic order).
 template <bool OF>
-__global__ void __launch_bounds__(1024)
-sor_wavefront_kernel(float* du_all, const float4* __restrict__ coef_all, const float* __restrict__ inv_all,
-                     const float* __restrict__ rhs_all, Dims d, int iters, float omega, int pipelined) {
+__global__ void __launch_bounds__(512)
+sor_wavefront_kernel(float* du_all, const float4* __restrict__ cA_all, const float4* __restrict__ cB_all, Dims d,
+                     int iters, float omega, int pipelined) {
   constexpr int NOP = OF ? 2 : 1;
   const int pair = blockIdx.x, w = d.w, h = d.h;
   float* du = du_all + (size_t)pair * d.plane * NOP;
-  const float4* coef = coef_all + (size_t)pair * d.plane;
-  const float* inv = inv_all + (size_t)pair * d.plane * (OF ? 4 : 1);
-  const float* rhs = rhs_all + (size_t)pair * d.plane * NOP;
-  const int tid = threadIdx.x;
-  float2 left = make_float2(0.f, 0.f);
+  const float4* cA = cA_all + (size_t)pair * d.plane;
+  const float4* cB = cB_all + (size_t)pair * d.plane;
   if (pipelined) {
-    const int s = tid / h, j = tid - s * h;
-    const bool act = s < iters;
-    const int nsteps = w + h - 1 + 2 * (iters - 1);
-    for (int step = 0; step < nsteps; ++step) {
-      const int i = step - j - 2 * s;
-      if (act && i >= 0 && i < w) sor_pixel<OF>(du, coef, inv, rhs, i, j, w, h, omega, left);
-      __syncthreads();
-    }
+    sor_wavefront<OF>(du, cA, cB, w, h, 0, h, iters, omega);
   } else {
     const int R = blockDim.x;
     for (int it = 0; it < iters; ++it)
-      for (int j0 = 0; j0 < h; j0 += R) {
-        const int j = j0 + tid, rows = min(R, h - j0);
-        const int nsteps = w + rows - 1;
-        for (int step = 0; step < nsteps; ++step) {
-          const int i = step - tid;
-          if (j < h && i >= 0 && i < w) sor_pixel<OF>(du, coef, inv, rhs, i, j, w, h, omega, left);
-          __syncthreads();
-        }
-      }
+      for (int j0 = 0; j0 < h; j0 += R) sor_wavefront<OF>(du, cA, cB, w, h, j0, min(R, h - j0), 1, omega);
   }
+}
+
+template <bool OF>
+__global__ void smooth_kernel2(const float* __restrict__ flow, const float* __restrict__ du, Dims d, int camlr,
+                               float quarter_alpha, int first_iter, float* __restrict__ s) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y, pair = blockIdx.z;
+  if (i >= d.w) return;
+  constexpr int NOP = OF ? 2 : 1;
+  s[(size_t)pair * d.plane + (size_t)j * d.w + i] =
+      smooth_pixel<OF>(flow + (size_t)pair * d.w * d.h * NOP, du + (size_t)pair * d.plane * NOP, i, j, d.w, d.h, camlr,
+                       quarter_alpha, first_iter != 0);
 }
 
 template <bool OF>
@@ -509,6 +604,53 @@ __global__ void finish_kernel(float* __restrict__ flow, const float* __restrict_
   if (OF) o[1] = v;
 }
 
+// Small levels: one CTA per frame pair runs ALL fixed-point iterations of the level —
+// diffusivity, linear system, wavefront SOR, flow update — with the flow increment and the
+// diffusivity plane resident in shared memory; only the coefficient pack goes through global
+// memory (L2).  Replaces 3 launches per fixed-point iteration by one launch per level.
+template <int C, bool OF>
+__global__ void __launch_bounds__(512)
+tv_fused_kernel(DerivPtrs D, const float* __restrict__ mask_all, float* __restrict__ flow_all, Dims d, int camlr,
+                float quarter_alpha, float hd3, float hg3, int n_inner, int iters, float omega,
+                float4* __restrict__ cA_all, float4* __restrict__ cB_all) {
+  constexpr int NOP = OF ? 2 : 1;
+  extern __shared__ float4 smem_raw[];
+  const int pair = blockIdx.x, w = d.w, h = d.h, npix = w * h;
+  float* du = reinterpret_cast<float*>(smem_raw);          // [npix][NOP]
+  float* sp = du + (size_t)npix * NOP;                      // [npix]
+  float* fl = flow_all + (size_t)pair * npix * NOP;
+  const float* mask = mask_all + (size_t)pair * d.plane;
+  float4* cA = cA_all + (size_t)pair * d.plane;
+  float4* cB = cB_all + (size_t)pair * d.plane;
+  const size_t o = (size_t)pair * C * d.plane;
+  const int tid = threadIdx.x, T = blockDim.x;
+  for (int k = tid; k < npix * NOP; k += T) du[k] = 0.f;
+  __syncthreads();
+  for (int it = 0; it < n_inner; ++it) {
+    for (int pix = tid; pix < npix; pix += T) {
+      const int j = pix / w, i = pix - j * w;
+      sp[pix] = smooth_pixel<OF>(fl, du, i, j, w, h, camlr, quarter_alpha, it == 0);
+    }
+    __syncthreads();
+    for (int pix = tid; pix < npix; pix += T) {
+      const int j = pix / w, i = pix - j * w;
+      float4 a, b;
+      system_pixel<C, OF>(D, mask, sp, fl, du, i, j, w, h, d.plane, o, hd3, hg3, a, b);
+      cA[pix] = a;
+      cB[pix] = b;
+    }
+    __syncthreads();
+    sor_wavefront<OF>(du, cA, cB, w, h, 0, h, iters, omega);
+  }
+  // wx = uu (refine_variational.cpp:226-227, 323)
+  for (int pix = tid; pix < npix; pix += T) {
+    float u, v;
+    load_uv<OF>(fl, du, pix, camlr, u, v);
+    fl[pix * NOP] = u;
+    if (OF) fl[pix * NOP + 1] = v;
+  }
+}
+
 template <int C, bool OF>
 void varref_level_impl(const float* im_a, const float* im_b, float* flow, const LevelGeom& g, const DisParams& p,
                        int camlr, const VarRefBuffers& vb, int n, cudaStream_t st, LaunchStats* ls) {
@@ -521,19 +663,31 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
   warp_kernel<C, OF><<<grd, blk, 0, st>>>(im_a, im_b, flow, d, vb.avg, vb.Iz, vb.mask);
   deriv1_kernel<<<grdc, blk, 0, st>>>(vb.avg, vb.Iz, d, vb.Ix, vb.Iy, vb.Ixz, vb.Iyz);
   deriv2_kernel<<<grdc, blk, 0, st>>>(vb.Ix, vb.Iy, d, vb.Ixx, vb.Ixy, vb.Iyy);
-  cudaMemsetAsync(vb.du, 0, sizeof(float) * vb.plane_cap * NOP * n, st);
   ls->launches += 3;
   DerivPtrs D{vb.Ix, vb.Iy, vb.Iz, vb.Ixx, vb.Ixy, vb.Iyy, vb.Ixz, vb.Iyz};
-  const bool pipelined = g.h * p.tv_solverit <= 1024;
-  int threads = pipelined ? g.h * p.tv_solverit : (g.h < 1024 ? g.h : 1024);
+  float4* cA = reinterpret_cast<float4*>(vb.coef);
+  float4* cB = reinterpret_cast<float4*>(vb.inv);
+  const bool pipelined = g.h * p.tv_solverit <= 512;
+  const size_t fused_smem = (size_t)g.w * g.h * (NOP + 1) * sizeof(float);
+  if (pipelined && fused_smem <= 100 * 1024) {
+    int threads = ((g.h * p.tv_solverit + 31) / 32) * 32;
+    if (threads < 256) threads = 256;
+    cudaFuncSetAttribute(tv_fused_kernel<C, OF>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+    if (ls->mark) ls->mark(ls->ctx, 5, 1);
+    tv_fused_kernel<C, OF><<<n, threads, fused_smem, st>>>(D, vb.mask, flow, d, camlr, qa, hd3, hg3, n_inner,
+                                                           p.tv_solverit, p.tv_sor, cA, cB);
+    if (ls->mark) ls->mark(ls->ctx, 5, 0);
+    ls->launches++;
+    return;
+  }
+  cudaMemsetAsync(vb.du, 0, sizeof(float) * vb.plane_cap * NOP * n, st);
+  int threads = pipelined ? g.h * p.tv_solverit : (g.h < 512 ? g.h : 512);
   threads = ((threads + 31) / 32) * 32;
   for (int it = 0; it < n_inner; ++it) {
-    smooth_kernel<OF><<<grd, blk, 0, st>>>(flow, vb.du, d, camlr, qa, it == 0, vb.smooth);
-    system_kernel<C, OF><<<grd, blk, 0, st>>>(D, vb.mask, vb.smooth, flow, vb.du, d, hd3, hg3,
-                                              reinterpret_cast<float4*>(vb.coef), vb.inv, vb.rhs);
+    smooth_kernel2<OF><<<grd, blk, 0, st>>>(flow, vb.du, d, camlr, qa, it == 0, vb.smooth);
+    system_kernel<C, OF><<<grd, blk, 0, st>>>(D, vb.mask, vb.smooth, flow, vb.du, d, hd3, hg3, cA, cB);
     if (ls->mark) ls->mark(ls->ctx, 5, 1);
-    sor_wavefront_kernel<OF><<<n, threads, 0, st>>>(vb.du, reinterpret_cast<const float4*>(vb.coef), vb.inv, vb.rhs, d,
-                                                    p.tv_solverit, p.tv_sor, pipelined ? 1 : 0);
+    sor_wavefront_kernel<OF><<<n, threads, 0, st>>>(vb.du, cA, cB, d, p.tv_solverit, p.tv_sor, pipelined ? 1 : 0);
     if (ls->mark) ls->mark(ls->ctx, 5, 0);
     ls->launches += 3;
   }
@@ -544,7 +698,7 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
 }  // namespace
 
 size_t varref_plane_count(int C, int nop) {
-  // avg, Iz, Ix, Iy, Ixx, Ixy, Iyy, Ixz, Iyz (C each) + mask + s + du (nop) + coef (4) + inv (4) + rhs (nop)
+  // avg, Iz, Ix, Iy, Ixx, Ixy, Iyy, Ixz, Iyz (C each) + mask + s + du (nop) + coefficient pack (2 x float4) + spare (nop)
   return (size_t)9 * C + 2 + nop + 4 + 4 + nop;
 }
 
