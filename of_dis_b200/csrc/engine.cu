@@ -5,6 +5,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -317,8 +318,17 @@ struct Engine {
 using namespace disb200;
 
 struct DisHandle {
-  Engine e;
+  Engine e;                       // sub-batch engine 0; owns the handle's main stream
+  std::vector<Engine*> extra;     // sub-batch engines 1.. (own stream each), created on demand
+  int nsub = 1;                   // sub-batches run concurrently on separate streams
+  int cap = 0;                    // pairs per sub-batch engine
+  int max_batch = 0;              // pairs per call
+  int last_per = 0;               // sub-batch size of the most recent run (for disb200_fetch)
+  cudaEvent_t ev_fork = nullptr;
+  std::vector<cudaEvent_t> ev_join;
+  int launches = 0;
   int w0 = 0, h0 = 0, padl = 0, padt = 0;
+  Engine& sub(int i) { return i == 0 ? e : *extra[i - 1]; }
   // double-buffered device staging for the host-pointer entry points
   uint8_t* dA[2] = {nullptr, nullptr};
   uint8_t* dB[2] = {nullptr, nullptr};
@@ -332,9 +342,9 @@ struct DisHandle {
   int ensure_staging() {
     if (staging) return DISB200_OK;
     for (int k = 0; k < 2; ++k) {
-      int rc = e.dalloc(&dA[k], in_bytes * e.max_batch);
-      if (!rc) rc = e.dalloc(&dB[k], in_bytes * e.max_batch);
-      if (!rc) rc = e.dalloc(&dOut[k], out_bytes / sizeof(float) * e.max_batch);
+      int rc = e.dalloc(&dA[k], in_bytes * max_batch);
+      if (!rc) rc = e.dalloc(&dB[k], in_bytes * max_batch);
+      if (!rc) rc = e.dalloc(&dOut[k], out_bytes / sizeof(float) * max_batch);
       if (rc) return rc;
       CU(cudaEventCreateWithFlags(&ev_h2d[k], cudaEventDisableTiming));
       CU(cudaEventCreateWithFlags(&ev_comp[k], cudaEventDisableTiming));
@@ -346,14 +356,64 @@ struct DisHandle {
     return DISB200_OK;
   }
 
-  // enqueue the whole per-batch pipeline on e.stream
-  int enqueue(const uint8_t* a, const uint8_t* b, int n, float* out) {
-    e.build_pyramids(a, b, n, w0, h0, padl, padt);
-    int rc = e.run_levels(n);
+  int ensure_subs() {
+    while ((int)extra.size() < nsub - 1) {
+      Engine* x = new Engine();
+      int rc = x->init(e.p, e.W, e.H, cap, e.device);
+      if (rc) { x->destroy(); delete x; return rc; }
+      extra.push_back(x);
+      cudaEvent_t ev;
+      CU(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
+      ev_join.push_back(ev);
+    }
+    if (!ev_fork) CU(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+    return DISB200_OK;
+  }
+
+  int enqueue_one(Engine& E, const uint8_t* a, const uint8_t* b, int n, float* out) {
+    E.build_pyramids(a, b, n, w0, h0, padl, padt);
+    int rc = E.run_levels(n);
     if (rc) return rc;
     {
-      Engine::StageScope sc(&e, 4);
-      launch_upsample_crop(e.flow[0][e.p.sc_l], e.geom[e.p.sc_l], e.nop, e.p.sc_l, padl, padt, w0, h0, out, n, e.stream, &e.stats);
+      Engine::StageScope sc(&E, 4);
+      launch_upsample_crop(E.flow[0][E.p.sc_l], E.geom[E.p.sc_l], E.nop, E.p.sc_l, padl, padt, w0, h0, out, n, E.stream, &E.stats);
+    }
+    return DISB200_OK;
+  }
+
+  // Enqueue the whole per-batch pipeline.  The batch is cut into nsub sub-batches that run on
+  // their own streams (forked from / joined into e.stream), so that the latency-bound kernels
+  // of one sub-batch (coarse-level SOR wavefronts) overlap the throughput-bound kernels of
+  // another (inverse search, upsample).
+  int enqueue(const uint8_t* a, const uint8_t* b, int n, float* out) {
+    const int S = std::min(nsub, n);
+    const bool serial = e.stage_timing;              // the per-stage stopwatch needs a single stream
+    const int per = (n + S - 1) / S;
+    if (per > cap) return fail(DISB200_EINVAL, "internal: sub-batch exceeds engine capacity");
+    last_per = per;
+    launches = 0;
+    if (S > 1 && !serial) {
+      int rc = ensure_subs();
+      if (rc) return rc;
+      CU(cudaEventRecord(ev_fork, e.stream));
+    }
+    const size_t out_elems = out_bytes / sizeof(float);
+    for (int i = 0; i < S; ++i) {
+      const int lo = i * per, m = std::min(per, n - lo);
+      if (m <= 0) break;
+      Engine& E = serial ? e : sub(i);
+      if (i > 0 && !serial) {
+        E.begin_run();
+        CU(cudaStreamWaitEvent(E.stream, ev_fork, 0));
+      }
+      int rc = enqueue_one(E, a + (size_t)lo * in_bytes, b + (size_t)lo * in_bytes, m, out + (size_t)lo * out_elems);
+      if (rc) return rc;
+      if (i == 0 || !serial) launches += E.stats.launches;
+      if (serial) launches = e.stats.launches;
+      if (i > 0 && !serial) {
+        CU(cudaEventRecord(ev_join[i - 1], E.stream));
+        CU(cudaStreamWaitEvent(e.stream, ev_join[i - 1], 0));
+      }
     }
     cudaError_t ce = cudaGetLastError();
     if (ce != cudaSuccess) return fail(DISB200_ECUDA, std::string("kernel launch: ") + cudaGetErrorString(ce));
@@ -362,11 +422,14 @@ struct DisHandle {
 
   int check_overflow() {
     if (!e.overflow) return DISB200_OK;
-    int v = 0;
-    CU(cudaMemcpy(&v, e.overflow, sizeof(int), cudaMemcpyDeviceToHost));
-    if (v > 0) {
-      cudaMemset(e.overflow, 0, sizeof(int));
-      return fail(DISB200_EUNSUPPORTED, "forward-backward merge: " + std::to_string(v) + " patches ended in one cell, capacity " + std::to_string(e.cell_cap));
+    for (int i = 0; i <= (int)extra.size(); ++i) {
+      Engine& E = sub(i);
+      int v = 0;
+      CU(cudaMemcpy(&v, E.overflow, sizeof(int), cudaMemcpyDeviceToHost));
+      if (v > 0) {
+        cudaMemset(E.overflow, 0, sizeof(int));
+        return fail(DISB200_EUNSUPPORTED, "forward-backward merge: " + std::to_string(v) + " patches ended in one cell, capacity " + std::to_string(E.cell_cap));
+      }
     }
     return DISB200_OK;
   }
@@ -426,7 +489,14 @@ int disb200_create(const DisParams* params, int w0, int h0, int max_batch, int d
   DisHandle* h = new DisHandle();
   int W, H;
   rc = disb200_padded_dims(w0, h0, params->sc_f, &W, &H, &h->padl, &h->padt);
-  if (!rc) rc = h->e.init(*params, W, H, max_batch, device);
+  h->max_batch = max_batch;
+  {
+    const char* ev = getenv("DISB200_STREAMS");
+    int want = ev ? atoi(ev) : 1;
+    h->nsub = std::max(1, std::min(std::min(want, 16), max_batch));
+  }
+  h->cap = (max_batch + h->nsub - 1) / h->nsub;
+  if (!rc) rc = h->e.init(*params, W, H, h->cap, device);
   if (!rc) {
     h->w0 = w0; h->h0 = h0;
     h->in_bytes = (size_t)w0 * h0 * params->channels;
@@ -447,6 +517,9 @@ int disb200_destroy(DisHandle* h) {
     for (int k = 0; k < 2; ++k) { cudaEventDestroy(h->ev_h2d[k]); cudaEventDestroy(h->ev_comp[k]); cudaEventDestroy(h->ev_d2h[k]); }
   if (h->t0) cudaEventDestroy(h->t0);
   if (h->t1) cudaEventDestroy(h->t1);
+  if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+  for (cudaEvent_t ev : h->ev_join) cudaEventDestroy(ev);
+  for (Engine* x : h->extra) { x->destroy(); delete x; }
   h->e.destroy();
   delete h;
   return DISB200_OK;
@@ -454,7 +527,7 @@ int disb200_destroy(DisHandle* h) {
 
 int disb200_run_batch_device(DisHandle* h, const uint8_t* dA, const uint8_t* dB, int n, float* dOut) {
   if (!h || !dA || !dB || !dOut) return fail(DISB200_EINVAL, "null argument");
-  if (n < 1 || n > h->e.max_batch) return fail(DISB200_EINVAL, "n must be in 1..max_batch");
+  if (n < 1 || n > h->max_batch) return fail(DISB200_EINVAL, "n must be in 1..max_batch");
   CU(cudaSetDevice(h->e.device));
   h->e.begin_run();
   return h->enqueue(dA, dB, n, dOut);
@@ -475,7 +548,7 @@ int disb200_run_batch_host(DisHandle* h, const uint8_t* A, const uint8_t* B, int
   int rc = h->ensure_staging();
   if (rc) return rc;
   h->e.begin_run();
-  const int mb = h->e.max_batch;
+  const int mb = h->max_batch;
   int k = 0;
   for (int i0 = 0; i0 < n; i0 += mb, ++k) {
     const int m = std::min(mb, n - i0), b = k & 1;
@@ -507,7 +580,7 @@ int disb200_run_batch(DisHandle* h, const uint8_t* const* imgA, const uint8_t* c
   int rc = h->ensure_staging();
   if (rc) return rc;
   h->e.begin_run();
-  const int mb = h->e.max_batch;
+  const int mb = h->max_batch;
   for (int i0 = 0; i0 < n; i0 += mb) {
     const int m = std::min(mb, n - i0);
     for (int i = 0; i < m; ++i) {
@@ -538,7 +611,7 @@ int disb200_timer_end(DisHandle* h, float* ms) {
   CU(cudaEventElapsedTime(ms, h->t0, h->t1));
   return DISB200_OK;
 }
-int disb200_last_launch_count(const DisHandle* h) { return h ? h->e.stats.launches : 0; }
+int disb200_last_launch_count(const DisHandle* h) { return h ? h->launches : 0; }
 int disb200_set_stage_timing(DisHandle* h, int on) {
   if (!h) return fail(DISB200_EINVAL, "null handle");
   h->e.stage_timing = on != 0;
@@ -552,10 +625,14 @@ int disb200_stage_ms(const DisHandle* h, int stage, float* ms) {
 
 int disb200_fetch(DisHandle* h, int kind, int which, int level, int pair, void* dst, size_t nbytes) {
   if (!h || !dst) return fail(DISB200_EINVAL, "null argument");
-  Engine& e = h->e;
-  if (pair < 0 || pair >= e.max_batch || which < 0 || which > 1) return fail(DISB200_EINVAL, "bad pair / which");
-  CU(cudaSetDevice(e.device));
-  CU(cudaStreamSynchronize(e.stream));
+  if (pair < 0 || pair >= h->max_batch || which < 0 || which > 1 || h->last_per < 1) return fail(DISB200_EINVAL, "bad pair / which");
+  int si = pair / h->last_per;
+  if (si > (int)h->extra.size()) return fail(DISB200_EINVAL, "pair was not part of the last run");
+  pair -= si * h->last_per;
+  if (h->e.stage_timing) si = 0;
+  CU(cudaSetDevice(h->e.device));
+  CU(cudaStreamSynchronize(h->e.stream));
+  Engine& e = h->sub(si);
   const void* src = nullptr;
   size_t bytes = 0;
   if (kind >= 0 && kind <= 3) {

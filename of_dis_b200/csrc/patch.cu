@@ -7,12 +7,16 @@
 //   getPatchStaticBil / LossComputeErrorImage                           (patch.cpp:221-273,346-413)
 // A sub-warp of G lanes owns one patch; value n of the patch (row-major, channels
 // interleaved) lives in lane n % G, slot n / G, so that a load instruction of the group
-// touches consecutive floats of the target image.  Template, gradients, the residual and
-// its weight stay in registers; reductions are xor-butterflies, which leave every lane with
-// the bit-identical sum, so all scalar state (p_iter, convergence flags) is replicated and
-// the loop is uniform inside a group.  Groups of one warp may need different trip counts
-// (min_iter < max_iter): the loop runs until every group of the warp has converged and
-// finished groups stop committing state.
+// touches consecutive floats of the target image.  When a patch row is exactly G values
+// (8x8 grey with G = 8) slot k is patch row k and the two lower bilinear taps of row k are
+// the two upper taps of row k+1, so each iteration loads 2 (PSZ + 1) values per lane instead
+// of 4 PSZ.  Template and gradients stay in registers; the residual is consumed on the fly
+// (its projections on the steepest-descent images and its weight sum are all the next
+// iteration needs) and the per-pixel weights are written once, by the evaluation that ends
+// the search.  Reductions are xor-butterflies, which leave every lane with the bit-identical
+// sum, so all scalar state is replicated and the loop is uniform inside a group.  Groups of
+// one warp may need different trip counts (min_iter < max_iter): the loop runs until every
+// group of the warp has converged and finished groups stop committing state.
 #include "dis_internal.h"
 
 namespace disb200 {
@@ -24,6 +28,21 @@ __device__ __forceinline__ float gsum(float v) {
   return v;
 }
 
+// LossComputeErrorImage for one value (patch.cpp:221-273): d = query - template
+template <int COST>
+__device__ __forceinline__ void loss(float d, float bsq, float bsq2, float& pd, float& pw) {
+  if (COST == 0) {          // L2, patch.cpp:228-241
+    pd = d;
+    pw = fabsf(d);
+  } else if (COST == 1) {   // L1, :242-257
+    pw = sqrtf(fabsf(d));
+    pd = copysignf(pw, d);
+  } else {                  // pseudo-Huber, :258-272
+    pw = sqrtf((sqrtf(1.0f + (d * d) / bsq) - 1.0f) * bsq2);
+    pd = copysignf(pw, d);
+  }
+}
+
 template <int PSZ, int C, int G, bool OF>
 __global__ void __launch_bounds__(128)
 patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
@@ -32,6 +51,8 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
   constexpr int ROWLEN = PSZ * C;
   constexpr int LB = -PSZ / 2;
   constexpr int NOP = OF ? 2 : 1;
+  constexpr bool FULL = (NV % G) == 0;       // every slot of every lane holds a value
+  constexpr bool ROWMAP = ROWLEN == G;       // slot k == patch row k
 
   const int lane = threadIdx.x % G;
   const int ip_raw = blockIdx.x * (blockDim.x / G) + threadIdx.x / G;
@@ -55,10 +76,10 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
 #pragma unroll
   for (int k = 0; k < VPL; ++k) {
     const int n = k * G + lane;
-    val[k] = n < NV;
+    val[k] = FULL || n < NV;
     const int nn = val[k] ? n : 0;
     const int row = nn / ROWLEN;
-    off[k] = row * rowstride + (nn - row * ROWLEN);
+    off[k] = ROWMAP ? k * rowstride + lane : row * rowstride + (nn - row * ROWLEN);
   }
 
   // ---- template, gradients, Hessian (patch.cpp:298-343, 69-86) ----
@@ -122,16 +143,20 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
   int cnt = 0;
   const bool start_ok = !(ptx < g.lb || pty < g.lb || ptx > g.ubw || pty > g.ubh);
   bool conv = !start_ok;
-
-  float pd[VPL], pw[VPL];
-#pragma unroll
-  for (int k = 0; k < VPL; ++k) { pd[k] = 0.f; pw[k] = 0.f; }
   float s0 = 0.f, s1 = 0.f;            // projections of the current residual on the sd images
+
+  const size_t pi = (size_t)pair * g.npatch + ip;
+  float* wout = a.pweight + pi * NV;
+  if (active && !start_ok) {
+    // pweight of a patch whose start is invalid is never written by the reference (patch.cpp:133-139);
+    // defined as 0
+#pragma unroll
+    for (int k = 0; k < VPL; ++k)
+      if (val[k]) wout[k * G + lane] = 0.f;
+  }
 
   const float bsq = o.normoutlier * o.normoutlier, bsq2 = bsq * 2.0f;
 
-  // One evaluation of OptimizeComputeErrImg at (ex, ey); `commit` selects whether this group
-  // still updates its state.  Returns through the captured variables.
   bool first = true;
   while (true) {
     const bool upd = first ? start_ok : !conv;
@@ -172,36 +197,44 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
     const float* qb = qimg + ((iy1 + g.pad + LB) * g.tw + (ix1 + g.pad + LB)) * C;
     float q[VPL];
     float qs = 0.f;
+    if (ROWMAP) {
+      const float* p = qb + lane;
+      float vc = __ldg(p - rowstride), vd = __ldg(p - rowstride - C);
 #pragma unroll
-    for (int k = 0; k < VPL; ++k) {
-      const float* p = qb + off[k];
-      const float va = __ldg(p), vb = __ldg(p - C), vc = __ldg(p - rowstride), vd = __ldg(p - rowstride - C);
-      q[k] = val[k] ? w0 * va + w1 * vb + w2 * vc + w3 * vd : 0.f;
-      qs += q[k];
+      for (int k = 0; k < VPL; ++k) {
+        const float va = __ldg(p + k * rowstride), vb = __ldg(p + k * rowstride - C);
+        q[k] = w0 * va + w1 * vb + w2 * vc + w3 * vd;
+        qs += q[k];
+        vc = va;
+        vd = vb;
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < VPL; ++k) {
+        const float* p = qb + off[k];
+        const float va = __ldg(p), vb = __ldg(p - C), vc = __ldg(p - rowstride), vd = __ldg(p - rowstride - C);
+        q[k] = val[k] ? w0 * va + w1 * vb + w2 * vc + w3 * vd : 0.f;
+        qs += q[k];
+      }
     }
     float m = 0.f;
     if (o.patnorm > 0) m = gsum<G>(qs) / (float)NV;
     float ns0 = 0.f, ns1 = 0.f, wsum = 0.f;
-    float npd[VPL], npw[VPL];
-#pragma unroll
-    for (int k = 0; k < VPL; ++k) {
-      const float d = (q[k] - m) - t[k];
-      float vpd, vpw;
-      if (o.costfct == 0) {                                         // patch.cpp:228-241
-        vpd = d; vpw = fabsf(d);
-      } else if (o.costfct == 1) {                                  // :242-257
-        vpw = sqrtf(fabsf(d));
-        vpd = copysignf(vpw, d);
-      } else {                                                      // :258-272
-        vpw = sqrtf((sqrtf(1.0f + (d * d) / bsq) - 1.0f) * bsq2);
-        vpd = copysignf(vpw, d);
-      }
-      if (!val[k]) { vpd = 0.f; vpw = 0.f; }
-      npd[k] = vpd; npw[k] = vpw;
-      ns0 += dx[k] * vpd;
-      if (OF) ns1 += dy[k] * vpd;
-      wsum += fabsf(vpw);
-    }
+    float npw[VPL];
+#define DISB200_RESIDUAL(COST)                                   \
+  _Pragma("unroll") for (int k = 0; k < VPL; ++k) {              \
+    float vpd, vpw;                                              \
+    loss<COST>((q[k] - m) - t[k], bsq, bsq2, vpd, vpw);          \
+    if (!FULL && !val[k]) { vpd = 0.f; vpw = 0.f; }              \
+    npw[k] = vpw;                                                \
+    ns0 += dx[k] * vpd;                                          \
+    if (OF) ns1 += dy[k] * vpd;                                  \
+    wsum += fabsf(vpw);                                          \
+  }
+    if (o.costfct == 0) { DISB200_RESIDUAL(0) }
+    else if (o.costfct == 1) { DISB200_RESIDUAL(1) }
+    else { DISB200_RESIDUAL(2) }
+#undef DISB200_RESIDUAL
     ns0 = gsum<G>(ns0);
     if (OF) ns1 = gsum<G>(ns1);
     wsum = gsum<G>(wsum);
@@ -218,26 +251,21 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
       mares = nmares;
       p0 = np0; p1 = np1; ptx = nptx; pty = npty; dp0 = ndp0; dp1 = ndp1; cnt = ncnt; conv = nconv;
       s0 = ns0; s1 = ns1;
+      if (nconv && active) {   // this evaluation is the patch's last one: its weights are the result
 #pragma unroll
-      for (int k = 0; k < VPL; ++k) { pd[k] = npd[k]; pw[k] = npw[k]; }
+        for (int k = 0; k < VPL; ++k)
+          if (val[k]) wout[k * G + lane] = npw[k];
+      }
     }
     first = false;
     if (!__any_sync(0xffffffffu, !conv)) break;
   }
 
-  if (active) {
-    const size_t pi = (size_t)pair * g.npatch + ip;
-    if (lane == 0) {
-      a.p_iter[pi * NOP] = p0;
-      if (OF) a.p_iter[pi * NOP + 1] = p1;
-      if (a.pt_iter) { a.pt_iter[pi * 2] = ptx; a.pt_iter[pi * 2 + 1] = pty; }
-    }
-    float* wout = a.pweight + pi * NV;
-#pragma unroll
-    for (int k = 0; k < VPL; ++k)
-      if (val[k]) wout[k * G + lane] = pw[k];
+  if (active && lane == 0) {
+    a.p_iter[pi * NOP] = p0;
+    if (OF) a.p_iter[pi * NOP + 1] = p1;
+    if (a.pt_iter) { a.pt_iter[pi * 2] = ptx; a.pt_iter[pi * 2 + 1] = pty; }
   }
-  (void)pd;
 }
 
 template <int PSZ, int C, int G>

@@ -15,6 +15,8 @@
 //   finish_kernel   flow += increment (with the DE sign clamp)         (refine_variational.cpp:208-227,301-323)
 // The planes read by the refinement are the unpadded interiors of the padded pyramid arrays,
 // addressed in place (the reference copies them out first, refine_variational.cpp:120-149).
+#include <cstdlib>
+
 #include "dis_internal.h"
 
 namespace disb200 {
@@ -560,6 +562,8 @@ __device__ __forceinline__ void sor_wavefront(float* du, const float4* cA, const
   }
 }
 
+#include "sor_lean.cuh"
+
 // General path: one CTA per frame pair, increment du in global memory.  When rows x sweeps
 // exceed the CTA, sweeps run one after another over row bands (same lexicographic order).
 template <bool OF>
@@ -669,7 +673,9 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
   float4* cB = reinterpret_cast<float4*>(vb.inv);
   const bool pipelined = g.h * p.tv_solverit <= 512;
   const size_t fused_smem = (size_t)g.w * g.h * (NOP + 1) * sizeof(float);
-  if (pipelined && fused_smem <= 100 * 1024) {
+  static const char* tv_path = getenv("DISB200_TV_PATH");   // experiment switch: "split" disables the fused kernel
+  const bool want_split = tv_path && tv_path[0] == 's';
+  if (!want_split && pipelined && fused_smem <= 100 * 1024) {
     int threads = ((g.h * p.tv_solverit + 31) / 32) * 32;
     if (threads < 256) threads = 256;
     cudaFuncSetAttribute(tv_fused_kernel<C, OF>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
@@ -683,11 +689,15 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
   cudaMemsetAsync(vb.du, 0, sizeof(float) * vb.plane_cap * NOP * n, st);
   int threads = pipelined ? g.h * p.tv_solverit : (g.h < 512 ? g.h : 512);
   threads = ((threads + 31) / 32) * 32;
+  const size_t lean_smem_bytes = ((size_t)(g.h + 2) * g.w + 4) * sizeof(float2);
+  const bool lean = OF && pipelined && (g.w % 4 == 0) && lean_smem_bytes <= 200 * 1024;
+  if (lean) cudaFuncSetAttribute(sor_lean_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   for (int it = 0; it < n_inner; ++it) {
     smooth_kernel2<OF><<<grd, blk, 0, st>>>(flow, vb.du, d, camlr, qa, it == 0, vb.smooth);
     system_kernel<C, OF><<<grd, blk, 0, st>>>(D, vb.mask, vb.smooth, flow, vb.du, d, hd3, hg3, cA, cB);
     if (ls->mark) ls->mark(ls->ctx, 5, 1);
-    sor_wavefront_kernel<OF><<<n, threads, 0, st>>>(vb.du, cA, cB, d, p.tv_solverit, p.tv_sor, pipelined ? 1 : 0);
+    if (lean) sor_lean_kernel<<<n, threads, lean_smem_bytes, st>>>(vb.du, cA, cB, d, p.tv_solverit, p.tv_sor);
+    else sor_wavefront_kernel<OF><<<n, threads, 0, st>>>(vb.du, cA, cB, d, p.tv_solverit, p.tv_sor, pipelined ? 1 : 0);
     if (ls->mark) ls->mark(ls->ctx, 5, 0);
     ls->launches += 3;
   }
