@@ -45,14 +45,21 @@ struct LaunchStats {
 // ---- stage 1: pyramid -------------------------------------------------------------------
 // u8 frames [n][h0][w0][C] -> padded level image of level `lvl` (2^lvl x 2^lvl box mean of
 // the replicate-padded frame), then Sobel/8 + border fill.  Exact for any lvl <= 8.
-void launch_downscale_u8(const uint8_t* frames, int n, int w0, int h0, int C, int padl, int padt, int lvl,
-                         const LevelGeom& g, float* img, cudaStream_t s, LaunchStats* st);
+struct PyrLevelPtrs {
+  float* img[2];   // [frame]: padded level arrays of frame A / B, [n][th][tw][C]
+  float* dx[2];
+  float* dy[2];
+};
+// Both frames per launch (blockIdx.z = 2 * pair + frame).
+void launch_downscale_u8(const uint8_t* framesA, const uint8_t* framesB, int n, int w0, int h0, int C, int padl,
+                         int padt, int lvl, const LevelGeom& g, float* imgA, float* imgB, cudaStream_t s,
+                         LaunchStats* st);
 // level image (padded array, interior valid) -> next coarser level image interior (2x2 mean)
-void launch_halve(const float* src, const LevelGeom& gs, float* dst, const LevelGeom& gd, int n, int C,
-                  cudaStream_t s, LaunchStats* st);
-// interior of img valid -> fill replicate border of img, write dx, dy (zero border)
-void launch_sobel_pad(float* img, float* dx, float* dy, const LevelGeom& g, int n, int C, cudaStream_t s,
-                      LaunchStats* st);
+void launch_halve(const float* srcA, const float* srcB, const LevelGeom& gs, float* dstA, float* dstB,
+                  const LevelGeom& gd, int n, int C, cudaStream_t s, LaunchStats* st);
+// interiors valid -> replicate borders of img, dx / dy (zero border), all levels in one launch
+void launch_sobel_pad_levels(const PyrLevelPtrs* lv, const LevelGeom* g, int nlev, int n, int C, cudaStream_t s,
+                             LaunchStats* st);
 
 // ---- stage 2: inverse search ------------------------------------------------------------
 struct PatchArgs {

@@ -248,14 +248,17 @@ struct Engine {
   // a1 + a2: u8 frames (device) -> padded pyramids of both frames
   void build_pyramids(const uint8_t* dA, const uint8_t* dB, int n, int w0, int h0, int padl, int padt) {
     StageScope sc(this, 0);
-    const uint8_t* fr[2] = {dA, dB};
-    for (int f = 0; f < 2; ++f) {
-      launch_downscale_u8(fr[f], n, w0, h0, C, padl, padt, p.sc_l, geom[p.sc_l], pyr[f][0][p.sc_l], stream, &stats);
-      for (int l = p.sc_l + 1; l <= p.sc_f; ++l)
-        launch_halve(pyr[f][0][l - 1], geom[l - 1], pyr[f][0][l], geom[l], n, C, stream, &stats);
-      for (int l = p.sc_l; l <= p.sc_f; ++l)
-        launch_sobel_pad(pyr[f][0][l], pyr[f][1][l], pyr[f][2][l], geom[l], n, C, stream, &stats);
+    launch_downscale_u8(dA, dB, n, w0, h0, C, padl, padt, p.sc_l, geom[p.sc_l], pyr[0][0][p.sc_l], pyr[1][0][p.sc_l], stream, &stats);
+    for (int l = p.sc_l + 1; l <= p.sc_f; ++l)
+      launch_halve(pyr[0][0][l - 1], pyr[1][0][l - 1], geom[l - 1], pyr[0][0][l], pyr[1][0][l], geom[l], n, C, stream, &stats);
+    PyrLevelPtrs lv[9];
+    LevelGeom gl[9];
+    int nlev = 0;
+    for (int l = p.sc_l; l <= p.sc_f; ++l, ++nlev) {
+      gl[nlev] = geom[l];
+      for (int f = 0; f < 2; ++f) { lv[nlev].img[f] = pyr[f][0][l]; lv[nlev].dx[f] = pyr[f][1][l]; lv[nlev].dy[f] = pyr[f][2][l]; }
     }
+    launch_sobel_pad_levels(lv, gl, nlev, n, C, stream, &stats);
   }
 
   // The scale loop, oflow.cpp:182-330.  Result: flow[0][sc_l].

@@ -7,6 +7,8 @@
 // rationals below 2^24, l <= 8), so the finest level that is actually read (sc_l) is computed
 // straight from the u8 frame in one pass; levels 0..sc_l-1, which the reference builds but
 // never reads (oflow.cpp:182), are skipped.  Coarser levels come from the previous one.
+// Both frames of every pair go through the same launch (blockIdx.z = 2 * pair + frame) and
+// one launch computes the Sobel gradients and border fills of all levels.
 #include "dis_internal.h"
 
 namespace disb200 {
@@ -19,27 +21,41 @@ __device__ __forceinline__ int reflect101(int i, int n) {
   return clampi(i, 0, n - 1);
 }
 
-// One thread per (level pixel, channel).  Reads the replicate-padded u8 frame.
+// One thread per level pixel.  Reads the replicate-padded u8 frame; interior grey blocks whose
+// rows are 4-byte aligned are summed with 32-bit loads + dp4a, everything else byte by byte.
 template <int C>
-__global__ void downscale_u8_kernel(const uint8_t* __restrict__ frames, int w0, int h0, int padl, int padt,
-                                    int lvl, int w, int h, int pad, int tw, size_t img_elems,
-                                    float* __restrict__ img) {
+__global__ void __launch_bounds__(128)
+downscale_u8_kernel(const uint8_t* __restrict__ framesA, const uint8_t* __restrict__ framesB, int w0, int h0, int padl,
+                    int padt, int lvl, int w, int h, int pad, int tw, size_t img_elems, float* __restrict__ imgA,
+                    float* __restrict__ imgB) {
   const int x = blockIdx.x * blockDim.x + threadIdx.x;
   const int y = blockIdx.y;
-  const int pair = blockIdx.z;
+  const int pair = blockIdx.z >> 1, frame = blockIdx.z & 1;
   if (x >= w) return;
-  const uint8_t* f = frames + (size_t)pair * w0 * h0 * C;
+  const uint8_t* f = (frame ? framesB : framesA) + (size_t)pair * w0 * h0 * C;
+  float* img = frame ? imgB : imgA;
   const int k = 1 << lvl;
   unsigned sum[C];
 #pragma unroll
   for (int c = 0; c < C; ++c) sum[c] = 0;
-  for (int j = 0; j < k; ++j) {
-    const int sy = clampi(y * k + j - padt, 0, h0 - 1);
-    const uint8_t* row = f + (size_t)sy * w0 * C;
-    for (int i = 0; i < k; ++i) {
-      const int sx = clampi(x * k + i - padl, 0, w0 - 1);
+  const int xs = x * k - padl;   // first source column of the block
+  const bool fast = C == 1 && k >= 4 && xs >= 0 && xs + k <= w0 && ((xs & 3) == 0) && ((w0 & 3) == 0) &&
+                    ((((size_t)f) & 3) == 0);
+  if (fast) {
+    for (int j = 0; j < k; ++j) {
+      const int sy = clampi(y * k + j - padt, 0, h0 - 1);
+      const unsigned* row = reinterpret_cast<const unsigned*>(f + (size_t)sy * w0 + xs);
+      for (int i = 0; i < k / 4; ++i) sum[0] = __dp4a(__ldg(row + i), 0x01010101u, sum[0]);
+    }
+  } else {
+    for (int j = 0; j < k; ++j) {
+      const int sy = clampi(y * k + j - padt, 0, h0 - 1);
+      const uint8_t* row = f + (size_t)sy * w0 * C;
+      for (int i = 0; i < k; ++i) {
+        const int sx = clampi(xs + i, 0, w0 - 1);
 #pragma unroll
-      for (int c = 0; c < C; ++c) sum[c] += row[sx * C + c];
+        for (int c = 0; c < C; ++c) sum[c] += row[sx * C + c];
+      }
     }
   }
   const float inv = 1.0f / (float)(1u << (2 * lvl));
@@ -49,33 +65,47 @@ __global__ void downscale_u8_kernel(const uint8_t* __restrict__ frames, int w0, 
 }
 
 template <int C>
-__global__ void halve_kernel(const float* __restrict__ src, int stw, int spad, size_t s_elems, float* __restrict__ dst,
-                             int w, int h, int pad, int tw, size_t d_elems) {
+__global__ void halve_kernel(const float* __restrict__ srcA, const float* __restrict__ srcB, int stw, int spad,
+                             size_t s_elems, float* __restrict__ dstA, float* __restrict__ dstB, int w, int h, int pad,
+                             int tw, size_t d_elems) {
   const int x = blockIdx.x * blockDim.x + threadIdx.x;
   const int y = blockIdx.y;
-  const int pair = blockIdx.z;
+  const int pair = blockIdx.z >> 1, frame = blockIdx.z & 1;
   if (x >= w) return;
-  const float* s = src + (size_t)pair * s_elems;
-  float* o = dst + (size_t)pair * d_elems + ((size_t)(y + pad) * tw + (x + pad)) * C;
+  const float* s = (frame ? srcB : srcA) + (size_t)pair * s_elems;
+  float* o = (frame ? dstB : dstA) + (size_t)pair * d_elems + ((size_t)(y + pad) * tw + (x + pad)) * C;
   const float* r0 = s + ((size_t)(2 * y + spad) * stw + (2 * x + spad)) * C;
   const float* r1 = r0 + (size_t)stw * C;
 #pragma unroll
   for (int c = 0; c < C; ++c) o[c] = ((r0[c] + r0[C + c]) + (r1[c] + r1[C + c])) * 0.25f;
 }
 
-// One thread per padded pixel: replicate the image border, Sobel(k=3, 1/8, REFLECT_101) on the
-// unpadded level image for the interior of dx/dy, zeros on their border.
+struct SobelLevels {
+  int nlev;
+  int w[9], h[9], tw[9], th[9], row0[9];   // row0: first grid row of the level
+  size_t elems[9];
+  float* img[9][2];
+  float* dx[9][2];
+  float* dy[9][2];
+};
+
+// One thread per padded pixel of every level: replicate the image border, Sobel(k=3, 1/8,
+// REFLECT_101) on the unpadded level image for the interior of dx/dy, zeros on their border.
 template <int C>
-__global__ void sobel_pad_kernel(float* __restrict__ img, float* __restrict__ dx, float* __restrict__ dy, int w,
-                                 int h, int pad, int tw, int th, size_t elems) {
+__global__ void __launch_bounds__(128) sobel_pad_kernel(SobelLevels L, int pad) {
+  int lv = 0;
+#pragma unroll 1
+  while (lv + 1 < L.nlev && (int)blockIdx.y >= L.row0[lv + 1]) ++lv;
   const int x = blockIdx.x * blockDim.x + threadIdx.x;
-  const int y = blockIdx.y;
-  const int pair = blockIdx.z;
+  const int y = blockIdx.y - L.row0[lv];
+  const int pair = blockIdx.z >> 1, frame = blockIdx.z & 1;
+  const int w = L.w[lv], h = L.h[lv], tw = L.tw[lv];
   if (x >= tw) return;
-  float* I = img + (size_t)pair * elems;
+  const size_t elems = L.elems[lv];
+  float* I = L.img[lv][frame] + (size_t)pair * elems;
   const size_t o = ((size_t)y * tw + x) * C;
-  float* gx = dx + (size_t)pair * elems + o;
-  float* gy = dy + (size_t)pair * elems + o;
+  float* gx = L.dx[lv][frame] + (size_t)pair * elems + o;
+  float* gy = L.dy[lv][frame] + (size_t)pair * elems + o;
   const int sx = x - pad, sy = y - pad;
   const bool inside = sx >= 0 && sy >= 0 && sx < w && sy < h;
   if (!inside) {
@@ -104,33 +134,42 @@ __global__ void sobel_pad_kernel(float* __restrict__ img, float* __restrict__ dx
 #undef S
 }
 
-void launch_downscale_u8(const uint8_t* frames, int n, int w0, int h0, int C, int padl, int padt, int lvl,
-                         const LevelGeom& g, float* img, cudaStream_t s, LaunchStats* st) {
-  dim3 blk(128), grd((g.w + 127) / 128, g.h, n);
+void launch_downscale_u8(const uint8_t* framesA, const uint8_t* framesB, int n, int w0, int h0, int C, int padl,
+                         int padt, int lvl, const LevelGeom& g, float* imgA, float* imgB, cudaStream_t s,
+                         LaunchStats* st) {
+  dim3 blk(128), grd((g.w + 127) / 128, g.h, 2 * n);
   if (C == 1)
-    downscale_u8_kernel<1><<<grd, blk, 0, s>>>(frames, w0, h0, padl, padt, lvl, g.w, g.h, g.pad, g.tw, g.img_elems, img);
+    downscale_u8_kernel<1><<<grd, blk, 0, s>>>(framesA, framesB, w0, h0, padl, padt, lvl, g.w, g.h, g.pad, g.tw, g.img_elems, imgA, imgB);
   else
-    downscale_u8_kernel<3><<<grd, blk, 0, s>>>(frames, w0, h0, padl, padt, lvl, g.w, g.h, g.pad, g.tw, g.img_elems, img);
+    downscale_u8_kernel<3><<<grd, blk, 0, s>>>(framesA, framesB, w0, h0, padl, padt, lvl, g.w, g.h, g.pad, g.tw, g.img_elems, imgA, imgB);
   st->launches++;
 }
 
-void launch_halve(const float* src, const LevelGeom& gs, float* dst, const LevelGeom& gd, int n, int C,
-                  cudaStream_t s, LaunchStats* st) {
-  dim3 blk(128), grd((gd.w + 127) / 128, gd.h, n);
+void launch_halve(const float* srcA, const float* srcB, const LevelGeom& gs, float* dstA, float* dstB,
+                  const LevelGeom& gd, int n, int C, cudaStream_t s, LaunchStats* st) {
+  dim3 blk(128), grd((gd.w + 127) / 128, gd.h, 2 * n);
   if (C == 1)
-    halve_kernel<1><<<grd, blk, 0, s>>>(src, gs.tw, gs.pad, gs.img_elems, dst, gd.w, gd.h, gd.pad, gd.tw, gd.img_elems);
+    halve_kernel<1><<<grd, blk, 0, s>>>(srcA, srcB, gs.tw, gs.pad, gs.img_elems, dstA, dstB, gd.w, gd.h, gd.pad, gd.tw, gd.img_elems);
   else
-    halve_kernel<3><<<grd, blk, 0, s>>>(src, gs.tw, gs.pad, gs.img_elems, dst, gd.w, gd.h, gd.pad, gd.tw, gd.img_elems);
+    halve_kernel<3><<<grd, blk, 0, s>>>(srcA, srcB, gs.tw, gs.pad, gs.img_elems, dstA, dstB, gd.w, gd.h, gd.pad, gd.tw, gd.img_elems);
   st->launches++;
 }
 
-void launch_sobel_pad(float* img, float* dx, float* dy, const LevelGeom& g, int n, int C, cudaStream_t s,
-                      LaunchStats* st) {
-  dim3 blk(128), grd((g.tw + 127) / 128, g.th, n);
-  if (C == 1)
-    sobel_pad_kernel<1><<<grd, blk, 0, s>>>(img, dx, dy, g.w, g.h, g.pad, g.tw, g.th, g.img_elems);
-  else
-    sobel_pad_kernel<3><<<grd, blk, 0, s>>>(img, dx, dy, g.w, g.h, g.pad, g.tw, g.th, g.img_elems);
+void launch_sobel_pad_levels(const PyrLevelPtrs* lv, const LevelGeom* g, int nlev, int n, int C, cudaStream_t s,
+                             LaunchStats* st) {
+  SobelLevels L;
+  L.nlev = nlev;
+  int rows = 0, maxtw = 0;
+  for (int i = 0; i < nlev; ++i) {
+    L.w[i] = g[i].w; L.h[i] = g[i].h; L.tw[i] = g[i].tw; L.th[i] = g[i].th; L.elems[i] = g[i].img_elems;
+    L.row0[i] = rows;
+    rows += g[i].th;
+    maxtw = g[i].tw > maxtw ? g[i].tw : maxtw;
+    for (int f = 0; f < 2; ++f) { L.img[i][f] = lv[i].img[f]; L.dx[i][f] = lv[i].dx[f]; L.dy[i][f] = lv[i].dy[f]; }
+  }
+  dim3 blk(128), grd((maxtw + 127) / 128, rows, 2 * n);
+  if (C == 1) sobel_pad_kernel<1><<<grd, blk, 0, s>>>(L, g[0].pad);
+  else sobel_pad_kernel<3><<<grd, blk, 0, s>>>(L, g[0].pad);
   st->launches++;
 }
 

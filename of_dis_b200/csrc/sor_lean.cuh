@@ -13,6 +13,13 @@
 #ifndef DISB200_SOR_LEAN_CUH_
 #define DISB200_SOR_LEAN_CUH_
 
+#ifdef SOR_PROFILE
+__device__ long long g_sor_prof[8];
+#define SOR_PROF(k) if (blockIdx.x == 0 && threadIdx.x == 0) g_sor_prof[k] = clock64();
+#else
+#define SOR_PROF(k)
+#endif
+
 __device__ __forceinline__ float2 sor_update_lean(const float4 cA, const float4 cB, float hl, bool mid, bool first,
                                                   float omega, float2 left, float2 cur, float2 r, float2 t,
                                                   float2 bt) {
@@ -77,7 +84,9 @@ sor_lean_kernel(float* __restrict__ du_all, const float4* __restrict__ cA_all, c
   }
   float2 left = make_float2(0.f, 0.f);
   float hprev = 0.f;
+  SOR_PROF(0)
   __syncthreads();
+  SOR_PROF(1)
   for (int m0 = 0; m0 < nsteps; m0 += 2) {
 #pragma unroll
     for (int u = 0; u < 2; ++u) {
@@ -111,7 +120,9 @@ sor_lean_kernel(float* __restrict__ du_all, const float4* __restrict__ cA_all, c
       __syncthreads();
     }
   }
+  SOR_PROF(2)
   for (int k = tid; k < npix; k += T) gdu[k] = sdu[w + k];
+  SOR_PROF(3)
 }
 
 #endif
