@@ -409,10 +409,10 @@ struct DisHandle {
         E.begin_run();
         CU(cudaStreamWaitEvent(E.stream, ev_fork, 0));
       }
+      E.stats.launches = 0;
       int rc = enqueue_one(E, a + (size_t)lo * in_bytes, b + (size_t)lo * in_bytes, m, out + (size_t)lo * out_elems);
       if (rc) return rc;
-      if (i == 0 || !serial) launches += E.stats.launches;
-      if (serial) launches = e.stats.launches;
+      launches += E.stats.launches;     // kernels of this enqueue() call (all sub-batches)
       if (i > 0 && !serial) {
         CU(cudaEventRecord(ev_join[i - 1], E.stream));
         CU(cudaStreamWaitEvent(e.stream, ev_join[i - 1], 0));
@@ -551,8 +551,18 @@ int disb200_run_batch_host(DisHandle* h, const uint8_t* A, const uint8_t* B, int
   int rc = h->ensure_staging();
   if (rc) return rc;
   h->e.begin_run();
-  const int mb = h->max_batch;
+  // Chunks are pipelined over three streams (upload, compute, download) with two staging
+  // buffers, so the PCIe transfers of neighbouring chunks hide the compute and each other.
+  // About eight chunks per call keep the un-overlapped head (first upload + first compute)
+  // small; chunks below 16 pairs would starve the one-CTA-per-pair kernels.
+  int mb = h->max_batch;
+  {
+    static const char* ev = getenv("DISB200_HOST_CHUNK");
+    const int want = ev ? atoi(ev) : std::max(16, (n + 7) / 8);
+    mb = std::max(1, std::min(mb, want));
+  }
   int k = 0;
+  int total_launches = 0;
   for (int i0 = 0; i0 < n; i0 += mb, ++k) {
     const int m = std::min(mb, n - i0), b = k & 1;
     // input buffer b is free once the compute of chunk k-2 is done
@@ -565,6 +575,7 @@ int disb200_run_batch_host(DisHandle* h, const uint8_t* A, const uint8_t* B, int
     if (k >= 2) CU(cudaStreamWaitEvent(h->e.stream, h->ev_d2h[b], 0));
     rc = h->enqueue(h->dA[b], h->dB[b], m, h->dOut[b]);
     if (rc) return rc;
+    total_launches += h->launches;
     CU(cudaEventRecord(h->ev_comp[b], h->e.stream));
     CU(cudaStreamWaitEvent(h->s_d2h, h->ev_comp[b], 0));
     CU(cudaMemcpyAsync(out + (size_t)i0 * (h->out_bytes / sizeof(float)), h->dOut[b], h->out_bytes * m, cudaMemcpyDeviceToHost, h->s_d2h));
@@ -572,6 +583,7 @@ int disb200_run_batch_host(DisHandle* h, const uint8_t* A, const uint8_t* B, int
   }
   CU(cudaStreamSynchronize(h->s_d2h));
   CU(cudaStreamSynchronize(h->e.stream));
+  h->launches = total_launches;
   h->e.collect_stage_times();
   return h->check_overflow();
 }
@@ -584,6 +596,7 @@ int disb200_run_batch(DisHandle* h, const uint8_t* const* imgA, const uint8_t* c
   if (rc) return rc;
   h->e.begin_run();
   const int mb = h->max_batch;
+  int total_launches = 0;
   for (int i0 = 0; i0 < n; i0 += mb) {
     const int m = std::min(mb, n - i0);
     for (int i = 0; i < m; ++i) {
@@ -595,7 +608,9 @@ int disb200_run_batch(DisHandle* h, const uint8_t* const* imgA, const uint8_t* c
     for (int i = 0; i < m; ++i)
       CU(cudaMemcpyAsync(out[i0 + i], h->dOut[0] + (size_t)i * (h->out_bytes / sizeof(float)), h->out_bytes, cudaMemcpyDeviceToHost, h->e.stream));
     CU(cudaStreamSynchronize(h->e.stream));
+    total_launches += h->launches;
   }
+  h->launches = total_launches;
   h->e.collect_stage_times();
   return h->check_overflow();
 }

@@ -7,7 +7,7 @@
 // cpu_baseline / --impl reference legs may load it.
 //
 // Pinning: validated in this container (a) bit-for-bit against the reference's
-// own sources compiled unmodified into oracle/_ref (tests/test_oracle_vs_ref.py)
+// own sources compiled unmodified into oracle/_ref (tests/test_oracle_cpu.py)
 // and (b) for the OpenCV steps the reference delegates (resize, Sobel,
 // copyMakeBorder, final resize; run_dense.cpp:131-179,299-312,407-415) against
 // python-cv2 4.13 golden vectors in tests/golden/ (made by
