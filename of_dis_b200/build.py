@@ -40,7 +40,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     nvcc = _nvcc()
     objdir = os.path.join(HERE, "build")
     os.makedirs(objdir, exist_ok=True)
-    headers = [os.path.join(CSRC, "dis_internal.h"), os.path.join(HERE, "..", "include", "disb200.h")]
+    headers = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".h", ".cuh"))]
+    headers.append(os.path.join(HERE, "..", "include", "disb200.h"))
     logs = {}
 
     def compile_one(src):

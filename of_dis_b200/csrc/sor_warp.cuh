@@ -1,0 +1,276 @@
+// Single-warp lexicographic SOR for levels of up to 64 rows (included by varref.cu, inside its
+// namespaces).
+//
+// Same update order and fp32 operation order as sor_coupled / sor_coupled_slow_but_readable_DE
+// (solver.c:83-471).  Pixel (i, j) of sweep s needs (i-1, j), (i, j-1) of sweep s and (i+1, j),
+// (i, j+1) of sweep s-1, so at step t sweep s may process pixel  i = t - j - 2 s  of row j: every
+// dependency was produced at step t-1 or t-2.
+//
+// Mapping: ONE warp per frame pair, lane = row (NB = 2: rows `lane` and `lane + 32`), and the
+// NS sweeps are interleaved inside each thread, so one step is NB x NS independent pixel updates
+// per lane and nothing ever crosses a warp: the values a pixel needs from its neighbours at
+// step t are exactly the results the neighbouring lanes (or this lane's previous sweep)
+// produced at step t-1 / t-2, so they travel through warp shuffles and registers — no barrier,
+// no shared-memory round trip inside a step:
+//     left   (i-1, j  ) sweep s    own result of sweep s        at step t-1
+//     top    (i,   j-1) sweep s    lane-1's result of sweep s   at step t-1        (shfl up)
+//     right  (i+1, j  ) sweep s-1  own result of sweep s-1      at step t-1
+//     centre (i,   j  ) sweep s-1  own result of sweep s-1      at step t-2
+//     bottom (i,   j+1) sweep s-1  lane+1's result of sweep s-1 at step t-1        (shfl down)
+// Everything a row reads from memory — the two coefficient float4 of system_pixel and, for
+// sweep 0, the increment left by the previous fixed-point iteration — is a sequential stream
+// along the row that does not depend on the wavefront: each lane streams its row from global
+// memory into a private shared ring with cp.async, SORW_D pixels ahead, and moves the values of
+// the next step into registers one step early.  The last sweep stores the result in place,
+// always behind every location still to be read.  A warp needs 10-40 KB of shared memory and
+// no CTA-wide resource, so the SOR of thousands of frame pairs is resident at once and the
+// schedulers interleave them; throughput, not the dependency chain of one pair, sets the time.
+#ifndef DISB200_SOR_WARP_CUH_
+#define DISB200_SOR_WARP_CUH_
+
+// Row streams are cut into chunks of 8 pixels.  Chunk q of a row is requested when the row's
+// sweep-0 pixel reaches 8 q - LEADPX; at every step the rows that reach such a point are
+// j = (t + LEADPX) mod 8 + 8 g, four per band, so ONE cp.async per stream serves them all:
+// lane = 8 g + e copies pixel 8 q + e of row j — four fully used 128-byte segments per
+// instruction instead of 32 scattered sectors.  The owner lane of a row reads its pixels from
+// the row's ring of NCH chunks one step before use.
+template <int NS>
+struct SorwCfg {
+  static constexpr int H = 2 * (NS - 1);             // pixels the last sweep trails sweep 0
+  static constexpr int NCH = NS <= 3 ? 2 : 4;        // chunk slots per row
+  static constexpr int RPX = NCH * 8;                // ring pixels per row
+  static constexpr int LEADPX = NS <= 3 ? 4 : 8;     // request distance in pixels
+  static constexpr int WAITN = LEADPX - 2;           // cp.async groups that may stay in flight
+  static constexpr int BAND_BYTES = 32 * RPX * (16 + 16 + 8);
+};
+__host__ __device__ inline size_t sorw_smem_bytes(int h, int ns) {
+  return (size_t)((h + 31) / 32) * (ns <= 3 ? SorwCfg<3>::BAND_BYTES : SorwCfg<5>::BAND_BYTES);
+}
+
+__device__ __forceinline__ void sorw_cp16(unsigned smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_dst), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void sorw_cp8(unsigned smem_dst, const void* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(smem_dst), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void sorw_cp4(unsigned smem_dst, const void* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_dst), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ float4 sorw_lds128(unsigned addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+template <bool OF>
+__device__ __forceinline__ float2 sorw_lds_du(unsigned addr) {
+  float2 v = make_float2(0.f, 0.f);
+  if (OF) asm volatile("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
+  else asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v.x) : "r"(addr));
+  return v;
+}
+
+// One OF update, branch-free (selects on the per-lane row type); same values as the expression trees of
+// solver.c:122-141 (first row), :184-203 (middle rows), :244-262 (last row).
+__device__ __forceinline__ float2 sorw_update_of(const float4 cA, const float4 cB, float hl, bool mid, float omega, float2 left, float2 cur, float2 r, float2 t, float2 bt) {
+  const float hh = cA.x, vv = cA.y, vt = cA.z, i12 = cA.w, i11 = cB.x, i22 = cB.y, b1 = cB.z, b2 = cB.w;
+  // x = h*r, y = vt*t, z = v*bt;  middle: (x + y) + (b + z)   first: (b + x) + z   last: (b + x) + y
+  const float x1 = hh * r.x, x2 = hh * r.y, y1 = vt * t.x, y2 = vt * t.y, z1 = vv * bt.x, z2 = vv * bt.y;
+  // (b + x) == (x + b) bit for bit, and in the first / last row the absent term (y / z) is +-0 because its
+  // weight is 0, so  first: (x + b) + (y + z) == (b + x) + z  and  last: (x + b) + (y + z) == (b + x) + y
+  const float q1 = mid ? y1 : b1, q2 = mid ? y2 : b2;
+  const float e1 = (mid ? b1 : y1) + z1, e2 = (mid ? b2 : y2) + z2;
+  const float s1 = (x1 + q1) + e1, s2 = (x2 + q2) + e2;
+  const float B1 = hl * left.x + s1, B2 = hl * left.y + s2;
+  float2 nw;
+  nw.x = cur.x + omega * (i11 * B1 + i12 * B2 - cur.x);
+  nw.y = cur.y + omega * (i12 * B1 + i22 * B2 - cur.y);
+  return nw;
+}
+// One DE update (solver.c:446-467): sigma accumulates top, left, bottom, right; absent neighbours
+// have weight 0 and a finite value here, and x - 0*y == x bit for bit (sigma is never -0).
+__device__ __forceinline__ float sorw_update_de(const float4 cA, float b1, float hl, float omega, float left, float cur,
+                                                float r, float t, float bt) {
+  float sigma = 0.f;
+  sigma -= cA.z * t;
+  sigma -= hl * left;
+  sigma -= cA.y * bt;
+  sigma -= cA.x * r;
+  const float B1 = b1 - sigma;
+  return (1.0f - omega) * cur + omega * (B1 / cA.w);
+}
+
+template <bool OF>
+__device__ __forceinline__ float2 sorw_shfl(float2 v, int src) {
+  float2 r;
+  r.x = __shfl_sync(0xffffffffu, v.x, src);
+  r.y = OF ? __shfl_sync(0xffffffffu, v.y, src) : 0.f;
+  return r;
+}
+
+// du: global increment plane of this pair, [h][w] float2 (OF) / float (DE), updated in place.
+// smem: sorw_smem_bytes(h, NS) bytes owned by this warp.  cA / cB: global coefficient planes of
+// this pair (row stride w).  Called by exactly one full warp; h <= 32 * NB.
+template <bool OF, int NS, int NB>
+__device__ __forceinline__ void sor_warp(float* __restrict__ du, unsigned smem, const float4* __restrict__ cA,
+                                         const float4* __restrict__ cB, int w, int h, float omega) {
+  typedef SorwCfg<NS> Cfg;
+  constexpr int NOP = OF ? 2 : 1, RPX = Cfg::RPX, LEADPX = Cfg::LEADPX;
+  const int lane = threadIdx.x & 31;
+  const unsigned uw = (unsigned)w;
+  const int T = w + h - 1 + 2 * (NS - 1);
+  const int up = (lane + 31) & 31, dn = (lane + 1) & 31;
+  const int cg = lane >> 3, ce = lane & 7;           // cooperative copies: row group, pixel in chunk
+
+  int i0[NB];                  // pixel of sweep 0 at the current step (row j = b * 32 + lane)
+  bool mid[NB];
+  unsigned rA[NB], rD[NB];     // shared addresses of the rings of this lane's own row: cA (cB at + 32*RPX*16), du
+  float* gD[NB];               // &du[j][i0]
+  float2 R[NB][NS], R2[NB][NS];
+  float hp[NB][NS];
+  float4 a[NB][NS], c[NB][NS];
+  float2 cur0[NB], nr0[NB];
+#pragma unroll
+  for (int b = 0; b < NB; ++b) {
+    const int j = b * 32 + lane;
+    const bool row = j < h;
+    i0[b] = row ? -j : -(1 << 28);
+    mid[b] = j > 0 && j < h - 1;
+    rA[b] = smem + (unsigned)(b * Cfg::BAND_BYTES) + lane * (RPX * 16u);
+    rD[b] = smem + (unsigned)(b * Cfg::BAND_BYTES) + 32u * RPX * 32u + lane * (RPX * 8u);
+    const int jr = row ? j : 0;
+    gD[b] = du + ((size_t)jr * w - jr) * NOP;
+    cur0[b] = nr0[b] = make_float2(0.f, 0.f);
+#pragma unroll
+    for (int s = 0; s < NS; ++s) {
+      R[b][s] = R2[b][s] = make_float2(0.f, 0.f);
+      hp[b][s] = 0.f;
+      a[b][s] = c[b][s] = make_float4(0.f, 0.f, 0.f, 1.f);
+    }
+  }
+  // cooperative copy of chunk q of row `r` (of band b) — this lane moves pixel 8 q + ce
+  auto copy_chunk = [&](int b, int r, int q) {
+    const int j = b * 32 + r, px = 8 * q + ce;
+    if (q >= 0 && j < h && px < w) {
+      const size_t g = (size_t)j * w + px;
+      const unsigned slot = (unsigned)(r * RPX + (px & (RPX - 1)));
+      const unsigned base = smem + (unsigned)(b * Cfg::BAND_BYTES);
+      sorw_cp16(base + slot * 16u, cA + g);
+      sorw_cp16(base + 32u * RPX * 16u + slot * 16u, cB + g);
+      if (OF) sorw_cp8(base + 32u * RPX * 32u + slot * 8u, du + g * 2);
+      else sorw_cp4(base + 32u * RPX * 32u + slot * 8u, du + g);
+    }
+  };
+  // rows whose sweep-0 pixel is at a request point when the step counter is tn
+  auto request = [&](int tn, int qmin) {
+#pragma unroll
+    for (int b = 0; b < NB; ++b) {
+      const int r = ((tn + LEADPX) & 7) + 8 * cg;
+      const int q = (tn - (b * 32 + r) + LEADPX) >> 3;
+      if (q >= qmin) copy_chunk(b, r, q);
+    }
+  };
+  auto fetch = [&](int b) {                // registers of the step whose sweep-0 pixel is i0[b]
+#pragma unroll
+    for (int s = 0; s < NS; ++s) {
+      const int i = i0[b] - 2 * s;
+      if ((unsigned)i < uw) {
+        const unsigned sc = rA[b] + ((unsigned)i & (RPX - 1)) * 16u;
+        a[b][s] = sorw_lds128(sc);
+        c[b][s] = sorw_lds128(sc + 32u * RPX * 16u);
+      }
+    }
+    // sweep 0: right neighbour (j, i0 + 1); pixel 0 also seeds the centre carry
+    if ((unsigned)(i0[b] + 1) < uw) nr0[b] = sorw_lds_du<OF>(rD[b] + ((unsigned)(i0[b] + 1) & (RPX - 1)) * 8u);
+    if (i0[b] == 0) cur0[b] = sorw_lds_du<OF>(rD[b]);
+  };
+  // prologue: chunk 0 of every row, plus whatever is due at step 0
+#pragma unroll
+  for (int rr = 0; rr < 8; ++rr) {
+#pragma unroll
+    for (int b = 0; b < NB; ++b) copy_chunk(b, rr + 8 * cg, 0);
+  }
+  request(0, 1);
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  __syncwarp();
+#pragma unroll
+  for (int b = 0; b < NB; ++b) fetch(b);
+
+  for (int t = 0; t < T; ++t) {
+    // ---- neighbour exchange: results of step t-1 (sweep 0: the streamed increment) ----
+    float2 top[NB][NS], bot[NB][NS];
+#pragma unroll
+    for (int s = 0; s < NS; ++s) {
+#pragma unroll
+      for (int b = 0; b < NB; ++b) {
+        // top of row b*32+lane: lane-1 of the same band; lane 0 of band 1 takes row 31 (lane 31 of band 0)
+        float2 st = R[b][s];
+        if (NB == 2 && b == 1 && lane == 31) st = R[0][s];
+        top[b][s] = sorw_shfl<OF>(st, up);
+        // bottom: lane+1's previous sweep (sweep 0: its right neighbour, which is (i0, j+1))
+        float2 sb = s > 0 ? R[b][s - 1] : nr0[b];
+        if (NB == 2 && b == 0 && lane == 0) sb = s > 0 ? R[NB - 1][s - 1] : nr0[NB - 1];
+        bot[b][s] = sorw_shfl<OF>(sb, dn);
+      }
+    }
+    // ---- updates ----
+    float2 N[NB][NS];
+#pragma unroll
+    for (int b = 0; b < NB; ++b) {
+#pragma unroll
+      for (int s = 0; s < NS; ++s) {
+        const int i = i0[b] - 2 * s;
+        const bool act = (unsigned)i < uw;
+        const float2 cur = s == 0 ? cur0[b] : R2[b][s - 1];
+        const float2 right = s == 0 ? nr0[b] : R[b][s - 1];
+        float2 nw;
+        if (OF) {
+          nw = sorw_update_of(a[b][s], c[b][s], hp[b][s], mid[b], omega, R[b][s], cur, right, top[b][s],
+                              bot[b][s]);
+        } else {
+          nw.x = sorw_update_de(a[b][s], c[b][s].x, hp[b][s], omega, R[b][s].x, cur.x, right.x, top[b][s].x,
+                                bot[b][s].x);
+          nw.y = 0.f;
+        }
+        N[b][s] = act ? nw : R[b][s];
+        hp[b][s] = a[b][s].x;   // stale (zero before the row starts) when the pixel is out of range: multiplies a zero / unused left
+#ifdef SORW_NOSTORE
+        if (s == NS - 1 && act && nw.x == 123.456f) {
+#else
+        if (s == NS - 1 && act) {
+#endif
+          if (OF) *reinterpret_cast<float2*>(gD[b] - 4 * (NS - 1)) = nw;
+          else gD[b][-2 * (NS - 1)] = nw.x;
+        }
+      }
+    }
+    // ---- rotate, advance, stream pixel i0 + D, fetch the registers of step t+1 ----
+#pragma unroll
+    for (int b = 0; b < NB; ++b) {
+#pragma unroll
+      for (int s = 0; s < NS; ++s) { R2[b][s] = R[b][s]; R[b][s] = N[b][s]; }
+      if ((unsigned)(i0[b] + 1) < uw) cur0[b] = nr0[b];   // centre of the next pixel = this step's right neighbour
+      ++i0[b]; gD[b] += NOP;
+    }
+    request(t + 1, 1);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group %0;" ::"n"(Cfg::WAITN) : "memory");
+    __syncwarp();
+#pragma unroll
+    for (int b = 0; b < NB; ++b) fetch(b);
+  }
+}
+
+// One warp (= one CTA) per frame pair.
+template <bool OF, int NS, int NB>
+__global__ void __launch_bounds__(32)
+sor_warp_kernel(float* __restrict__ du_all, const float4* __restrict__ cA_all, const float4* __restrict__ cB_all, Dims d,
+                float omega) {
+  extern __shared__ float4 sorw_smem[];
+  constexpr int NOP = OF ? 2 : 1;
+  const int pair = blockIdx.x;
+  sor_warp<OF, NS, NB>(du_all + (size_t)pair * d.plane * NOP, (unsigned)__cvta_generic_to_shared(sorw_smem),
+                       cA_all + (size_t)pair * d.plane, cB_all + (size_t)pair * d.plane, d.w, d.h, omega);
+}
+
+#endif

@@ -47,8 +47,8 @@ template <int C, bool OF>
 __global__ void warp_kernel(const float* __restrict__ im_a, const float* __restrict__ im_b,
                             const float* __restrict__ flow, Dims d, float* __restrict__ avg,
                             float* __restrict__ Iz, float* __restrict__ mask) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y, pair = blockIdx.z;
-  if (i >= d.w) return;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y, pair = blockIdx.z;
+  if (i >= d.w || j >= d.h) return;
   constexpr int NOP = OF ? 2 : 1;
   const size_t pix = (size_t)j * d.w + i;
   const float* fl = flow + ((size_t)pair * d.w * d.h + pix) * NOP;
@@ -87,8 +87,8 @@ __device__ __forceinline__ float conv5v(const float* p, int i, int j, int w, int
 __global__ void deriv1_kernel(const float* __restrict__ avg, const float* __restrict__ Iz, Dims d,
                               float* __restrict__ Ix, float* __restrict__ Iy, float* __restrict__ Ixz,
                               float* __restrict__ Iyz) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
-  if (i >= d.w) return;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y;
+  if (i >= d.w || j >= d.h) return;
   const size_t po = (size_t)blockIdx.z * d.plane, pix = (size_t)j * d.w + i;
   Ix[po + pix] = conv5h(avg + po, i, j, d.w);
   Iy[po + pix] = conv5v(avg + po, i, j, d.w, d.h);
@@ -97,8 +97,8 @@ __global__ void deriv1_kernel(const float* __restrict__ avg, const float* __rest
 }
 __global__ void deriv2_kernel(const float* __restrict__ Ix, const float* __restrict__ Iy, Dims d,
                               float* __restrict__ Ixx, float* __restrict__ Ixy, float* __restrict__ Iyy) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y;
-  if (i >= d.w) return;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y;
+  if (i >= d.w || j >= d.h) return;
   const size_t po = (size_t)blockIdx.z * d.plane, pix = (size_t)j * d.w + i;
   Ixx[po + pix] = conv5h(Ix + po, i, j, d.w);
   Ixy[po + pix] = conv5v(Ix + po, i, j, d.w, d.h);
@@ -124,8 +124,8 @@ __device__ __forceinline__ void load_uv(const float* flow, const float* du, size
 template <bool OF>
 __global__ void smooth_kernel(const float* __restrict__ flow, const float* __restrict__ du, Dims d, int camlr,
                               float quarter_alpha, int first_iter, float* __restrict__ s) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y, pair = blockIdx.z;
-  if (i >= d.w) return;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y, pair = blockIdx.z;
+  if (i >= d.w || j >= d.h) return;
   constexpr int NOP = OF ? 2 : 1;
   const float* fl = flow + (size_t)pair * d.w * d.h * NOP;
   const float* q = du + (size_t)pair * d.plane * NOP;
@@ -169,6 +169,10 @@ __device__ __forceinline__ void data_term_of(const DerivPtrs& D, size_t o, size_
                                              float& B2) {
 #define P(p, c) __ldg(D.p + o + (size_t)(c)*cstride)
   A11 = 0.f; A12 = 0.f; A22 = 0.f; B1 = 0.f; B2 = 0.f;
+  // mask == 0 (pixel warped out of the image): both robust weights are +0 and every term below is an exact
+  // +0.  Skipping them is bit-identical and keeps the zero numerators off the IEEE-division slow path, which
+  // a whole warp would take for one such lane.
+  if (m == 0.f) return;
   float tmp, tmp2, tmp3, tmpx, tmpy, tmpxy, n1, n2, n3 = 0.f, n4 = 0.f, n5 = 0.f, n6 = 0.f;
   if (hd3 != 0.f) {
     tmpx = P(Ix, 0); tmpy = P(Iy, 0);
@@ -261,6 +265,7 @@ __device__ __forceinline__ void data_term_de(const DerivPtrs& D, size_t o, size_
                                              float hd3, float hg3, float& A11, float& B1) {
 #define P(p, c) __ldg(D.p + o + (size_t)(c)*cstride)
   A11 = 0.f; B1 = 0.f;
+  if (m == 0.f) return;   // see data_term_of
   float tmp, tmp2, tmp3, tmpx, tmpy, tmpxy, n1, n2, n3 = 0.f, n4 = 0.f, n5 = 0.f, n6 = 0.f;
   if (hd3 != 0.f) {
     tmpx = P(Ix, 0); tmpy = P(Iy, 0);
@@ -400,8 +405,8 @@ template <int C, bool OF>
 __global__ void system_kernel(DerivPtrs D, const float* __restrict__ mask, const float* __restrict__ s,
                               const float* __restrict__ flow, const float* __restrict__ du, Dims d, float hd3,
                               float hg3, float4* __restrict__ cA, float4* __restrict__ cB) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y, pair = blockIdx.z;
-  if (i >= d.w) return;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y, pair = blockIdx.z;
+  if (i >= d.w || j >= d.h) return;
   constexpr int NOP = OF ? 2 : 1;
   const size_t po = (size_t)pair * d.plane;
   float4 a, b;
@@ -563,6 +568,7 @@ __device__ __forceinline__ void sor_wavefront(float* du, const float4* cA, const
 }
 
 #include "sor_lean.cuh"
+#include "sor_warp.cuh"
 
 // General path: one CTA per frame pair, increment du in global memory.  When rows x sweeps
 // exceed the CTA, sweeps run one after another over row bands (same lexicographic order).
@@ -587,8 +593,8 @@ sor_wavefront_kernel(float* du_all, const float4* __restrict__ cA_all, const flo
 template <bool OF>
 __global__ void smooth_kernel2(const float* __restrict__ flow, const float* __restrict__ du, Dims d, int camlr,
                                float quarter_alpha, int first_iter, float* __restrict__ s) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y, pair = blockIdx.z;
-  if (i >= d.w) return;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y, pair = blockIdx.z;
+  if (i >= d.w || j >= d.h) return;
   constexpr int NOP = OF ? 2 : 1;
   s[(size_t)pair * d.plane + (size_t)j * d.w + i] =
       smooth_pixel<OF>(flow + (size_t)pair * d.w * d.h * NOP, du + (size_t)pair * d.plane * NOP, i, j, d.w, d.h, camlr,
@@ -597,8 +603,8 @@ __global__ void smooth_kernel2(const float* __restrict__ flow, const float* __re
 
 template <bool OF>
 __global__ void finish_kernel(float* __restrict__ flow, const float* __restrict__ du, Dims d, int camlr) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y, pair = blockIdx.z;
-  if (i >= d.w) return;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y, pair = blockIdx.z;
+  if (i >= d.w || j >= d.h) return;
   constexpr int NOP = OF ? 2 : 1;
   const size_t pix = (size_t)j * d.w + i;
   float u, v;
@@ -663,7 +669,8 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
   const int n_inner = p.tv_innerit * (g.level + 1);                       // refine_variational.cpp:36
   if (n_inner <= 0) return;
   const float qa = 0.25f * p.tv_alpha, hg3 = p.tv_gamma * 0.5f / 3.0f, hd3 = p.tv_delta * 0.5f / 3.0f;
-  dim3 blk(128), grd((g.w + 127) / 128, g.h, n), grdc((g.w + 127) / 128, g.h, n * C);
+  // 32 x 4 pixel tiles: every warp of a block is a full row segment at all level widths
+  dim3 blk(32, 4), grd((g.w + 31) / 32, (g.h + 3) / 4, n), grdc((g.w + 31) / 32, (g.h + 3) / 4, n * C);
   warp_kernel<C, OF><<<grd, blk, 0, st>>>(im_a, im_b, flow, d, vb.avg, vb.Iz, vb.mask);
   deriv1_kernel<<<grdc, blk, 0, st>>>(vb.avg, vb.Iz, d, vb.Ix, vb.Iy, vb.Ixz, vb.Iyz);
   deriv2_kernel<<<grdc, blk, 0, st>>>(vb.Ix, vb.Iy, d, vb.Ixx, vb.Ixy, vb.Iyy);
@@ -673,8 +680,11 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
   float4* cB = reinterpret_cast<float4*>(vb.inv);
   const bool pipelined = g.h * p.tv_solverit <= 512;
   const size_t fused_smem = (size_t)g.w * g.h * (NOP + 1) * sizeof(float);
-  static const char* tv_path = getenv("DISB200_TV_PATH");   // experiment switch: "split" disables the fused kernel
-  const bool want_split = tv_path && tv_path[0] == 's';
+  const char* tv_path = getenv("DISB200_TV_PATH");   // experiment / test switch, see below
+  // "fused": one CTA per pair runs the whole level (best latency while every pair of the batch is resident,
+  // i.e. up to two CTAs per SM); larger batches take the split path, whose one-warp-per-pair SOR keeps
+  // thousands of pairs resident.  DISB200_TV_PATH = fused | split | old (general wavefront SOR) overrides.
+  const bool want_split = tv_path ? tv_path[0] != 'f' : n > 2 * 148;
   if (!want_split && pipelined && fused_smem <= 100 * 1024) {
     int threads = ((g.h * p.tv_solverit + 31) / 32) * 32;
     if (threads < 256) threads = 256;
@@ -687,16 +697,26 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
     return;
   }
   cudaMemsetAsync(vb.du, 0, sizeof(float) * vb.plane_cap * NOP * n, st);
+  // SOR launcher: one warp per pair (levels of up to 64 rows, up to 5 sweeps), else the general wavefront
+  void (*sorw)(float*, const float4*, const float4*, Dims, float) = nullptr;
+  if (g.h <= 64 && !(tv_path && tv_path[0] == 'o')) {
+    const bool two = g.h > 32;
+    switch (p.tv_solverit) {
+#define DISB200_SORW_CASE(NS_) case NS_: sorw = two ? sor_warp_kernel<OF, NS_, 2> : sor_warp_kernel<OF, NS_, 1>; break;
+      DISB200_SORW_CASE(1) DISB200_SORW_CASE(2) DISB200_SORW_CASE(3) DISB200_SORW_CASE(4) DISB200_SORW_CASE(5)
+#undef DISB200_SORW_CASE
+      default: break;
+    }
+  }
+  const size_t sorw_smem = sorw_smem_bytes(g.h, p.tv_solverit);
+  if (sorw) cudaFuncSetAttribute(sorw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sorw_smem);
   int threads = pipelined ? g.h * p.tv_solverit : (g.h < 512 ? g.h : 512);
   threads = ((threads + 31) / 32) * 32;
-  const size_t lean_smem_bytes = ((size_t)(g.h + 2) * g.w + 4) * sizeof(float2);
-  const bool lean = OF && pipelined && (g.w % 4 == 0) && lean_smem_bytes <= 200 * 1024;
-  if (lean) cudaFuncSetAttribute(sor_lean_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   for (int it = 0; it < n_inner; ++it) {
     smooth_kernel2<OF><<<grd, blk, 0, st>>>(flow, vb.du, d, camlr, qa, it == 0, vb.smooth);
     system_kernel<C, OF><<<grd, blk, 0, st>>>(D, vb.mask, vb.smooth, flow, vb.du, d, hd3, hg3, cA, cB);
     if (ls->mark) ls->mark(ls->ctx, 5, 1);
-    if (lean) sor_lean_kernel<<<n, threads, lean_smem_bytes, st>>>(vb.du, cA, cB, d, p.tv_solverit, p.tv_sor);
+    if (sorw) sorw<<<n, 32, sorw_smem, st>>>(vb.du, cA, cB, d, p.tv_sor);
     else sor_wavefront_kernel<OF><<<n, threads, 0, st>>>(vb.du, cA, cB, d, p.tv_solverit, p.tv_sor, pipelined ? 1 : 0);
     if (ls->mark) ls->mark(ls->ctx, 5, 0);
     ls->launches += 3;

@@ -30,17 +30,19 @@ int main(int argc,char**argv){
     cudaEvent_t e0,e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
     float ms1=0,ms2=0,ms3=0; const int reps=20;
     float* du3; CK(cudaMalloc(&du3,sizeof(float)*2*plane*np));
-    const int G=(h+31)/32; const int fthreads=32*iters*G; const size_t fsmem=smem+32*sizeof(int);
-    for(int v=0;v<2;++v){
+    const int G=(h+31)/32; const int rthreads=32*iters*G<128?128:32*iters*G; const size_t rsmem=((sorr_du_elems(w,h)*2+3)&~3ull)*4+sorr_ring_bytes(h,3);
+    CK(cudaFuncSetAttribute(sor_rows_kernel<true,3>,cudaFuncAttributeMaxDynamicSharedMemorySize,200*1024));
+    for(int v=0;v<3;++v){
       float* du=v==0?du1:(v==1?du2:du3);
       for(int rep=-3;rep<reps;++rep){
         if(rep<=0){ CK(cudaMemset(du,0,sizeof(float)*2*plane*np)); }
         if(rep==0) cudaEventRecord(e0);
         if(v==0) sor_wavefront_kernel<true><<<np,threads>>>(du,dA,dB,d,iters,omega,1);
-        else sor_lean_kernel<<<np,threads,smem>>>(du,dA,dB,d,iters,omega);
+        else if(v==1) sor_lean_kernel<<<np,threads,smem>>>(du,dA,dB,d,iters,omega);
+        else sor_rows_kernel<true,3><<<np,rthreads,rsmem>>>(du,dA,dB,d,omega);
       }
       cudaEventRecord(e1); CK(cudaEventSynchronize(e1)); float ms; cudaEventElapsedTime(&ms,e0,e1);
-      if(v>0){ long long pr[8]; cudaMemcpyFromSymbol(pr,g_sor_prof,sizeof(pr)); printf("   v%d: prologue-sync %lld  loop %lld cycles (%.0f per step)  epilogue %lld\n",v,pr[1]-pr[0],pr[2]-pr[1],(double)(pr[2]-pr[1])/(v==1?(w/4+h-1+4):(w+ (h<32?h:32) -1)),pr[3]-pr[2]); } (v==0?ms1:(v==1?ms2:ms3))=ms/reps;
+      if(v==1){ long long pr[8]; cudaMemcpyFromSymbol(pr,g_sor_prof,sizeof(pr)); printf("   v%d: prologue-sync %lld  loop %lld cycles (%.0f per step)  epilogue %lld\n",v,pr[1]-pr[0],pr[2]-pr[1],(double)(pr[2]-pr[1])/(v==1?(w/4+h-1+4):(w+ (h<32?h:32) -1)),pr[3]-pr[2]); } (v==0?ms1:(v==1?ms2:ms3))=ms/reps;
       CK(cudaGetLastError());
     }
     // compare after identical number of calls
@@ -48,8 +50,9 @@ int main(int argc,char**argv){
     CK(cudaMemcpy(r1.data(),du1,r1.size()*4,cudaMemcpyDeviceToHost)); CK(cudaMemcpy(r2.data(),du2,r2.size()*4,cudaMemcpyDeviceToHost));
     std::vector<float> r3(2*plane*np); CK(cudaMemcpy(r3.data(),du3,r3.size()*4,cudaMemcpyDeviceToHost));
     size_t nd=0; double md=0; for(size_t k=0;k<r1.size();++k){ if(r1[k]!=r2[k]){++nd; md=fmax(md,fabs(r1[k]-r2[k]));} }
+    size_t nd3=0; for(size_t k=0;k<r1.size();++k) if(r1[k]!=r3[k]) ++nd3;
     int nchunks=w/4; int steps=nchunks+h-1+2*(iters-1);
-    printf("pairs %4d  %3dx%2d: general %.1f us  lean %.1f us (%d macro-steps, %.0f cycles/step @1.9GHz) flow %.1f us  mismatches %zu maxdiff %.3g  sample %.5f\n",np,w,h,ms1*1e3,ms2*1e3,steps,ms2*1e-3*1.9e9/steps,ms3*1e3,nd,md,r2[plane]);
+    printf("pairs %4d  %3dx%2d: general %.1f us  lean %.1f us (%d macro-steps, %.0f cycles/step @1.9GHz) rows %.1f us (%d steps, %.0f cycles/step)  mismatches lean %zu rows %zu maxdiff %.3g  sample %.5f\n",np,w,h,ms1*1e3,ms2*1e3,steps,ms2*1e-3*1.9e9/steps,ms3*1e3,w+h-1+4,ms3*1e-3*1.9e9/(w+h-1+4),nd,nd3,md,r2[plane]);
     cudaFree(dA);cudaFree(dB);cudaFree(du1);cudaFree(du2);cudaFree(du3);
   }
   return 0;
