@@ -163,7 +163,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--batch", type=int, default=256, help="frame pairs per step per GPU")
+    ap.add_argument("--batch", type=int, default=1480, help="frame pairs per step per GPU (1480 = 10 resident SOR warps on each of the 148 SMs)")
     ap.add_argument("--workload", default="C1", choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU baseline sample budget per thread")
@@ -184,7 +184,7 @@ def main():
     bytes_per_pair = 2 * w0 * h0 * ch + 4 * w0 * h0 * nop     # compulsory traffic of the whole path
     config = {"workload": "%s: %s, params %s" % (args.workload, desc, " ".join("%g" % v for v in p.cli_args())),
               "pairs_per_step_per_gpu": args.batch, "frame": [w0, h0, ch], "l2_policy": "inputs+outputs per step (%.0f MB) exceed the 126 MB L2" % (args.batch * bytes_per_pair / 1e6),
-              "sor": "lexicographic wavefront (parity mode)"}
+              "sor": "lexicographic wavefront (parity mode, bit-exact with solver.c sor_coupled)"}
 
     # ------------------------------------------------------------------ reference arm (CPU)
     if args.impl == "reference":
@@ -271,8 +271,24 @@ def main():
     W, H = hd.W, hd.H
     lv = [(W >> l, H >> l, l) for l in range(p.sc_l, p.sc_f + 1)]
     pad = p.patchsz
+    C_ = ch
+    steps_ = max(1, int(np.floor(np.float32(pad) * (np.float32(1) - np.float32(p.patove)))))
+    npatch = [int(np.ceil(w / steps_)) * int(np.ceil(h / steps_)) for w, h, _ in lv]
+    novals = C_ * pad * pad
+    ndir = 2 if p.usefbcon else 1
     alg = {
+        # read both u8 frames, write image + dx + dy of every level for both frames
         "pyramid": 2 * w0 * h0 * ch + sum(2 * 3 * 4 * ch * (w + 2 * pad) * (h + 2 * pad) for w, h, _ in lv),
+        # per level and direction: template image/dx/dy + target image once, per patch p_iter, pt_iter, weights out
+        "inverse_search": ndir * sum(4 * 4 * ch * (w + 2 * pad) * (h + 2 * pad) + npatch[k] * 4 * (nop + 2 + novals)
+                                     for k, (w, h, _) in enumerate(lv)),
+        # patch results in, dense flow out
+        "densify": sum(npatch[k] * 4 * (nop + novals) + 4 * nop * w * h for k, (w, h, _) in enumerate(lv)),
+        # warp + derivatives once per level (2 images + flow in, 9C+1 planes out), then per fixed-point iteration
+        # 8C derivative planes + mask + flow + increment in, diffusivity + two float4 coefficient packs out;
+        # finally flow + increment in, flow out
+        "varref_other": sum(4 * w * h * ((2 * ch + nop) + (9 * ch + 1) + p.tv_innerit * (l + 1) * ((8 * ch + 1 + 2 * nop + 1) + 1 + 8)
+                                         + 3 * nop) for w, h, l in lv) if p.usetvref else 0,
         "upsample": 4 * nop * lv[0][0] * lv[0][1] + 4 * nop * w0 * h0,
         # per sweep read 9 planes (a11 a12 a22 b1 b2 h v du dv), write 2 (DE: 5 + 1)
         "sor": sum(p.tv_innerit * (l + 1) * p.tv_solverit * (4 * w * h) * (11 if nop == 2 else 6) for w, h, l in lv) if p.usetvref else 0,

@@ -19,6 +19,9 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false",
     "-Xcompiler", "-fPIC", "-Xptxas", "-v",
 ]
+# Files whose results are compared with a tolerance (the inverse search differs from the CPU code by the
+# order of its reductions anyway) may contract a*b+c into FMA; everything bit-compared may not.
+FMA_OK = set()   # measured: FMA in patch.cu gains 2 % of that kernel; not worth the drift from the CPU code
 CLI_VARIANTS = {"run_OF_INT": (1, 1), "run_OF_RGB": (1, 3), "run_DE_INT": (2, 1), "run_DE_RGB": (2, 3)}
 
 
@@ -48,7 +51,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
         s = os.path.join(CSRC, src)
         o = os.path.join(objdir, src.replace(".cu", ".o"))
         if force or _stale(o, [s] + headers):
-            r = subprocess.run([nvcc] + NVCC_FLAGS + ["-c", s, "-o", o], capture_output=True, text=True)
+            flags = [f for f in NVCC_FLAGS if not (src in FMA_OK and f == "-fmad=false")]
+            r = subprocess.run([nvcc] + flags + ["-c", s, "-o", o], capture_output=True, text=True)
             logs[src] = r.stderr
             if r.returncode != 0:
                 raise RuntimeError("nvcc failed on %s:\n%s" % (src, r.stderr))

@@ -81,6 +81,7 @@ static int validate(const DisParams& p) {
   if (p.costfct != 0 && p.costfct != 1 && p.costfct != 2)
     return fail(DISB200_EUNSUPPORTED, "costfct must be 0 (L2), 1 (L1) or 2 (pseudo-Huber)");
   if (p.max_iter < 0 || p.min_iter < 0) return fail(DISB200_EINVAL, "iteration counts must be >= 0");
+  if (p.sor_mode != DISB200_SOR_LEXICOGRAPHIC && p.sor_mode != DISB200_SOR_REDBLACK) return fail(DISB200_EINVAL, "sor_mode must be 0 (lexicographic) or 1 (red-black)");
   if (p.usetvref && (p.tv_innerit < 0 || p.tv_solverit < 1)) return fail(DISB200_EINVAL, "tv_innerit >= 0 and tv_solverit >= 1 required");
   return DISB200_OK;
 }

@@ -162,12 +162,28 @@ struct DerivPtrs {
 #define EPSC (0.001f * 0.001f)
 #define EPSG (0.001f * 0.001f)
 
+// The eight derivative values of one pixel and channel, loaded up front so that all loads of a pixel
+// are in flight together.
+struct Deriv8 {
+  float Ix, Iy, Iz, Ixx, Ixy, Iyy, Ixz, Iyz;
+};
+template <int C>
+__device__ __forceinline__ void load_derivs(const DerivPtrs& D, size_t o, size_t cstride, Deriv8 (&dv)[C]) {
+#pragma unroll
+  for (int c = 0; c < C; ++c) {
+    const size_t k = o + (size_t)c * cstride;
+    dv[c].Ix = __ldg(D.Ix + k); dv[c].Iy = __ldg(D.Iy + k); dv[c].Iz = __ldg(D.Iz + k);
+    dv[c].Ixx = __ldg(D.Ixx + k); dv[c].Ixy = __ldg(D.Ixy + k); dv[c].Iyy = __ldg(D.Iyy + k);
+    dv[c].Ixz = __ldg(D.Ixz + k); dv[c].Iyz = __ldg(D.Iyz + k);
+  }
+}
+
 // compute_data (opticalflow_aux.c:409-594), one pixel.  P(plane, c) reads channel c.
 template <int C>
-__device__ __forceinline__ void data_term_of(const DerivPtrs& D, size_t o, size_t cstride, float m, float u, float v,
+__device__ __forceinline__ void data_term_of(const Deriv8 (&dv)[C], float m, float u, float v,
                                              float hd3, float hg3, float& A11, float& A12, float& A22, float& B1,
                                              float& B2) {
-#define P(p, c) __ldg(D.p + o + (size_t)(c)*cstride)
+#define P(p, c) dv[c].p
   A11 = 0.f; A12 = 0.f; A22 = 0.f; B1 = 0.f; B2 = 0.f;
   // mask == 0 (pixel warped out of the image): both robust weights are +0 and every term below is an exact
   // +0.  Skipping them is bit-identical and keeps the zero numerators off the IEEE-division slow path, which
@@ -261,9 +277,9 @@ __device__ __forceinline__ void data_term_of(const DerivPtrs& D, size_t o, size_
 
 // compute_data_DE (opticalflow_aux.c:602-747), one pixel
 template <int C>
-__device__ __forceinline__ void data_term_de(const DerivPtrs& D, size_t o, size_t cstride, float m, float u,
+__device__ __forceinline__ void data_term_de(const Deriv8 (&dv)[C], float m, float u,
                                              float hd3, float hg3, float& A11, float& B1) {
-#define P(p, c) __ldg(D.p + o + (size_t)(c)*cstride)
+#define P(p, c) dv[c].p
   A11 = 0.f; B1 = 0.f;
   if (m == 0.f) return;   // see data_term_of
   float tmp, tmp2, tmp3, tmpx, tmpy, tmpxy, n1, n2, n3 = 0.f, n4 = 0.f, n5 = 0.f, n6 = 0.f;
@@ -354,48 +370,58 @@ __device__ __forceinline__ void system_pixel(const DerivPtrs& D, const float* __
                                              float4& cB) {
   constexpr int NOP = OF ? 2 : 1;
   const int pix = j * w + i;
-  const float sc = sp[pix];
-  // smooth_horiz / smooth_vert (opticalflow_aux.c:161-184): h(i) = s(i)+s(i+1), 0 in the last column
-  const float hh = i < w - 1 ? sc + sp[pix + 1] : 0.f;
-  const float hl = i > 0 ? sp[pix - 1] + sc : 0.f;
-  const float vv = j < h - 1 ? sc + sp[pix + w] : 0.f;
-  const float vt = j > 0 ? sp[pix - w] + sc : 0.f;
+  // Every load of the pixel is issued before the first use (one exposed memory latency instead of one per
+  // branch).  Neighbours outside the image are clamped to the pixel itself and get weight 0, which adds the
+  // same +0 the reference's skipped branches do not add: x -+ 0 * (w - w) == x.
+  const bool hasl = i > 0, hasr = i < w - 1, hast = j > 0, hasb = j < h - 1;
+  const int pl = hasl ? pix - 1 : pix, pr = hasr ? pix + 1 : pix, pt = hast ? pix - w : pix, pb = hasb ? pix + w : pix;
+  Deriv8 dv[C];
+  load_derivs<C>(D, o + pix, cstride, dv);
   const float m = mask[pix];
+  const float sc = sp[pix], sl = sp[pl], sr = sp[pr], st = sp[pt], sb = sp[pb];
+  float wc[NOP], wl[NOP], wr[NOP], wt[NOP], wb[NOP], qc[NOP];
+  if (OF) {
+    const float2* f2 = reinterpret_cast<const float2*>(fl);
+    const float2 c2 = f2[pix], l2 = f2[pl], r2 = f2[pr], t2 = f2[pt], b2 = f2[pb];
+    const float2 q2 = reinterpret_cast<const float2*>(q)[pix];
+    wc[0] = c2.x; wc[NOP - 1] = c2.y; wl[0] = l2.x; wl[NOP - 1] = l2.y; wr[0] = r2.x; wr[NOP - 1] = r2.y;
+    wt[0] = t2.x; wt[NOP - 1] = t2.y; wb[0] = b2.x; wb[NOP - 1] = b2.y; qc[0] = q2.x; qc[NOP - 1] = q2.y;
+  } else {
+    wc[0] = fl[pix]; wl[0] = fl[pl]; wr[0] = fl[pr]; wt[0] = fl[pt]; wb[0] = fl[pb]; qc[0] = q[pix];
+  }
+  // smooth_horiz / smooth_vert (opticalflow_aux.c:161-184): h(i) = s(i)+s(i+1), 0 in the last column
+  const float hh = hasr ? sc + sr : 0.f;
+  const float hl = hasl ? sl + sc : 0.f;
+  const float vv = hasb ? sc + sb : 0.f;
+  const float vt = hast ? st + sc : 0.f;
   float b[NOP];
   float A11, A12 = 0.f, A22 = 0.f;
   if (OF) {
-    data_term_of<C>(D, o + pix, cstride, m, q[pix * NOP], q[pix * NOP + NOP - 1], hd3, hg3, A11, A12, A22, b[0], b[NOP - 1]);
+    data_term_of<C>(dv, m, qc[0], qc[NOP - 1], hd3, hg3, A11, A12, A22, b[0], b[NOP - 1]);
   } else {
-    data_term_de<C>(D, o + pix, cstride, m, q[pix], hd3, hg3, A11, b[0]);
+    data_term_de<C>(dv, m, qc[0], hd3, hg3, A11, b[0]);
   }
   // sub_laplacian (opticalflow_aux.c:194-223): b = (((b - t(i-1)) + t(i)) - tv(j-1)) + tv(j)
 #pragma unroll
   for (int k = 0; k < NOP; ++k) {
-    const float wc = fl[pix * NOP + k];
     float bb = b[k];
-    if (i > 0) bb -= hl * (wc - fl[(pix - 1) * NOP + k]);
-    if (i < w - 1) bb += hh * (fl[(pix + 1) * NOP + k] - wc);
-    if (j > 0) bb -= vt * (wc - fl[(pix - w) * NOP + k]);
-    if (j < h - 1) bb += vv * (fl[(pix + w) * NOP + k] - wc);
+    bb -= hl * (wc[k] - wl[k]);
+    bb += hh * (wr[k] - wc[k]);
+    bb -= vt * (wc[k] - wt[k]);
+    bb += vv * (wb[k] - wc[k]);
     b[k] = bb;
   }
   if (OF) {
     // solver.c:122-128,184,244
-    float dpsis;
-    if (j == 0) dpsis = hl + (hh + vv);
-    else if (j < h - 1) dpsis = (hl + hh) + (vt + vv);
-    else dpsis = hl + (hh + vt);
+    const float dfirst = hl + (hh + vv), dmid = (hl + hh) + (vt + vv), dlast = hl + (hh + vt);
+    const float dpsis = !hast ? dfirst : (hasb ? dmid : dlast);
     const float I11 = A22 + dpsis, I22 = A11 + dpsis;
     const float det = I11 * I22 - A12 * A12;
     cA = make_float4(hh, vv, vt, A12 / (0.f - det));
     cB = make_float4(I11 / det, I22 / det, b[0], b[NOP - 1]);
   } else {
-    // solver.c:447-465: sum_dpsis accumulates top, left, bottom, right
-    float sum = 0.f;
-    if (j > 0) sum += vt;
-    if (i > 0) sum += hl;
-    if (j < h - 1) sum += vv;
-    if (i < w - 1) sum += hh;
+    // solver.c:447-465: sum_dpsis accumulates top, left, bottom, right (absent ones are +0)
+    const float sum = (((0.f + vt) + hl) + vv) + hh;
     cA = make_float4(hh, vv, vt, A11 + sum);
     cB = make_float4(b[0], 0.f, 0.f, 0.f);
   }
@@ -590,6 +616,29 @@ sor_wavefront_kernel(float* du_all, const float4* __restrict__ cA_all, const flo
   }
 }
 
+// Red-black SOR (DISB200_SOR_REDBLACK): one thread per pixel of one colour ((i + j) & 1 == colour), same
+// per-pixel formulas as the lexicographic sweep but every neighbour is read at its current value.  Not the
+// reference's iteration order: results differ from solver.c (oracle/dis_oracle.cpp restates this order for
+// the tests) and are reported with their own EPE, never as the parity result.
+template <bool OF>
+__global__ void sor_redblack_kernel(float* __restrict__ du_all, const float4* __restrict__ cA_all,
+                                    const float4* __restrict__ cB_all, Dims d, float omega, int colour) {
+  constexpr int NOP = OF ? 2 : 1;
+  const int j = blockIdx.y * blockDim.y + threadIdx.y, pair = blockIdx.z;
+  const int i = 2 * (blockIdx.x * blockDim.x + threadIdx.x) + ((j + colour) & 1);
+  if (i >= d.w || j >= d.h) return;
+  const int w = d.w, h = d.h, pix = j * w + i;
+  float* du = du_all + (size_t)pair * d.plane * NOP;
+  const float4 cA = cA_all[(size_t)pair * d.plane + pix], cB = cB_all[(size_t)pair * d.plane + pix];
+  const float2 z = make_float2(0.f, 0.f);
+  const float2 cur = ld_du<OF>(du, pix);
+  const float2 left = i > 0 ? ld_du<OF>(du, pix - 1) : z, r = i < w - 1 ? ld_du<OF>(du, pix + 1) : z;
+  const float2 t = j > 0 ? ld_du<OF>(du, pix - w) : z, bt = j < h - 1 ? ld_du<OF>(du, pix + w) : z;
+  const float hl = i > 0 ? cA_all[(size_t)pair * d.plane + pix - 1].x : 0.f;
+  const int rowtype = j == 0 ? 0 : (j < h - 1 ? 1 : 2);
+  st_du<OF>(du, pix, sor_update<OF>(cA, cB, hl, i > 0, rowtype, omega, left, cur, r, t, bt));
+}
+
 template <bool OF>
 __global__ void smooth_kernel2(const float* __restrict__ flow, const float* __restrict__ du, Dims d, int camlr,
                                float quarter_alpha, int first_iter, float* __restrict__ s) {
@@ -684,7 +733,7 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
   // "fused": one CTA per pair runs the whole level (best latency while every pair of the batch is resident,
   // i.e. up to two CTAs per SM); larger batches take the split path, whose one-warp-per-pair SOR keeps
   // thousands of pairs resident.  DISB200_TV_PATH = fused | split | old (general wavefront SOR) overrides.
-  const bool want_split = tv_path ? tv_path[0] != 'f' : n > 2 * 148;
+  const bool want_split = p.sor_mode == DISB200_SOR_REDBLACK || (tv_path ? tv_path[0] != 'f' : n > 2 * 148);
   if (!want_split && pipelined && fused_smem <= 100 * 1024) {
     int threads = ((g.h * p.tv_solverit + 31) / 32) * 32;
     if (threads < 256) threads = 256;
@@ -716,7 +765,12 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
     smooth_kernel2<OF><<<grd, blk, 0, st>>>(flow, vb.du, d, camlr, qa, it == 0, vb.smooth);
     system_kernel<C, OF><<<grd, blk, 0, st>>>(D, vb.mask, vb.smooth, flow, vb.du, d, hd3, hg3, cA, cB);
     if (ls->mark) ls->mark(ls->ctx, 5, 1);
-    if (sorw) sorw<<<n, 32, sorw_smem, st>>>(vb.du, cA, cB, d, p.tv_sor);
+    if (p.sor_mode == DISB200_SOR_REDBLACK) {
+      dim3 rblk(32, 4), rgrd((g.w / 2 + 1 + 31) / 32, (g.h + 3) / 4, n);
+      for (int sw = 0; sw < 2 * p.tv_solverit; ++sw)
+        sor_redblack_kernel<OF><<<rgrd, rblk, 0, st>>>(vb.du, cA, cB, d, p.tv_sor, sw & 1);
+      ls->launches += 2 * p.tv_solverit - 1;
+    } else if (sorw) sorw<<<n, 32, sorw_smem, st>>>(vb.du, cA, cB, d, p.tv_sor);
     else sor_wavefront_kernel<OF><<<n, threads, 0, st>>>(vb.du, cA, cB, d, p.tv_solverit, p.tv_sor, pipelined ? 1 : 0);
     if (ls->mark) ls->mark(ls->ctx, 5, 0);
     ls->launches += 3;

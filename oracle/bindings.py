@@ -86,6 +86,10 @@ class Port:
         self.lib.orc_operating_point(op, width, mode, noc, C.byref(p))
         return p
 
+    def set_sor_order(self, order: int):
+        """0 = raster order (reference); 1 = red-black (restatement of the product's DISB200_SOR_REDBLACK)."""
+        self.lib.orc_set_sor_order(int(order))
+
     def pad_dims(self, w0, h0, sc_f):
         W, H, pl, pt = C.c_int(), C.c_int(), C.c_int(), C.c_int()
         self.lib.orc_pad_dims(w0, h0, sc_f, C.byref(W), C.byref(H), C.byref(pl), C.byref(pt))

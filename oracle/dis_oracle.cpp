@@ -840,6 +840,22 @@ void compute_data_DE(const Derivs& D, const Plane& mask, const Plane& du, float 
   }
 }
 
+// Pixel order of one SOR sweep.  0: raster order (the reference, solver.c).  1: red-black — NOT in the
+// reference; the restatement of the product's DISB200_SOR_REDBLACK mode (all pixels with even i + j, then all
+// with odd i + j, same update formulas), so that mode too has a CPU oracle.
+int g_sor_order = 0;
+template <class F>
+inline void sweep_pixels(int w, int h, F f) {
+  if (g_sor_order == 0) {
+    for (int j = 0; j < h; ++j)
+      for (int i = 0; i < w; ++i) f(i, j);
+  } else {
+    for (int colour = 0; colour < 2; ++colour)
+      for (int j = 0; j < h; ++j)
+        for (int i = (j + colour) & 1; i < w; i += 2) f(i, j);
+  }
+}
+
 // sor_coupled_slow_but_readable, solver.c:34-78 (used by sor_coupled for degenerate sizes, solver.c:86-89)
 void sor_readable(Plane& du, Plane& dv, const Plane& a11, const Plane& a12, const Plane& a22, const Plane& b1,
                   const Plane& b2, const Plane& sh, const Plane& sv, int iters, float omega) {
@@ -865,8 +881,7 @@ void sor_coupled(Plane& du, Plane& dv, Plane& a11, Plane& a12, Plane& a22, const
   const int w = du.w, h = du.h;
   if (w < 2 || h < 2 || iters < 1) { sor_readable(du, dv, a11, a12, a22, b1, b2, sh, sv, iters, omega); return; }
   for (int it = 0; it < iters; ++it)
-    for (int j = 0; j < h; ++j)
-      for (int i = 0; i < w; ++i) {
+    sweep_pixels(w, h, [&](int i, int j) {
         const float hl = i > 0 ? sh.at(i - 1, j) : 0.f;     // f1[0] = 0 (solver.c:102)
         const float hh = sh.at(i, j), vv = sv.at(i, j);      // 0 in last column / row by construction
         const float dur = i < w - 1 ? du.at(i + 1, j) : 0.f, dvr = i < w - 1 ? dv.at(i + 1, j) : 0.f;
@@ -900,15 +915,14 @@ void sor_coupled(Plane& du, Plane& dv, Plane& a11, Plane& a12, Plane& a22, const
         const float nv = dv.at(i, j) + omega * (a12.at(i, j) * B1 + a22.at(i, j) * B2 - dv.at(i, j));
         du.at(i, j) = nu;
         dv.at(i, j) = nv;
-      }
+      });
 }
 
 // a21  sor_coupled_slow_but_readable_DE, solver.c:439-471
 void sor_DE(Plane& du, const Plane& a11, const Plane& b1, const Plane& sh, const Plane& sv, int iters, float omega) {
   const int w = du.w, h = du.h;
   for (int it = 0; it < iters; ++it)
-    for (int j = 0; j < h; ++j)
-      for (int i = 0; i < w; ++i) {
+    sweep_pixels(w, h, [&](int i, int j) {
         float su = 0.f, sum = 0.f;
         if (j > 0) { su -= sv.at(i, j - 1) * du.at(i, j - 1); sum += sv.at(i, j - 1); }
         if (i > 0) { su -= sh.at(i - 1, j) * du.at(i - 1, j); sum += sh.at(i - 1, j); }
@@ -916,7 +930,7 @@ void sor_DE(Plane& du, const Plane& a11, const Plane& b1, const Plane& sh, const
         if (i < w - 1) { su -= sh.at(i, j) * du.at(i + 1, j); sum += sh.at(i, j); }
         float A11 = a11.at(i, j) + sum, B1 = b1.at(i, j) - su;
         du.at(i, j) = (1.0f - omega) * du.at(i, j) + omega * (B1 / A11);
-      }
+      });
 }
 
 // a13 + a22  VarRefClass ctor + RefLevelOF / RefLevelDE, refine_variational.cpp:25-116,153-342
@@ -1052,6 +1066,8 @@ void orc_operating_point(int op, int width, int mode, int noc, OrcParams* p) {
   }
 }
 
+// 0 raster order (reference), 1 red-black (product's throughput mode); process-global, tests reset it to 0
+void orc_set_sor_order(int order) { g_sor_order = order ? 1 : 0; }
 void orc_pad_dims(int w0, int h0, int sc_f, int* W, int* H, int* padl, int* padt) { pad_dims(w0, h0, sc_f, W, H, padl, padt); }
 
 // One padded pyramid level (img, dx, dy) from a u8 image; out arrays hold (h_l+2pad)*(w_l+2pad)*C floats.

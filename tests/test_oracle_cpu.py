@@ -259,3 +259,24 @@ def test_pair_sharding_world2_gloo(tmp_path, port):
                         "--master-addr", "127.0.0.1", "--master-port", "29741", str(script), ROOT],
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "OK" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
+
+
+def test_oracle_redblack_order_is_a_different_iterate_of_the_same_problem(port):
+    """orc_set_sor_order(1) restates the product's DISB200_SOR_REDBLACK schedule (not in the reference)."""
+    from of_dis_b200.synth import make_pair
+    from tests.helpers import base_orc
+    A, B, _ = make_pair(100, 160, seed=2)
+    q = base_orc(1, 1, sc_f=1, sc_l=1)
+    a, b = port.pyramid_level(A, 1, 1, 8)[0], port.pyramid_level(B, 1, 1, 8)[0]
+    fl = np.full((50, 80, 2), 0.25, np.float32)
+    lex = port.varref_level(q, a, b, 80, 50, 1, 0, fl)
+    try:
+        port.set_sor_order(1)
+        rb = port.varref_level(q, a, b, 80, 50, 1, 0, fl)
+        rb_many = port.varref_level(q.copy(tv_solverit=200), a, b, 80, 50, 1, 0, fl)
+    finally:
+        port.set_sor_order(0)
+    lex_many = port.varref_level(q.copy(tv_solverit=200), a, b, 80, 50, 1, 0, fl)
+    assert np.array_equal(lex, port.varref_level(q, a, b, 80, 50, 1, 0, fl))      # order was reset
+    assert not np.array_equal(rb, lex) and np.abs(rb - lex).mean() < 0.1
+    assert np.abs(rb_many - lex_many).max() < 5e-2                                  # both orders converge to one solution

@@ -90,6 +90,49 @@ def test_varref_tall_level_uses_band_mode(gpu, port):
     assert np.array_equal(gpu.varref_level(to_dis(gpu, q), a, b, 96, 400, 0, 0, fl), port.varref_level(q, a, b, 96, 400, 0, 0, fl))
 
 
+@pytest.mark.parametrize("mode,ch", [(1, 1), (1, 3), (2, 1), (2, 3)])
+@pytest.mark.parametrize("w0,h0,level,solverit", [(1024, 436, 3, 3), (500, 218, 2, 3), (260, 128, 1, 5), (250, 120, 2, 2)])
+def test_tv_paths_agree_bit_for_bit(gpu, port, monkeypatch, mode, ch, w0, h0, level, solverit):
+    """The three schedules of the lexicographic SOR — one CTA per pair (fused), one warp per pair with shuffles
+    and cp.async row streams (split, used for large batches), general wavefront (old) — are the same iteration."""
+    A, B, _ = make_pair(h0, w0, channels=ch, mode="OF" if mode == 1 else "DE", seed=5)
+    q = base_orc(mode, ch, sc_f=level, sc_l=level, tv_solverit=solverit)
+    W, H, _, _ = port.pad_dims(w0, h0, level)
+    a, b = port.pyramid_level(A, level, level, 8)[0], port.pyramid_level(B, level, level, 8)[0]
+    wl, hl = W >> level, H >> level
+    nop = 2 if mode == 1 else 1
+    fl = (np.random.default_rng(1).standard_normal((hl, wl, nop)) * 0.5).astype(np.float32)
+    if mode == 2:
+        fl = -np.abs(fl)
+    want = port.varref_level(q, a, b, wl, hl, level, 0, fl)
+    for path in ("fused", "split", "old"):
+        monkeypatch.setenv("DISB200_TV_PATH", path)
+        got = gpu.varref_level(to_dis(gpu, q), a, b, wl, hl, level, 0, fl)
+        assert np.array_equal(got, want), (path, float(np.abs(got - want).max()))
+
+
+@pytest.mark.parametrize("mode,ch", [(1, 1), (2, 1), (1, 3)])
+def test_varref_redblack_matches_its_oracle(gpu, port, mode, ch):
+    """DISB200_SOR_REDBLACK is not the reference's order; the oracle restates it (orc_set_sor_order)."""
+    w0, h0, level = 500, 218, 1
+    A, B, _ = make_pair(h0, w0, channels=ch, mode="OF" if mode == 1 else "DE", seed=3)
+    q = base_orc(mode, ch, sc_f=level, sc_l=level)
+    W, H, _, _ = port.pad_dims(w0, h0, level)
+    a, b = port.pyramid_level(A, level, level, 8)[0], port.pyramid_level(B, level, level, 8)[0]
+    wl, hl = W >> level, H >> level
+    fl = np.full((hl, wl, 2 if mode == 1 else 1), -0.4, np.float32)
+    lex = port.varref_level(q, a, b, wl, hl, level, 0, fl)
+    try:
+        port.set_sor_order(1)
+        want = port.varref_level(q, a, b, wl, hl, level, 0, fl)
+    finally:
+        port.set_sor_order(0)
+    got = gpu.varref_level(to_dis(gpu, q, sor_mode=1), a, b, wl, hl, level, 0, fl)
+    assert np.array_equal(got, want), float(np.abs(got - want).max())
+    assert not np.array_equal(want, lex)                      # a different iterate ...
+    assert np.abs(want - lex).mean() < 0.1                    # ... of the same problem
+
+
 # ------------------------------------------------------------------------------ OFClass level (drop-in boundary)
 @pytest.mark.parametrize("name", sorted(REF_CASES))
 def test_ofclass_against_reference_golden(gpu, port, ref_golden, name):
@@ -174,6 +217,49 @@ def test_run_list_and_chunking(gpu, port):
         assert epe(outs[i], port.run_dense(to_orc(p), As[i], Bs[i]))[0] <= MEAN_TOL
 
 
+def test_redblack_whole_path(gpu, port):
+    """Throughput mode end to end: its own EPE against the CPU reference and against the ground truth."""
+    A, B, gt = make_pair(436, 1024, seed=0)
+    p = gpu.operating_point(2, 1024).copy(verbosity=0)
+    want = port.run_dense(to_orc(p), A, B)
+    with gpu.Handle(p.copy(sor_mode=1), 1024, 436, 1) as hd:
+        out = hd.run_host(A[None], B[None])[0]
+    m, mx = epe(out, want)
+    print("red-black vs lexicographic CPU: mean %.4f max %.3f px; vs GT %.4f (CPU %.4f)" % (m, mx, epe(out, gt)[0], epe(want, gt)[0]))
+    assert 1e-4 < m < 0.15                                    # not the parity iterate, but the same flow
+    assert abs(epe(out, gt)[0] - epe(want, gt)[0]) < 0.05
+
+
+def test_cli_matches_library(gpu, tmp_path):
+    """run_OF_INT / run_DE_INT (reference argv grammar, PGM in, .flo / .pfm out) against the batch entry point."""
+    import subprocess
+    exe_dir = os.path.join(ROOT, "of_dis_b200", "bin")
+    for mode, exe, ext in ((1, "run_OF_INT", "flo"), (2, "run_DE_INT", "pfm")):
+        A, B, _ = make_pair(120, 200, mode="OF" if mode == 1 else "DE", seed=2)
+        for name, img in (("a.pgm", A), ("b.pgm", B)):
+            with open(tmp_path / name, "wb") as f:
+                f.write(b"P5\n200 120\n255\n" + img.tobytes())
+        out = tmp_path / ("out." + ext)
+        r = subprocess.run([os.path.join(exe_dir, exe), str(tmp_path / "a.pgm"), str(tmp_path / "b.pgm"), str(out), "2"],
+                           capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        assert "O.Flow Run-Time" in r.stdout
+        p = gpu.operating_point(2, 200, mode, 1)
+        with gpu.Handle(p, 200, 120, 1) as hd:
+            want = hd.run_host(A[None], B[None])[0]
+        raw = open(out, "rb").read()
+        if mode == 1:
+            assert raw[:4] == b"PIEH" and np.frombuffer(raw[4:12], np.int32).tolist() == [200, 120]
+            got = np.frombuffer(raw[12:], np.float32).reshape(120, 200, 2)
+        else:
+            hdr = b"Pf\n200 120\n-1.000000\n"
+            assert raw.startswith(hdr)
+            got = -np.frombuffer(raw[len(hdr):], np.float32).reshape(120, 200)[::-1, :, None]
+        assert np.array_equal(got, want)
+    # malformed argument lists are errors, not out-of-bounds reads (run_dense.cpp:272-292)
+    assert subprocess.run([os.path.join(exe_dir, "run_OF_INT"), "x", "y", "z", "1", "2", "3"], capture_output=True).returncode != 0
+
+
 def test_identical_frames_give_exactly_zero(gpu):
     A, _, _ = make_pair(218, 512, seed=1)
     p = gpu.operating_point(2, 512).copy(verbosity=0)
@@ -220,7 +306,7 @@ def test_full_batch_properties(gpu, port):
     """BASELINE.json configs[0] at the bench batch size: every copy of a pair gives the same bits,
     distinct pairs match the oracle, device-pointer and host-pointer entry points agree."""
     import torch
-    w0, h0, nb = 1024, 436, 256
+    w0, h0, nb = 1024, 436, 592    # > 2 x 148 pairs: takes the large-batch (one warp per pair) SOR schedule
     p = gpu.operating_point(2, w0).copy(verbosity=0)
     pairs = [make_pair(h0, w0, seed=s)[:2] for s in range(2)]
     A = np.stack([pairs[i % 2][0] for i in range(nb)])
