@@ -78,8 +78,8 @@ static int validate(const DisParams& p) {
   if (p.patove < 0.f || p.patove >= 1.f) return fail(DISB200_EINVAL, "patove must be in [0,1)");
   if (p.patchsz != 4 && p.patchsz != 8 && p.patchsz != 12 && p.patchsz != 16)
     return fail(DISB200_EUNSUPPORTED, "patch size must be one of 4, 8, 12, 16");
-  if (p.costfct != 0 && p.costfct != 1 && p.costfct != 2)
-    return fail(DISB200_EUNSUPPORTED, "costfct must be 0 (L2), 1 (L1) or 2 (pseudo-Huber)");
+  if (p.costfct != 0 && p.costfct != 1 && p.costfct != 2 && p.costfct != 10)
+    return fail(DISB200_EUNSUPPORTED, "costfct must be 0 (L2), 1 (L1), 2 (pseudo-Huber) or 10 (NCC)");
   if (p.max_iter < 0 || p.min_iter < 0) return fail(DISB200_EINVAL, "iteration counts must be >= 0");
   if (p.sor_mode != DISB200_SOR_LEXICOGRAPHIC && p.sor_mode != DISB200_SOR_REDBLACK) return fail(DISB200_EINVAL, "sor_mode must be 0 (lexicographic) or 1 (red-black)");
   if (p.usetvref && (p.tv_innerit < 0 || p.tv_solverit < 1)) return fail(DISB200_EINVAL, "tv_innerit >= 0 and tv_solverit >= 1 required");

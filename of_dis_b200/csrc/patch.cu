@@ -95,11 +95,19 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
       dy[k] = (OF && val[k]) ? __ldg(tdyp + base + off[k]) : 0.f;
       s += t[k];
     }
-    if (o.patnorm > 0) {
+    if (o.patnorm > 0 || o.costfct == 10) {
       const float m = gsum<G>(s) / (float)NV;
 #pragma unroll
       for (int k = 0; k < VPL; ++k) t[k] = val[k] ? t[k] - m : 0.f;
     }
+  }
+  // NCC (costfct 10; defined by this build, the reference has no branch for it: DESIGN.md "NCC"): |t^|
+  float tnorm = 0.f;
+  if (o.costfct == 10) {
+    float s2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) s2 += t[k] * t[k];
+    tnorm = sqrtf(gsum<G>(s2));
   }
   float H00 = 0.f, H01 = 0.f, H11 = 0.f;
 #pragma unroll
@@ -218,22 +226,31 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
       }
     }
     float m = 0.f;
-    if (o.patnorm > 0) m = gsum<G>(qs) / (float)NV;
+    if (o.patnorm > 0 || o.costfct == 10) m = gsum<G>(qs) / (float)NV;
     float ns0 = 0.f, ns1 = 0.f, wsum = 0.f;
     float npw[VPL];
-#define DISB200_RESIDUAL(COST)                                   \
+#define DISB200_RESIDUAL(COST, QV)                                 \
   _Pragma("unroll") for (int k = 0; k < VPL; ++k) {              \
     float vpd, vpw;                                              \
-    loss<COST>((q[k] - m) - t[k], bsq, bsq2, vpd, vpw);          \
+    loss<COST>(QV - t[k], bsq, bsq2, vpd, vpw);                  \
     if (!FULL && !val[k]) { vpd = 0.f; vpw = 0.f; }              \
     npw[k] = vpw;                                                \
     ns0 += dx[k] * vpd;                                          \
     if (OF) ns1 += dy[k] * vpd;                                  \
     wsum += fabsf(vpw);                                          \
   }
-    if (o.costfct == 0) { DISB200_RESIDUAL(0) }
-    else if (o.costfct == 1) { DISB200_RESIDUAL(1) }
-    else { DISB200_RESIDUAL(2) }
+    float qscale = 1.0f;
+    if (o.costfct == 10) {           // r = q^ * (|t^| / |q^|) - t^
+      float s2 = 0.f;
+#pragma unroll
+      for (int k = 0; k < VPL; ++k) s2 += val[k] ? (q[k] - m) * (q[k] - m) : 0.f;
+      const float qn = sqrtf(gsum<G>(s2));
+      qscale = qn > 0.f ? tnorm / qn : 0.f;
+    }
+    if (o.costfct == 0) { DISB200_RESIDUAL(0, (q[k] - m)) }
+    else if (o.costfct == 10) { DISB200_RESIDUAL(0, (q[k] - m) * qscale) }
+    else if (o.costfct == 1) { DISB200_RESIDUAL(1, (q[k] - m)) }
+    else { DISB200_RESIDUAL(2, (q[k] - m)) }
 #undef DISB200_RESIDUAL
     ns0 = gsum<G>(ns0);
     if (OF) ns1 = gsum<G>(ns1);

@@ -304,7 +304,7 @@ void patch_bilinear(const float* img, const Level& L, const Opt& o, float mx, fl
     const float* d = c - C;                                                // (x0, y0)
     for (int k = 0; k < o.psz * C; ++k) *t++ = we0 * a[k] + we1 * b[k] + we2 * c[k] + we3 * d[k];
   }
-  if (o.patnorm > 0) {                                                     // patch.cpp:411-412
+  if (o.patnorm > 0 || o.costfct == 10) {                                  // patch.cpp:411-412 (NCC: always)
     float m = packet_redux(o.novals, [out](size_t i) { return out[i]; }) / o.novals;
     for (int i = 0; i < o.novals; ++i) out[i] -= m;
   }
@@ -314,6 +314,21 @@ void patch_bilinear(const float* img, const Level& L, const Opt& o, float mx, fl
 void loss_error_image(const Opt& o, float* pdiff, float* pweight, const float* tmpl) {
   const int nblk = (o.novals / 4) * 4;
   const float bsq = o.normoutlier * o.normoutlier, bsq2 = bsq * 2.0f;
+  if (o.costfct == 10) {
+    // NCC.  NO REFERENCE SEMANTICS: README.md:79 advertises costfct 10 but LossComputeErrorImage has no branch
+    // for it (patch.cpp:228,242,258) and leaves pweight uninitialised.  This is the definition the product
+    // implements (DESIGN.md "NCC"): zero-mean patches, query rescaled to the template's norm,
+    //   r = q^ * (|t^| / |q^|) - t^ ,  pdiff = r,  pweight = |r|   (r = -t^ when the query is flat).
+    const float nt = std::sqrt(packet_redux(o.novals, [tmpl](size_t i) { return tmpl[i] * tmpl[i]; }));
+    const float nq = std::sqrt(packet_redux(o.novals, [pdiff](size_t i) { return pdiff[i] * pdiff[i]; }));
+    const float scale = nq > 0.f ? nt / nq : 0.f;
+    for (int i = 0; i < nblk; ++i) {
+      const float d = pdiff[i] * scale - tmpl[i];
+      pdiff[i] = d;
+      pweight[i] = std::fabs(d);
+    }
+    return;
+  }
   for (int i = 0; i < nblk; ++i) {
     float d = pdiff[i] - tmpl[i];
     if (o.costfct == 0) {
@@ -328,7 +343,7 @@ void loss_error_image(const Opt& o, float* pdiff, float* pweight, const float* t
       pweight[i] = w;
       pdiff[i] = std::signbit(d) ? -w : w;
     }
-    // any other costfct (README "10/NCC"): the reference has no branch; nothing is written.
+    // any other costfct: the reference has no branch; nothing is written.
   }
 }
 
@@ -352,7 +367,7 @@ void optimize_patch(Grid& g, int ip, const Level& L, const Opt& o, const float* 
         size_t idx = ((size_t)(py + j) * L.tmp_w + (px + i)) * C;
         for (int c = 0; c < C; ++c, ++n) { tmpl[n] = a[idx + c]; tdx[n] = adx[idx + c]; tdy[n] = ady[idx + c]; }
       }
-    if (o.patnorm > 0) {
+    if (o.patnorm > 0 || o.costfct == 10) {
       float m = packet_redux(nv, [tmpl](size_t i) { return tmpl[i]; }) / nv;
       for (int i = 0; i < nv; ++i) tmpl[i] -= m;
     }

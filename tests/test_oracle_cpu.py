@@ -175,7 +175,7 @@ def test_compute_entry_points_fail_loudly_without_gpu(dis):
 
 def test_invalid_parameters_are_rejected(dis):
     p = dis.operating_point(2, 256)
-    for kw in (dict(mode=3), dict(channels=2), dict(sc_l=4, sc_f=3), dict(patove=1.0), dict(patchsz=7), dict(costfct=10)):
+    for kw in (dict(mode=3), dict(channels=2), dict(sc_l=4, sc_f=3), dict(patove=1.0), dict(patchsz=7), dict(costfct=3), dict(sor_mode=2)):
         with pytest.raises(dis.DisError) as e:
             dis.Handle(p.copy(**kw), 256, 128, 1)
         assert e.value.code in (1, 4), kw
@@ -280,3 +280,17 @@ def test_oracle_redblack_order_is_a_different_iterate_of_the_same_problem(port):
     assert np.array_equal(lex, port.varref_level(q, a, b, 80, 50, 1, 0, fl))      # order was reset
     assert not np.array_equal(rb, lex) and np.abs(rb - lex).mean() < 0.1
     assert np.abs(rb_many - lex_many).max() < 5e-2                                  # both orders converge to one solution
+
+
+def test_oracle_ncc_definition(port):
+    """costfct 10 is defined by this build (no reference branch): deterministic, sane flow, insensitive to gain."""
+    from of_dis_b200.synth import make_pair
+    A, B, gt = make_pair(120, 256, seed=1)
+    q = port.operating_point(2, 256).copy(verbosity=0, costfct=10, usetvref=0)
+    f1, f2 = port.run_dense(q, A, B), port.run_dense(q, A, B)
+    assert np.array_equal(f1, f2)
+    e = np.sqrt(((f1 - gt) ** 2).sum(-1)).mean()
+    B2 = np.clip(B.astype(np.float32) * 0.7 + 20, 0, 255).astype(np.uint8)
+    e2 = np.sqrt(((port.run_dense(q, A, B2) - gt) ** 2).sum(-1)).mean()
+    e2_l2 = np.sqrt(((port.run_dense(q.copy(costfct=0), A, B2) - gt) ** 2).sum(-1)).mean()
+    assert e < 1.5 and e2 < e + 0.1 and e2 < e2_l2

@@ -175,6 +175,11 @@ CONFIGS = [
     ("of_int_l1", 1, 1, 2, 1024, 436, dict(costfct=1), MAX_TOL_FINE),
     ("of_int_huber", 1, 1, 2, 1024, 436, dict(costfct=2), MAX_TOL_FINE),
     ("of_int_fb", 1, 1, 2, 1024, 436, dict(usefbcon=1), MAX_TOL_FINE),
+    # NCC has no reference semantics: the oracle restates the definition of DESIGN.md "NCC"
+    ("of_int_ncc", 1, 1, 2, 1024, 436, dict(costfct=10), 0.05),
+    ("of_int_ncc_fb", 1, 1, 2, 640, 272, dict(costfct=10, usefbcon=1), 0.05),
+    ("of_rgb_l1_fb", 1, 3, 2, 640, 272, dict(costfct=1, usefbcon=1), 0.05),
+    ("de_int_ncc", 2, 1, 2, 1280, 720, dict(costfct=10), 0.05),
     ("de_int_fb_op3", 2, 1, 3, 640, 360, dict(usefbcon=1), MAX_TOL_DENSE),
     ("of_int_early_stop", 1, 1, 2, 1024, 436, dict(min_iter=2, max_iter=30, res_thresh=0.4), 0.05),
     ("of_int_nonorm", 1, 1, 2, 1024, 436, dict(patnorm=0), MAX_TOL_FINE),
@@ -258,6 +263,20 @@ def test_cli_matches_library(gpu, tmp_path):
         assert np.array_equal(got, want)
     # malformed argument lists are errors, not out-of-bounds reads (run_dense.cpp:272-292)
     assert subprocess.run([os.path.join(exe_dir, "run_OF_INT"), "x", "y", "z", "1", "2", "3"], capture_output=True).returncode != 0
+
+
+def test_ncc_is_gain_invariant(gpu):
+    """Second frame darkened by 30 % (+ offset): the NCC flow barely moves, the L2 flow does."""
+    A, B, gt = make_pair(218, 512, seed=4)
+    B2 = np.clip(B.astype(np.float32) * 0.7 + 20, 0, 255).astype(np.uint8)
+    res = {}
+    for cost in (0, 10):
+        p = gpu.operating_point(2, 512).copy(verbosity=0, costfct=cost, usetvref=0)
+        with gpu.Handle(p, 512, 218, 2) as hd:
+            out = hd.run_host(np.stack([A, A]), np.stack([B, B2]))
+        res[cost] = (epe(out[0], gt)[0], epe(out[1], gt)[0])
+    assert res[10][1] < res[10][0] + 0.1          # NCC: same quality under the gain change
+    assert res[10][1] < res[0][1]                 # and better than L2 on the darkened frame
 
 
 def test_identical_frames_give_exactly_zero(gpu):
