@@ -180,7 +180,15 @@ def main():
 
     import of_dis_b200 as dis   # raises if libdisb200.so is missing: there is no fallback
     p = dis.operating_point(op, w0, mode, ch).copy(verbosity=0)
-    A, B = make_inputs(mode, ch, w0, h0)
+    seq = args.workload == "C5"       # video: consecutive frames, pair i = (i, i+1), pyramids shared
+    if seq:
+        from of_dis_b200.synth import make_sequence
+        fr = make_sequence(h0, w0, 5, seed=0)
+        A, B = np.stack(fr[:-1]), np.stack(fr[1:])
+        if args.batch == 1480:
+            args.batch = 256          # BASELINE.json configs[4]: 256 consecutive pairs
+    else:
+        A, B = make_inputs(mode, ch, w0, h0)
     bytes_per_pair = 2 * w0 * h0 * ch + 4 * w0 * h0 * nop     # compulsory traffic of the whole path
     config = {"workload": "%s: %s, params %s" % (args.workload, desc, " ".join("%g" % v for v in p.cli_args())),
               "pairs_per_step_per_gpu": args.batch, "frame": [w0, h0, ch], "l2_policy": "inputs+outputs per step (%.0f MB) exceed the 126 MB L2" % (args.batch * bytes_per_pair / 1e6),
@@ -231,8 +239,18 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    if seq:
+        # ping-pong over the 5 synthetic frames so that every consecutive pair is a real, small motion
+        order = [(i % 8) if (i % 8) < 5 else 8 - (i % 8) for i in range(nb + 1)]
+        frames_np = np.stack([fr[k] for k in order])
+        hF = torch.from_numpy(frames_np).pin_memory()
+        dF = hF.cuda()
+
     def step():
-        hd.run_device(dA.data_ptr(), dB.data_ptr(), nb, dOut.data_ptr())
+        if seq:
+            hd.run_sequence_device(dF.data_ptr(), nb + 1, dOut.data_ptr())
+        else:
+            hd.run_device(dA.data_ptr(), dB.data_ptr(), nb, dOut.data_ptr())
 
     for _ in range(W_):
         step()
@@ -311,21 +329,28 @@ def main():
 
     # ---- end to end through the host-pointer C-ABI entry (pinned host buffers) ----
     e2e = None
+
+    def host_call():
+        if seq:
+            hd.run_sequence_host_ptr(hF.data_ptr(), nb + 1, hOut.data_ptr())
+        else:
+            hd.run_host_ptr(hA.data_ptr(), hB.data_ptr(), nb, hOut.data_ptr())
+
     if not args.no_e2e:
         for _ in range(2):
-            hd.run_host_ptr(hA.data_ptr(), hB.data_ptr(), nb, hOut.data_ptr())
+            host_call()
         barrier()
         t0 = time.perf_counter()
         for _ in range(args.steps):
-            hd.run_host_ptr(hA.data_ptr(), hB.data_ptr(), nb, hOut.data_ptr())
+            host_call()
         barrier()
         dt = time.perf_counter() - t0
         if world > 1:
             t = torch.tensor([dt], device="cuda")
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             dt = float(t.item())
-        e2e = {"value": pairs / dt, "unit": "pairs/s", "h2d_bytes_per_step": 2 * nb * w0 * h0 * ch,
-               "d2h_bytes_per_step": nb * w0 * h0 * nop * 4, "checksum": float(hOut[0].double().abs().mean())}
+        e2e = {"value": pairs / dt, "unit": "pairs/s", "h2d_bytes_per_step": ((nb + 1) if seq else 2 * nb) * w0 * h0 * ch * world,
+               "d2h_bytes_per_step": nb * w0 * h0 * nop * 4 * world, "checksum": float(hOut[0].double().abs().mean())}
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

@@ -99,6 +99,13 @@ int disb200_run_batch_host(DisHandle* h, const uint8_t* A, const uint8_t* B, int
 int disb200_run_batch_device(DisHandle* h, const uint8_t* dA, const uint8_t* dB, int n, float* dOut);
 int disb200_sync(DisHandle* h);
 
+/* Video: nframes consecutive frames (contiguous, each h0*w0*channels u8) -> nframes-1 flows, pair i =
+ * frames (i, i+1).  The front end SURVEY.md 8(f) ranks first: every frame's pyramid is built once and serves
+ * both pairs it belongs to (the reference would rebuild it, run_dense.cpp:344-345).  Results are identical to
+ * run_batch* on the explicit pairs.  _device: nframes-1 <= max_batch, asynchronous like run_batch_device. */
+int disb200_run_sequence_device(DisHandle* h, const uint8_t* dFrames, int nframes, float* dOut);
+int disb200_run_sequence_host(DisHandle* h, const uint8_t* frames, int nframes, float* out);
+
 /* CUDA-event stopwatch on the handle's stream (the stream every kernel is launched on). */
 int disb200_timer_begin(DisHandle* h);
 int disb200_timer_end(DisHandle* h, float* elapsed_ms);

@@ -136,6 +136,21 @@ class Handle:
         _check(lib().disb200_run_batch_host(self.h, _ptr(A, C.c_uint8), _ptr(B, C.c_uint8), n, _ptr(out)))
         return out
 
+    def run_sequence(self, frames: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
+        """frames: uint8 (nframes, h0, w0[, C]) contiguous -> float32 (nframes - 1, h0, w0, nop); pair i = (i, i+1)."""
+        nf = frames.shape[0]
+        assert frames.dtype == np.uint8 and frames.flags.c_contiguous and frames.size == nf * self.h0 * self.w0 * self.p.channels
+        if out is None:
+            out = np.empty((nf - 1, self.h0, self.w0, self.p.nop), np.float32)
+        _check(lib().disb200_run_sequence_host(self.h, _ptr(frames, C.c_uint8), nf, _ptr(out)))
+        return out
+
+    def run_sequence_host_ptr(self, frames_ptr: int, nframes: int, out_ptr: int):
+        _check(lib().disb200_run_sequence_host(self.h, C.c_void_p(frames_ptr), nframes, C.c_void_p(out_ptr)))
+
+    def run_sequence_device(self, dFrames: int, nframes: int, dOut: int):
+        _check(lib().disb200_run_sequence_device(self.h, C.c_void_p(dFrames), nframes, C.c_void_p(dOut)))
+
     def run_host_ptr(self, a_ptr: int, b_ptr: int, n: int, out_ptr: int):
         _check(lib().disb200_run_batch_host(self.h, C.c_void_p(a_ptr), C.c_void_p(b_ptr), n, C.c_void_p(out_ptr)))
 

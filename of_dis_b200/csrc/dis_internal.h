@@ -50,15 +50,15 @@ struct PyrLevelPtrs {
   float* dx[2];
   float* dy[2];
 };
-// Both frames per launch (blockIdx.z = 2 * pair + frame).
-void launch_downscale_u8(const uint8_t* framesA, const uint8_t* framesB, int n, int w0, int h0, int C, int padl,
+// All images per launch: blockIdx.z enumerates the nA images of role A, then the nB of role B.
+void launch_downscale_u8(const uint8_t* framesA, const uint8_t* framesB, int nA, int nB, int w0, int h0, int C, int padl,
                          int padt, int lvl, const LevelGeom& g, float* imgA, float* imgB, cudaStream_t s,
                          LaunchStats* st);
 // level image (padded array, interior valid) -> next coarser level image interior (2x2 mean)
 void launch_halve(const float* srcA, const float* srcB, const LevelGeom& gs, float* dstA, float* dstB,
-                  const LevelGeom& gd, int n, int C, cudaStream_t s, LaunchStats* st);
+                  const LevelGeom& gd, int nA, int nB, int C, cudaStream_t s, LaunchStats* st);
 // interiors valid -> replicate borders of img, dx / dy (zero border), all levels in one launch
-void launch_sobel_pad_levels(const PyrLevelPtrs* lv, const LevelGeom* g, int nlev, int n, int C, cudaStream_t s,
+void launch_sobel_pad_levels(const PyrLevelPtrs* lv, const LevelGeom* g, int nlev, int nA, int nB, int C, cudaStream_t s,
                              LaunchStats* st);
 
 // ---- stage 2: inverse search ------------------------------------------------------------

@@ -145,7 +145,7 @@ struct Engine {
       if (g.w < 2 || g.h < 2) return fail(DISB200_EUNSUPPORTED, "coarsest level smaller than 2x2 pixels");
       for (int f = 0; f < 2; ++f)
         for (int a = 0; a < 3; ++a) {
-          int rc = dalloc(&pyr[f][a][l], g.img_elems * max_batch);
+          int rc = dalloc(&pyr[f][a][l], g.img_elems * (max_batch + (f == 0 ? 1 : 0)));
           if (rc) return rc;
         }
       for (int d = 0; d < (p.usefbcon ? 2 : 1); ++d) {
@@ -246,12 +246,19 @@ struct Engine {
     }
   }
 
-  // a1 + a2: u8 frames (device) -> padded pyramids of both frames
+  // Sequence mode (video): pair i = frames (i, i+1); the n + 1 frame pyramids live in the role-A arrays and the
+  // second frame of pair i is simply the first frame of pair i + 1.
+  bool seq = false;
+  float* P(int f, int a, int l) const { return seq ? pyr[0][a][l] + (f ? geom[l].img_elems : 0) : pyr[f][a][l]; }
+
+  // a1 + a2: u8 frames (device) -> padded pyramids of both frames (dB == nullptr: dA holds n + 1 consecutive frames)
   void build_pyramids(const uint8_t* dA, const uint8_t* dB, int n, int w0, int h0, int padl, int padt) {
     StageScope sc(this, 0);
-    launch_downscale_u8(dA, dB, n, w0, h0, C, padl, padt, p.sc_l, geom[p.sc_l], pyr[0][0][p.sc_l], pyr[1][0][p.sc_l], stream, &stats);
+    seq = dB == nullptr;
+    const int nA = seq ? n + 1 : n, nB = seq ? 0 : n;
+    launch_downscale_u8(dA, dB, nA, nB, w0, h0, C, padl, padt, p.sc_l, geom[p.sc_l], pyr[0][0][p.sc_l], pyr[1][0][p.sc_l], stream, &stats);
     for (int l = p.sc_l + 1; l <= p.sc_f; ++l)
-      launch_halve(pyr[0][0][l - 1], pyr[1][0][l - 1], geom[l - 1], pyr[0][0][l], pyr[1][0][l], geom[l], n, C, stream, &stats);
+      launch_halve(pyr[0][0][l - 1], pyr[1][0][l - 1], geom[l - 1], pyr[0][0][l], pyr[1][0][l], geom[l], nA, nB, C, stream, &stats);
     PyrLevelPtrs lv[9];
     LevelGeom gl[9];
     int nlev = 0;
@@ -259,7 +266,7 @@ struct Engine {
       gl[nlev] = geom[l];
       for (int f = 0; f < 2; ++f) { lv[nlev].img[f] = pyr[f][0][l]; lv[nlev].dx[f] = pyr[f][1][l]; lv[nlev].dy[f] = pyr[f][2][l]; }
     }
-    launch_sobel_pad_levels(lv, gl, nlev, n, C, stream, &stats);
+    launch_sobel_pad_levels(lv, gl, nlev, nA, nB, C, stream, &stats);
   }
 
   // The scale loop, oflow.cpp:182-330.  Result: flow[0][sc_l].
@@ -271,8 +278,8 @@ struct Engine {
         StageScope sc(this, 1);
         for (int d = 0; d < ndir; ++d) {                               // oflow.cpp:191-232
           PatchArgs a;
-          a.tmpl_img = pyr[d][0][sl]; a.tmpl_dx = pyr[d][1][sl]; a.tmpl_dy = pyr[d][2][sl];
-          a.tgt_img = pyr[1 - d][0][sl];
+          a.tmpl_img = P(d, 0, sl); a.tmpl_dx = P(d, 1, sl); a.tmpl_dy = P(d, 2, sl);
+          a.tgt_img = P(1 - d, 0, sl);
           a.flow_prev = nullptr; a.flow_prev_stride = 0;
           if (sl < p.sc_f) {
             a.flow_prev = flow[d][sl + 1];
@@ -303,9 +310,9 @@ struct Engine {
       }
       if (p.usetvref) {                                                // oflow.cpp:281-290
         StageScope sc(this, 3);
-        launch_varref_level(pyr[0][0][sl], pyr[1][0][sl], flow[0][sl], g, p, 0, vb, n, stream, &stats);
+        launch_varref_level(P(0, 0, sl), P(1, 0, sl), flow[0][sl], g, p, 0, vb, n, stream, &stats);
         if (p.usefbcon && sl > p.sc_l)
-          launch_varref_level(pyr[1][0][sl], pyr[0][0][sl], flow[1][sl], g, p, 1, vb, n, stream, &stats);
+          launch_varref_level(P(1, 0, sl), P(0, 0, sl), flow[1][sl], g, p, 1, vb, n, stream, &stats);
       }
     }
     cudaError_t e = cudaGetLastError();
@@ -346,7 +353,7 @@ struct DisHandle {
   int ensure_staging() {
     if (staging) return DISB200_OK;
     for (int k = 0; k < 2; ++k) {
-      int rc = e.dalloc(&dA[k], in_bytes * max_batch);
+      int rc = e.dalloc(&dA[k], in_bytes * (max_batch + 1));   // + 1: a sequence chunk of m pairs is m + 1 frames
       if (!rc) rc = e.dalloc(&dB[k], in_bytes * max_batch);
       if (!rc) rc = e.dalloc(&dOut[k], out_bytes / sizeof(float) * max_batch);
       if (rc) return rc;
@@ -411,7 +418,7 @@ struct DisHandle {
         CU(cudaStreamWaitEvent(E.stream, ev_fork, 0));
       }
       E.stats.launches = 0;
-      int rc = enqueue_one(E, a + (size_t)lo * in_bytes, b + (size_t)lo * in_bytes, m, out + (size_t)lo * out_elems);
+      int rc = enqueue_one(E, a + (size_t)lo * in_bytes, b ? b + (size_t)lo * in_bytes : nullptr, m, out + (size_t)lo * out_elems);
       if (rc) return rc;
       launches += E.stats.launches;     // kernels of this enqueue() call (all sub-batches)
       if (i > 0 && !serial) {
@@ -589,6 +596,52 @@ int disb200_run_batch_host(DisHandle* h, const uint8_t* A, const uint8_t* B, int
   return h->check_overflow();
 }
 
+int disb200_run_sequence_device(DisHandle* h, const uint8_t* dFrames, int nframes, float* dOut) {
+  if (!h || !dFrames || !dOut) return fail(DISB200_EINVAL, "null argument");
+  if (nframes < 2 || nframes - 1 > h->max_batch) return fail(DISB200_EINVAL, "nframes - 1 must be in 1..max_batch");
+  CU(cudaSetDevice(h->e.device));
+  h->e.begin_run();
+  return h->enqueue(dFrames, nullptr, nframes - 1, dOut);
+}
+
+int disb200_run_sequence_host(DisHandle* h, const uint8_t* frames, int nframes, float* out) {
+  if (!h || !frames || !out) return fail(DISB200_EINVAL, "null argument");
+  if (nframes < 2) return fail(DISB200_EINVAL, "a sequence needs at least two frames");
+  CU(cudaSetDevice(h->e.device));
+  int rc = h->ensure_staging();
+  if (rc) return rc;
+  h->e.begin_run();
+  const int n = nframes - 1;
+  int mb = h->max_batch;
+  {
+    static const char* ev = getenv("DISB200_HOST_CHUNK");
+    const int want = ev ? atoi(ev) : std::max(16, (n + 7) / 8);
+    mb = std::max(1, std::min(mb, want));
+  }
+  int k = 0, total_launches = 0;
+  for (int i0 = 0; i0 < n; i0 += mb, ++k) {
+    const int m = std::min(mb, n - i0), b = k & 1;
+    if (k >= 2) CU(cudaStreamWaitEvent(h->s_h2d, h->ev_comp[b], 0));
+    // pairs i0 .. i0+m-1 need frames i0 .. i0+m (the last one is uploaded again with the next chunk)
+    CU(cudaMemcpyAsync(h->dA[b], frames + (size_t)i0 * h->in_bytes, h->in_bytes * (m + 1), cudaMemcpyHostToDevice, h->s_h2d));
+    CU(cudaEventRecord(h->ev_h2d[b], h->s_h2d));
+    CU(cudaStreamWaitEvent(h->e.stream, h->ev_h2d[b], 0));
+    if (k >= 2) CU(cudaStreamWaitEvent(h->e.stream, h->ev_d2h[b], 0));
+    rc = h->enqueue(h->dA[b], nullptr, m, h->dOut[b]);
+    if (rc) return rc;
+    total_launches += h->launches;
+    CU(cudaEventRecord(h->ev_comp[b], h->e.stream));
+    CU(cudaStreamWaitEvent(h->s_d2h, h->ev_comp[b], 0));
+    CU(cudaMemcpyAsync(out + (size_t)i0 * (h->out_bytes / sizeof(float)), h->dOut[b], h->out_bytes * m, cudaMemcpyDeviceToHost, h->s_d2h));
+    CU(cudaEventRecord(h->ev_d2h[b], h->s_d2h));
+  }
+  CU(cudaStreamSynchronize(h->s_d2h));
+  CU(cudaStreamSynchronize(h->e.stream));
+  h->launches = total_launches;
+  h->e.collect_stage_times();
+  return h->check_overflow();
+}
+
 int disb200_run_batch(DisHandle* h, const uint8_t* const* imgA, const uint8_t* const* imgB, int n, float* const* out) {
   if (!h || !imgA || !imgB || !out) return fail(DISB200_EINVAL, "null argument");
   if (n < 1) return fail(DISB200_EINVAL, "n must be >= 1");
@@ -659,7 +712,7 @@ int disb200_fetch(DisHandle* h, int kind, int which, int level, int pair, void* 
     const LevelGeom& g = e.geom[level];
     if (kind <= 2) {
       bytes = g.img_elems * sizeof(float);
-      src = e.pyr[which][kind][level] + (size_t)pair * g.img_elems;
+      src = e.P(which, kind, level) + (size_t)pair * g.img_elems;
     } else {
       if (!e.flow[which][level]) return fail(DISB200_EINVAL, "no backward flow (usefbcon = 0)");
       bytes = (size_t)g.w * g.h * e.nop * sizeof(float);

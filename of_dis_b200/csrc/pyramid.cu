@@ -7,7 +7,8 @@
 // rationals below 2^24, l <= 8), so the finest level that is actually read (sc_l) is computed
 // straight from the u8 frame in one pass; levels 0..sc_l-1, which the reference builds but
 // never reads (oflow.cpp:182), are skipped.  Coarser levels come from the previous one.
-// Both frames of every pair go through the same launch (blockIdx.z = 2 * pair + frame) and
+// Both frames of every pair go through the same launch (blockIdx.z enumerates the images of role A, then B;
+// a video sequence is role A only: each frame's pyramid is built once and serves two pairs) and
 // one launch computes the Sobel gradients and border fills of all levels.
 #include "dis_internal.h"
 
@@ -27,10 +28,11 @@ template <int C>
 __global__ void __launch_bounds__(128)
 downscale_u8_kernel(const uint8_t* __restrict__ framesA, const uint8_t* __restrict__ framesB, int w0, int h0, int padl,
                     int padt, int lvl, int w, int h, int pad, int tw, size_t img_elems, float* __restrict__ imgA,
-                    float* __restrict__ imgB) {
+                    float* __restrict__ imgB, int nA) {
   const int x = blockIdx.x * blockDim.x + threadIdx.x;
   const int y = blockIdx.y;
-  const int pair = blockIdx.z >> 1, frame = blockIdx.z & 1;
+  // blockIdx.z enumerates images: the nA images of role A (first frames / all frames of a sequence), then role B
+  const int frame = (int)blockIdx.z >= nA, pair = frame ? blockIdx.z - nA : blockIdx.z;
   if (x >= w) return;
   const uint8_t* f = (frame ? framesB : framesA) + (size_t)pair * w0 * h0 * C;
   float* img = frame ? imgB : imgA;
@@ -67,10 +69,10 @@ downscale_u8_kernel(const uint8_t* __restrict__ framesA, const uint8_t* __restri
 template <int C>
 __global__ void halve_kernel(const float* __restrict__ srcA, const float* __restrict__ srcB, int stw, int spad,
                              size_t s_elems, float* __restrict__ dstA, float* __restrict__ dstB, int w, int h, int pad,
-                             int tw, size_t d_elems) {
+                             int tw, size_t d_elems, int nA) {
   const int x = blockIdx.x * blockDim.x + threadIdx.x;
   const int y = blockIdx.y;
-  const int pair = blockIdx.z >> 1, frame = blockIdx.z & 1;
+  const int frame = (int)blockIdx.z >= nA, pair = frame ? blockIdx.z - nA : blockIdx.z;
   if (x >= w) return;
   const float* s = (frame ? srcB : srcA) + (size_t)pair * s_elems;
   float* o = (frame ? dstB : dstA) + (size_t)pair * d_elems + ((size_t)(y + pad) * tw + (x + pad)) * C;
@@ -92,13 +94,13 @@ struct SobelLevels {
 // One thread per padded pixel of every level: replicate the image border, Sobel(k=3, 1/8,
 // REFLECT_101) on the unpadded level image for the interior of dx/dy, zeros on their border.
 template <int C>
-__global__ void __launch_bounds__(128) sobel_pad_kernel(SobelLevels L, int pad) {
+__global__ void __launch_bounds__(128) sobel_pad_kernel(SobelLevels L, int pad, int nA) {
   int lv = 0;
 #pragma unroll 1
   while (lv + 1 < L.nlev && (int)blockIdx.y >= L.row0[lv + 1]) ++lv;
   const int x = blockIdx.x * blockDim.x + threadIdx.x;
   const int y = blockIdx.y - L.row0[lv];
-  const int pair = blockIdx.z >> 1, frame = blockIdx.z & 1;
+  const int frame = (int)blockIdx.z >= nA, pair = frame ? blockIdx.z - nA : blockIdx.z;
   const int w = L.w[lv], h = L.h[lv], tw = L.tw[lv];
   if (x >= tw) return;
   const size_t elems = L.elems[lv];
@@ -134,28 +136,28 @@ __global__ void __launch_bounds__(128) sobel_pad_kernel(SobelLevels L, int pad) 
 #undef S
 }
 
-void launch_downscale_u8(const uint8_t* framesA, const uint8_t* framesB, int n, int w0, int h0, int C, int padl,
+void launch_downscale_u8(const uint8_t* framesA, const uint8_t* framesB, int nA, int nB, int w0, int h0, int C, int padl,
                          int padt, int lvl, const LevelGeom& g, float* imgA, float* imgB, cudaStream_t s,
                          LaunchStats* st) {
-  dim3 blk(128), grd((g.w + 127) / 128, g.h, 2 * n);
+  dim3 blk(128), grd((g.w + 127) / 128, g.h, nA + nB);
   if (C == 1)
-    downscale_u8_kernel<1><<<grd, blk, 0, s>>>(framesA, framesB, w0, h0, padl, padt, lvl, g.w, g.h, g.pad, g.tw, g.img_elems, imgA, imgB);
+    downscale_u8_kernel<1><<<grd, blk, 0, s>>>(framesA, framesB, w0, h0, padl, padt, lvl, g.w, g.h, g.pad, g.tw, g.img_elems, imgA, imgB, nA);
   else
-    downscale_u8_kernel<3><<<grd, blk, 0, s>>>(framesA, framesB, w0, h0, padl, padt, lvl, g.w, g.h, g.pad, g.tw, g.img_elems, imgA, imgB);
+    downscale_u8_kernel<3><<<grd, blk, 0, s>>>(framesA, framesB, w0, h0, padl, padt, lvl, g.w, g.h, g.pad, g.tw, g.img_elems, imgA, imgB, nA);
   st->launches++;
 }
 
 void launch_halve(const float* srcA, const float* srcB, const LevelGeom& gs, float* dstA, float* dstB,
-                  const LevelGeom& gd, int n, int C, cudaStream_t s, LaunchStats* st) {
-  dim3 blk(128), grd((gd.w + 127) / 128, gd.h, 2 * n);
+                  const LevelGeom& gd, int nA, int nB, int C, cudaStream_t s, LaunchStats* st) {
+  dim3 blk(128), grd((gd.w + 127) / 128, gd.h, nA + nB);
   if (C == 1)
-    halve_kernel<1><<<grd, blk, 0, s>>>(srcA, srcB, gs.tw, gs.pad, gs.img_elems, dstA, dstB, gd.w, gd.h, gd.pad, gd.tw, gd.img_elems);
+    halve_kernel<1><<<grd, blk, 0, s>>>(srcA, srcB, gs.tw, gs.pad, gs.img_elems, dstA, dstB, gd.w, gd.h, gd.pad, gd.tw, gd.img_elems, nA);
   else
-    halve_kernel<3><<<grd, blk, 0, s>>>(srcA, srcB, gs.tw, gs.pad, gs.img_elems, dstA, dstB, gd.w, gd.h, gd.pad, gd.tw, gd.img_elems);
+    halve_kernel<3><<<grd, blk, 0, s>>>(srcA, srcB, gs.tw, gs.pad, gs.img_elems, dstA, dstB, gd.w, gd.h, gd.pad, gd.tw, gd.img_elems, nA);
   st->launches++;
 }
 
-void launch_sobel_pad_levels(const PyrLevelPtrs* lv, const LevelGeom* g, int nlev, int n, int C, cudaStream_t s,
+void launch_sobel_pad_levels(const PyrLevelPtrs* lv, const LevelGeom* g, int nlev, int nA, int nB, int C, cudaStream_t s,
                              LaunchStats* st) {
   SobelLevels L;
   L.nlev = nlev;
@@ -167,9 +169,9 @@ void launch_sobel_pad_levels(const PyrLevelPtrs* lv, const LevelGeom* g, int nle
     maxtw = g[i].tw > maxtw ? g[i].tw : maxtw;
     for (int f = 0; f < 2; ++f) { L.img[i][f] = lv[i].img[f]; L.dx[i][f] = lv[i].dx[f]; L.dy[i][f] = lv[i].dy[f]; }
   }
-  dim3 blk(128), grd((maxtw + 127) / 128, rows, 2 * n);
-  if (C == 1) sobel_pad_kernel<1><<<grd, blk, 0, s>>>(L, g[0].pad);
-  else sobel_pad_kernel<3><<<grd, blk, 0, s>>>(L, g[0].pad);
+  dim3 blk(128), grd((maxtw + 127) / 128, rows, nA + nB);
+  if (C == 1) sobel_pad_kernel<1><<<grd, blk, 0, s>>>(L, g[0].pad, nA);
+  else sobel_pad_kernel<3><<<grd, blk, 0, s>>>(L, g[0].pad, nA);
   st->launches++;
 }
 

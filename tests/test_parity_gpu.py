@@ -279,6 +279,22 @@ def test_ncc_is_gain_invariant(gpu):
     assert res[10][1] < res[0][1]                 # and better than L2 on the darkened frame
 
 
+def test_video_sequence_reuses_pyramids_and_matches_explicit_pairs(gpu):
+    """C5-style front end: n + 1 frames -> n flows, bit-identical to the explicit (i, i+1) pairs, chunked too."""
+    from of_dis_b200.synth import make_pair
+    frames = np.stack([make_pair(136, 240, seed=s)[0] for s in range(7)])
+    for kw in (dict(), dict(usefbcon=1)):
+        p = gpu.operating_point(2, 240).copy(verbosity=0, sc_f=3, sc_l=1, **kw)
+        with gpu.Handle(p, 240, 136, max_batch=4) as hd:
+            want = hd.run_host(frames[:-1].copy(), frames[1:].copy())
+            l_pairs = hd.launch_count()
+            got = hd.run_sequence(frames)              # 6 pairs, max_batch 4 -> two chunks
+            got3 = hd.run_sequence(frames[:4].copy())  # one chunk
+            assert hd.launch_count() > 0 and l_pairs > 0
+        assert np.array_equal(got, want)
+        assert np.array_equal(got3, want[:3])
+
+
 def test_identical_frames_give_exactly_zero(gpu):
     A, _, _ = make_pair(218, 512, seed=1)
     p = gpu.operating_point(2, 512).copy(verbosity=0)
