@@ -209,6 +209,34 @@ def test_run_dense_parity(gpu, port, cfg):
     assert epe(out[1], want_swapped)[0] <= MEAN_TOL
 
 
+def test_c2_rgb_op4_full_size(gpu, port):
+    """BASELINE.json configs[1]: run_OF_RGB operating point 4 (128 iterations, psz 12, overlap .75, scales 5..0)."""
+    A, B, gt = make_pair(436, 1024, channels=3, seed=0)
+    p = gpu.operating_point(4, 1024, 1, 3).copy(verbosity=0)
+    assert (p.sc_f, p.sc_l, p.max_iter, p.patchsz) == (5, 0, 128, 12)
+    want = port.run_dense(to_orc(p), A, B)
+    with gpu.Handle(p, 1024, 436, 1) as hd:
+        out = hd.run_host(A[None], B[None])[0]
+    m, mx = epe(out, want)
+    assert m <= MEAN_TOL and mx <= MAX_TOL_DENSE, (m, mx)
+    assert abs(epe(out, gt)[0] - epe(want, gt)[0]) < 5e-3
+
+
+def test_c4_4k_cost_variants_with_fb_consistency(gpu, port):
+    """BASELINE.json configs[3] on ONE GPU: 3840x2160, forward-backward consistency, L1 / Huber / NCC, explicit
+    parameters `7 2 16 16 .05 .95 0 8 .40 1 1 {1,2,10} 1 10 10 5 1 3 1.6 0` (lighter line)."""
+    A, B, gt = make_pair(2160, 3840, seed=0)
+    base = gpu.operating_point(2, 3840).copy(verbosity=0, sc_f=7, sc_l=2, max_iter=16, min_iter=16, usefbcon=1)
+    for cost in (1, 2, 10):
+        p = base.copy(costfct=cost)
+        want = port.run_dense(to_orc(p), A, B)
+        with gpu.Handle(p, 3840, 2160, 1) as hd:
+            out = hd.run_host(A[None], B[None])[0]
+        m, mx = epe(out, want)
+        assert m <= MEAN_TOL and mx <= 0.25, (cost, m, mx)
+        assert epe(out, gt)[0] < 0.5
+
+
 def test_run_list_and_chunking(gpu, port):
     """disb200_run_batch (pointer lists) and n > max_batch chunking give the same answers."""
     pairs = [make_pair(100, 180, seed=s)[:2] for s in range(5)]
