@@ -43,7 +43,21 @@ downscale_u8_kernel(const uint8_t* __restrict__ framesA, const uint8_t* __restri
   const int xs = x * k - padl;   // first source column of the block
   const bool fast = C == 1 && k >= 4 && xs >= 0 && xs + k <= w0 && ((xs & 3) == 0) && ((w0 & 3) == 0) &&
                     ((((size_t)f) & 3) == 0);
-  if (fast) {
+  const bool fast8 = fast && k >= 8 && ((xs & 7) == 0) && ((w0 & 7) == 0) && ((((size_t)f) & 7) == 0);
+  if (fast8) {                     // 64-bit loads: one per 8 source pixels
+    unsigned s1 = 0;
+#pragma unroll 4
+    for (int j = 0; j < k; ++j) {
+      const int sy = clampi(y * k + j - padt, 0, h0 - 1);
+      const uint2* row = reinterpret_cast<const uint2*>(f + (size_t)sy * w0 + xs);
+      for (int i = 0; i < k / 8; ++i) {
+        const uint2 v = __ldg(row + i);
+        sum[0] = __dp4a(v.x, 0x01010101u, sum[0]);
+        s1 = __dp4a(v.y, 0x01010101u, s1);
+      }
+    }
+    sum[0] += s1;
+  } else if (fast) {
     for (int j = 0; j < k; ++j) {
       const int sy = clampi(y * k + j - padt, 0, h0 - 1);
       const unsigned* row = reinterpret_cast<const unsigned*>(f + (size_t)sy * w0 + xs);
@@ -83,7 +97,7 @@ __global__ void halve_kernel(const float* __restrict__ srcA, const float* __rest
 }
 
 struct SobelLevels {
-  int nlev;
+  int nlev, rows;
   int w[9], h[9], tw[9], th[9], row0[9];   // row0: first grid row of the level
   size_t elems[9];
   float* img[9][2];
@@ -91,49 +105,80 @@ struct SobelLevels {
   float* dy[9][2];
 };
 
-// One thread per padded pixel of every level: replicate the image border, Sobel(k=3, 1/8,
-// REFLECT_101) on the unpadded level image for the interior of dx/dy, zeros on their border.
+// One thread per FOUR adjacent padded pixels of a row, all levels in one launch: replicate the image border,
+// Sobel(k=3, 1/8, REFLECT_101) on the unpadded level image for the interior of dx/dy, zeros on their border.
+// The 3 x 6 neighbourhood of the four pixels is loaded once (18 loads for 8 gradient values).
+constexpr int SOBEL_PX = 4;
 template <int C>
 __global__ void __launch_bounds__(128) sobel_pad_kernel(SobelLevels L, int pad, int nA) {
+  const int yg = blockIdx.y * blockDim.y + threadIdx.y;   // row over all levels
+  if (yg >= L.rows) return;
   int lv = 0;
 #pragma unroll 1
-  while (lv + 1 < L.nlev && (int)blockIdx.y >= L.row0[lv + 1]) ++lv;
-  const int x = blockIdx.x * blockDim.x + threadIdx.x;
-  const int y = blockIdx.y - L.row0[lv];
+  while (lv + 1 < L.nlev && yg >= L.row0[lv + 1]) ++lv;
+  const int x0 = (blockIdx.x * blockDim.x + threadIdx.x) * SOBEL_PX;
+  const int y = yg - L.row0[lv];
   const int frame = (int)blockIdx.z >= nA, pair = frame ? blockIdx.z - nA : blockIdx.z;
   const int w = L.w[lv], h = L.h[lv], tw = L.tw[lv];
-  if (x >= tw) return;
+  if (x0 >= tw) return;
   const size_t elems = L.elems[lv];
   float* I = L.img[lv][frame] + (size_t)pair * elems;
-  const size_t o = ((size_t)y * tw + x) * C;
-  float* gx = L.dx[lv][frame] + (size_t)pair * elems + o;
-  float* gy = L.dy[lv][frame] + (size_t)pair * elems + o;
-  const int sx = x - pad, sy = y - pad;
-  const bool inside = sx >= 0 && sy >= 0 && sx < w && sy < h;
-  if (!inside) {
-    const float* srcp = I + ((size_t)(clampi(sy, 0, h - 1) + pad) * tw + (clampi(sx, 0, w - 1) + pad)) * C;
+  float* gx = L.dx[lv][frame] + (size_t)pair * elems;
+  float* gy = L.dy[lv][frame] + (size_t)pair * elems;
+  const int sy = y - pad, sx0 = x0 - pad;
+  const int npx = min(SOBEL_PX, tw - x0);
+  const size_t rowo = (size_t)y * tw;
+  if (sy < 0 || sy >= h) {                       // border row: replicate the image, zero gradients
+    const float* srow = I + (size_t)(clampi(sy, 0, h - 1) + pad) * tw * C;
+    for (int k = 0; k < npx; ++k) {
+      const int cx = clampi(sx0 + k, 0, w - 1) + pad;
 #pragma unroll
-    for (int c = 0; c < C; ++c) {
-      I[o + c] = srcp[c];
-      gx[c] = 0.f;
-      gy[c] = 0.f;
+      for (int c = 0; c < C; ++c) {
+        const size_t o = (rowo + x0 + k) * C + c;
+        I[o] = srow[cx * C + c];
+        gx[o] = 0.f;
+        gy[o] = 0.f;
+      }
     }
     return;
   }
-  const int xm = reflect101(sx - 1, w) + pad, xp = reflect101(sx + 1, w) + pad, xc = sx + pad;
-  const int ym = reflect101(sy - 1, h) + pad, yp = reflect101(sy + 1, h) + pad, yc = sy + pad;
-#define S(X, Y, c) I[((size_t)(Y)*tw + (X)) * C + (c)]
+  int col[SOBEL_PX + 2];
+#pragma unroll
+  for (int e = 0; e < SOBEL_PX + 2; ++e) col[e] = (reflect101(sx0 + e - 1, w) + pad) * C;
+  const float* rm = I + (size_t)(reflect101(sy - 1, h) + pad) * tw * C;
+  const float* rc = I + (size_t)(sy + pad) * tw * C;
+  const float* rp = I + (size_t)(reflect101(sy + 1, h) + pad) * tw * C;
 #pragma unroll
   for (int c = 0; c < C; ++c) {
-    const float r0 = S(xp, ym, c) - S(xm, ym, c);
-    const float r1 = S(xp, yc, c) - S(xm, yc, c);
-    const float r2 = S(xp, yp, c) - S(xm, yp, c);
-    gx[c] = 0.25f * r1 + 0.125f * (r2 + r0);
-    const float s0 = 0.25f * S(xc, ym, c) + 0.125f * (S(xp, ym, c) + S(xm, ym, c));
-    const float s2 = 0.25f * S(xc, yp, c) + 0.125f * (S(xp, yp, c) + S(xm, yp, c));
-    gy[c] = s2 - s0;
+    float vm[SOBEL_PX + 2], vc[SOBEL_PX + 2], vp[SOBEL_PX + 2];
+#pragma unroll
+    for (int e = 0; e < SOBEL_PX + 2; ++e) { vm[e] = rm[col[e] + c]; vc[e] = rc[col[e] + c]; vp[e] = rp[col[e] + c]; }
+    float ox[SOBEL_PX], oy[SOBEL_PX];
+    bool in[SOBEL_PX];
+#pragma unroll
+    for (int k = 0; k < SOBEL_PX; ++k) {
+      const int sx = sx0 + k;
+      in[k] = sx >= 0 && sx < w;
+      const float r0 = vm[k + 2] - vm[k], r1 = vc[k + 2] - vc[k], r2 = vp[k + 2] - vp[k];
+      const float s0 = 0.25f * vm[k + 1] + 0.125f * (vm[k + 2] + vm[k]);
+      const float s2 = 0.25f * vp[k + 1] + 0.125f * (vp[k + 2] + vp[k]);
+      ox[k] = in[k] ? 0.25f * r1 + 0.125f * (r2 + r0) : 0.f;
+      oy[k] = in[k] ? s2 - s0 : 0.f;
+    }
+    const size_t o0 = (rowo + x0) * C + c;
+    if (C == 1 && npx == SOBEL_PX && (((size_t)(gx + o0) | (size_t)(gy + o0)) & 15) == 0) {
+      *reinterpret_cast<float4*>(gx + o0) = make_float4(ox[0], ox[1], ox[2], ox[3]);
+      *reinterpret_cast<float4*>(gy + o0) = make_float4(oy[0], oy[1], oy[2], oy[3]);
+    } else {
+#pragma unroll
+      for (int k = 0; k < SOBEL_PX; ++k)
+        if (k < npx) { gx[o0 + (size_t)k * C] = ox[k]; gy[o0 + (size_t)k * C] = oy[k]; }
+    }
+    // left / right border of an interior row: replicate the nearest interior pixel (vc of the clamped column)
+#pragma unroll
+    for (int k = 0; k < SOBEL_PX; ++k)
+      if (k < npx && !in[k]) I[o0 + (size_t)k * C] = rc[(clampi(sx0 + k, 0, w - 1) + pad) * C + c];
   }
-#undef S
 }
 
 void launch_downscale_u8(const uint8_t* framesA, const uint8_t* framesB, int nA, int nB, int w0, int h0, int C, int padl,
@@ -169,7 +214,9 @@ void launch_sobel_pad_levels(const PyrLevelPtrs* lv, const LevelGeom* g, int nle
     maxtw = g[i].tw > maxtw ? g[i].tw : maxtw;
     for (int f = 0; f < 2; ++f) { L.img[i][f] = lv[i].img[f]; L.dx[i][f] = lv[i].dx[f]; L.dy[i][f] = lv[i].dy[f]; }
   }
-  dim3 blk(128), grd((maxtw + 127) / 128, rows, nA + nB);
+  L.rows = rows;
+  const int per_block = 16 * SOBEL_PX;   // 16 x 8 threads: 64 pixels x 8 rows per block
+  dim3 blk(16, 8), grd((maxtw + per_block - 1) / per_block, (rows + 7) / 8, nA + nB);
   if (C == 1) sobel_pad_kernel<1><<<grd, blk, 0, s>>>(L, g[0].pad, nA);
   else sobel_pad_kernel<3><<<grd, blk, 0, s>>>(L, g[0].pad, nA);
   st->launches++;
