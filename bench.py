@@ -314,8 +314,15 @@ def main():
     dom = max(stage_share, key=stage_share.get)
     dom_ms = stage_share[dom]
     dom_bytes = alg.get(dom)
+    # DRAM traffic per pair and stage from the committed ncu --set full captures (profiles/r01_traffic.json; C1 only)
+    traffic = {}
+    tpath = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    if args.workload == "C1" and os.path.exists(tpath):
+        with open(tpath) as f:
+            traffic = {k: v["dram_read_bytes_per_pair"] + v["dram_write_bytes_per_pair"] for k, v in json.load(f)["per_stage"].items()}
     roof = {"bound": "hbm", "kernel": dom, "unit": "GB/s", "peak": peak, "peak_source": peak_src,
-            "share_of_step": dom_ms / step_ms if step_ms else None, "traffic": None}
+            "share_of_step": dom_ms / step_ms if step_ms else None,
+            "traffic": traffic[dom] * nb if dom in traffic else None}
     if dom_bytes:
         roof["achieved"] = dom_bytes * nb / (dom_ms / 1e3) / 1e9
         roof["frac"] = roof["achieved"] / peak
@@ -323,6 +330,10 @@ def main():
     else:
         roof["achieved"] = None
         roof["frac"] = None
+    # every stage: algorithmic GB/s against the same peak (the launch set of the stage, per step)
+    roof["per_stage"] = {k: {"ms": round(v, 4), "algorithmic_bytes": alg[k] * nb, "achieved": round(alg[k] * nb / (v / 1e3) / 1e9, 1) if v > 0 else None,
+                             "frac": round(alg[k] * nb / (v / 1e3) / 1e9 / peak, 4) if v > 0 else None,
+                             "traffic": traffic[k] * nb if k in traffic else None} for k, v in stage_share.items()}
     path_gbs = value / world * bytes_per_pair / 1e9
     roof["whole_path"] = {"algorithmic_bytes_per_pair": bytes_per_pair, "achieved": path_gbs, "frac": path_gbs / peak}
     roof["stage_ms_per_step"] = {k: round(v, 4) for k, v in stage_share.items()}
