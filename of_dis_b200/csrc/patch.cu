@@ -21,6 +21,13 @@
 
 namespace disb200 {
 
+// sum / NV; for a power-of-two NV the product with the exact reciprocal is the same bits as the division
+template <int NV>
+__device__ __forceinline__ float mean_of(float sum) {
+  if ((NV & (NV - 1)) == 0) return sum * (1.0f / (float)NV);
+  return sum / (float)NV;
+}
+
 template <int G>
 __device__ __forceinline__ float gsum(float v) {
 #pragma unroll
@@ -96,7 +103,7 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
       s += t[k];
     }
     if (o.patnorm > 0 || o.costfct == 10) {
-      const float m = gsum<G>(s) / (float)NV;
+      const float m = mean_of<NV>(gsum<G>(s));
 #pragma unroll
       for (int k = 0; k < VPL; ++k) t[k] = val[k] ? t[k] - m : 0.f;
     }
@@ -226,7 +233,7 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
       }
     }
     float m = 0.f;
-    if (o.patnorm > 0 || o.costfct == 10) m = gsum<G>(qs) / (float)NV;
+    if (o.patnorm > 0 || o.costfct == 10) m = mean_of<NV>(gsum<G>(qs));
     float ns0 = 0.f, ns1 = 0.f, wsum = 0.f;
     float npw[VPL];
 #define DISB200_RESIDUAL(COST, QV)                                 \
@@ -260,10 +267,12 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
       const float dpsq = OF ? ndp0 * ndp0 + ndp1 * ndp1 : ndp0 * ndp0;
       if (ncnt == 1) dpsq_init = dpsq;
       const float mares_old = mares;
-      const float nmares = wsum / (float)NV;
-      if (!((ncnt < o.max_iter) & (nmares > o.res_thresh) &
-            ((ncnt < o.min_iter) | (dpsq / dpsq_init >= o.dp_thresh_sq)) &
-            ((ncnt < o.min_iter) | (nmares / mares_old <= o.dr_thresh))))
+      const float nmares = mean_of<NV>(wsum);
+      // patch.cpp:290-293; the two rate tests (one division each) only matter once min_iter is reached
+      bool go_on = (ncnt < o.max_iter) & (nmares > o.res_thresh);
+      if (go_on && ncnt >= o.min_iter)
+        go_on = (dpsq / dpsq_init >= o.dp_thresh_sq) & (nmares / mares_old <= o.dr_thresh);
+      if (!go_on)
         nconv = true;
       mares = nmares;
       p0 = np0; p1 = np1; ptx = nptx; pty = npty; dp0 = ndp0; dp1 = ndp1; cnt = ncnt; conv = nconv;
