@@ -1,4 +1,4 @@
-// Single-warp lexicographic SOR for levels of up to 64 rows (included by varref.cu, inside its
+// Single-warp lexicographic SOR for levels of up to 32 * NB rows, NB <= 3 (included by varref.cu, inside its
 // namespaces).
 //
 // Same update order and fp32 operation order as sor_coupled / sor_coupled_slow_but_readable_DE
@@ -6,7 +6,7 @@
 // (i, j+1) of sweep s-1, so at step t sweep s may process pixel  i = t - j - 2 s  of row j: every
 // dependency was produced at step t-1 or t-2.
 //
-// Mapping: ONE warp per frame pair, lane = row (NB = 2: rows `lane` and `lane + 32`), and the
+// Mapping: ONE warp per frame pair, lane = row (NB bands: rows `lane`, `lane + 32`, ...), and the
 // NS sweeps are interleaved inside each thread, so one step is NB x NS independent pixel updates
 // per lane and nothing ever crosses a warp: the values a pixel needs from its neighbours at
 // step t are exactly the results the neighbouring lanes (or this lane's previous sweep)
@@ -203,13 +203,14 @@ __device__ __forceinline__ void sor_warp(float* __restrict__ du, unsigned smem, 
     for (int s = 0; s < NS; ++s) {
 #pragma unroll
       for (int b = 0; b < NB; ++b) {
-        // top of row b*32+lane: lane-1 of the same band; lane 0 of band 1 takes row 31 (lane 31 of band 0)
+        // top of row b*32+lane: lane-1 of the same band; lane 0 of band b takes the last row of band b-1
+        // (lane 31 of band b-1 is read by nobody else in this shuffle, so it offers that value instead)
         float2 st = R[b][s];
-        if (NB == 2 && b == 1 && lane == 31) st = R[0][s];
+        if (b > 0 && lane == 31) st = R[b > 0 ? b - 1 : 0][s];
         top[b][s] = sorw_shfl<OF>(st, up);
         // bottom: lane+1's previous sweep (sweep 0: its right neighbour, which is (i0, j+1))
         float2 sb = s > 0 ? R[b][s - 1] : nr0[b];
-        if (NB == 2 && b == 0 && lane == 0) sb = s > 0 ? R[NB - 1][s - 1] : nr0[NB - 1];
+        if (b + 1 < NB && lane == 0) sb = s > 0 ? R[b + 1 < NB ? b + 1 : b][s - 1] : nr0[b + 1 < NB ? b + 1 : b];
         bot[b][s] = sorw_shfl<OF>(sb, dn);
       }
     }

@@ -746,12 +746,12 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
     return;
   }
   cudaMemsetAsync(vb.du, 0, sizeof(float) * vb.plane_cap * NOP * n, st);
-  // SOR launcher: one warp per pair (levels of up to 64 rows, up to 5 sweeps), else the general wavefront
+  // SOR launcher: one warp per pair (levels of up to 96 rows, up to 5 sweeps), else the general wavefront
   void (*sorw)(float*, const float4*, const float4*, Dims, float) = nullptr;
-  if (g.h <= 64 && !(tv_path && tv_path[0] == 'o')) {
-    const bool two = g.h > 32;
+  if (g.h <= 96 && !(tv_path && tv_path[0] == 'o')) {
+    const int nb = (g.h + 31) / 32;
     switch (p.tv_solverit) {
-#define DISB200_SORW_CASE(NS_) case NS_: sorw = two ? sor_warp_kernel<OF, NS_, 2> : sor_warp_kernel<OF, NS_, 1>; break;
+#define DISB200_SORW_CASE(NS_) case NS_: sorw = nb == 3 ? sor_warp_kernel<OF, NS_, 3> : (nb == 2 ? sor_warp_kernel<OF, NS_, 2> : sor_warp_kernel<OF, NS_, 1>); break;
       DISB200_SORW_CASE(1) DISB200_SORW_CASE(2) DISB200_SORW_CASE(3) DISB200_SORW_CASE(4) DISB200_SORW_CASE(5)
 #undef DISB200_SORW_CASE
       default: break;

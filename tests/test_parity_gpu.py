@@ -91,7 +91,7 @@ def test_varref_tall_level_uses_band_mode(gpu, port):
 
 
 @pytest.mark.parametrize("mode,ch", [(1, 1), (1, 3), (2, 1), (2, 3)])
-@pytest.mark.parametrize("w0,h0,level,solverit", [(1024, 436, 3, 3), (500, 218, 2, 3), (260, 128, 1, 5), (250, 120, 2, 2)])
+@pytest.mark.parametrize("w0,h0,level,solverit", [(1024, 436, 3, 3), (500, 218, 2, 3), (260, 128, 1, 5), (250, 120, 2, 2), (1920, 1080, 4, 3), (300, 180, 1, 1)])
 def test_tv_paths_agree_bit_for_bit(gpu, port, monkeypatch, mode, ch, w0, h0, level, solverit):
     """The three schedules of the lexicographic SOR — one CTA per pair (fused), one warp per pair with shuffles
     and cp.async row streams (split, used for large batches), general wavefront (old) — are the same iteration."""
