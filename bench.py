@@ -35,7 +35,10 @@ WORKLOADS = {
     "op3": (1, 1, 3, 1024, 436, "run_OF_INT op3 1024x436 grey"),
     "op4": (1, 1, 4, 1024, 436, "run_OF_INT op4 1024x436 grey"),
     "C5": (1, 1, 2, 1920, 1080, "run_OF_INT op2 1920x1080 grey video pairs"),
+    # SURVEY.md 8(d) C4, lighter explicit line: fwd/bwd consistency, L1 cost, finest level 960x544
+    "C4": (1, 1, 2, 3840, 2160, "run_OF_INT explicit params 3840x2160 grey, fb consistency + L1"),
 }
+C4_OVERRIDE = dict(sc_f=7, sc_l=2, max_iter=16, min_iter=16, patchsz=8, patove=0.4, usefbcon=1, costfct=1)
 N_DISTINCT = 4  # distinct synthetic pairs, tiled over the batch
 
 
@@ -180,6 +183,10 @@ def main():
 
     import of_dis_b200 as dis   # raises if libdisb200.so is missing: there is no fallback
     p = dis.operating_point(op, w0, mode, ch).copy(verbosity=0)
+    if args.workload == "C4":
+        p = p.copy(**C4_OVERRIDE)
+        if args.batch == 1480:
+            args.batch = 16
     seq = args.workload == "C5"       # video: consecutive frames, pair i = (i, i+1), pyramids shared
     if seq:
         from of_dis_b200.synth import make_sequence

@@ -51,7 +51,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         s = os.path.join(CSRC, src)
         o = os.path.join(objdir, src.replace(".cu", ".o"))
         if force or _stale(o, [s] + headers):
-            flags = [f for f in NVCC_FLAGS if not (src in FMA_OK and f == "-fmad=false")]
+            flags = [f for f in NVCC_FLAGS if not (src in FMA_OK and f == "-fmad=false")] + os.environ.get("DISB200_NVCC_EXTRA", "").split()
             r = subprocess.run([nvcc] + flags + ["-c", s, "-o", o], capture_output=True, text=True)
             logs[src] = r.stderr
             if r.returncode != 0:

@@ -106,7 +106,9 @@ struct VarRefBuffers {
   float* smooth; // float2 {h, v}
   float* coef;   // float4 {hl, h, vt, v}
   float* inv;    // float4 {i11, i12, i22, 0}   (DE: {a11+sum,0,0,0})
-  float* rhs;    // float2 {b1, b2}            (DE: float)
+  float* rhs;    // spare [nop] planes: boundary-row exchange of the banded SOR (sor_band.cuh), zeroed at create
+  unsigned* sorb_ctl = nullptr;   // device: {ticket counter, error flag} of the banded SOR; null = banded SOR off
+  unsigned* sorb_host = nullptr;  // host:   {launch epoch, tickets issued so far}
   size_t plane_cap;  // elements per pair per plane (>= w*h of the largest level)
 };
 void launch_varref_level(const float* im_a, const float* im_b, float* flow, const LevelGeom& g, const DisParams& p,

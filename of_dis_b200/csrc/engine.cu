@@ -105,6 +105,8 @@ struct Engine {
   int* cell_list = nullptr;
   int cell_cap = 0;
   int* overflow = nullptr;
+  unsigned* sorb_ctl = nullptr;     // banded SOR: device {ticket counter, error flag}
+  unsigned sorb_host[2] = {0, 0};   //             host {launch epoch, tickets issued}
   size_t ncell_max = 0;
   std::vector<void*> allocs;
   cudaStream_t stream = nullptr;
@@ -189,6 +191,13 @@ struct Engine {
       vb.avg = take(C); vb.Iz = take(C); vb.Ix = take(C); vb.Iy = take(C);
       vb.Ixx = take(C); vb.Ixy = take(C); vb.Iyy = take(C); vb.Ixz = take(C); vb.Iyz = take(C);
       vb.mask = take(1); vb.smooth = take(1);
+      // banded SOR of tall levels: tagged exchange rows live in the spare planes and must never hold a live epoch
+      CU(cudaMemset(vpool, 0, sizeof(float) * plane * nplanes * max_batch));
+      rc = dalloc(&sorb_ctl, 2);
+      if (rc) return rc;
+      CU(cudaMemset(sorb_ctl, 0, 2 * sizeof(unsigned)));
+      sorb_host[0] = sorb_host[1] = 0;
+      vb.sorb_ctl = sorb_ctl; vb.sorb_host = sorb_host;
     }
     return DISB200_OK;
   }
@@ -201,6 +210,18 @@ struct Engine {
     ev_pool.clear();
     if (stream) cudaStreamDestroy(stream);
     stream = nullptr;
+  }
+
+  // banded SOR (sor_band.cuh): a band that waited too long for its neighbour raised the flag
+  int check_sorb() {
+    if (!sorb_ctl || sorb_host[0] == 0) return DISB200_OK;
+    unsigned v = 0;
+    CU(cudaMemcpy(&v, sorb_ctl + 1, sizeof(unsigned), cudaMemcpyDeviceToHost));
+    if (v) {
+      cudaMemset(sorb_ctl + 1, 0, sizeof(unsigned));
+      return fail(DISB200_ECUDA, "banded SOR: a band timed out waiting for its neighbour (result invalid)");
+    }
+    return DISB200_OK;
   }
 
   cudaEvent_t next_event() {
@@ -431,16 +452,20 @@ struct DisHandle {
     return DISB200_OK;
   }
 
+  // device-side error flags, read after the work has been synchronised
   int check_overflow() {
-    if (!e.overflow) return DISB200_OK;
     for (int i = 0; i <= (int)extra.size(); ++i) {
       Engine& E = sub(i);
-      int v = 0;
-      CU(cudaMemcpy(&v, E.overflow, sizeof(int), cudaMemcpyDeviceToHost));
-      if (v > 0) {
-        cudaMemset(E.overflow, 0, sizeof(int));
-        return fail(DISB200_EUNSUPPORTED, "forward-backward merge: " + std::to_string(v) + " patches ended in one cell, capacity " + std::to_string(E.cell_cap));
+      if (E.overflow) {
+        int v = 0;
+        CU(cudaMemcpy(&v, E.overflow, sizeof(int), cudaMemcpyDeviceToHost));
+        if (v > 0) {
+          cudaMemset(E.overflow, 0, sizeof(int));
+          return fail(DISB200_EUNSUPPORTED, "forward-backward merge: " + std::to_string(v) + " patches ended in one cell, capacity " + std::to_string(E.cell_cap));
+        }
       }
+      int rc = E.check_sorb();
+      if (rc) return rc;
     }
     return DISB200_OK;
   }
@@ -768,6 +793,7 @@ int disb200_ofclass(const DisParams* params, const float* const* im_ao, const fl
     cudaMemcpy(&v, e.overflow, sizeof(int), cudaMemcpyDeviceToHost);
     if (v > 0) rc = fail(DISB200_EUNSUPPORTED, "forward-backward merge cell overflow");
   }
+  if (!rc) rc = e.check_sorb();
   e.destroy();
   return rc;
 }
@@ -801,6 +827,7 @@ int disb200_varref_level(const DisParams* params, const float* im_a, const float
     if (ce == cudaSuccess) ce = cudaMemcpyAsync(flow, e.flow[0][0], fb, cudaMemcpyDeviceToHost, e.stream);
     if (ce == cudaSuccess) ce = cudaStreamSynchronize(e.stream);
     if (ce != cudaSuccess) rc = fail(DISB200_ECUDA, std::string("varref_level: ") + cudaGetErrorString(ce));
+    if (!rc) rc = e.check_sorb();
   }
   e.destroy();
   return rc;

@@ -17,6 +17,9 @@
 // addressed in place (the reference copies them out first, refine_variational.cpp:120-149).
 #include <cstdlib>
 
+#ifdef SORB_STATS
+#include <cstdio>
+#endif
 #include "dis_internal.h"
 
 namespace disb200 {
@@ -595,6 +598,7 @@ __device__ __forceinline__ void sor_wavefront(float* du, const float4* cA, const
 
 #include "sor_lean.cuh"
 #include "sor_warp.cuh"
+#include "sor_band.cuh"
 
 // General path: one CTA per frame pair, increment du in global memory.  When rows x sweeps
 // exceed the CTA, sweeps run one after another over row bands (same lexicographic order).
@@ -757,6 +761,27 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
       default: break;
     }
   }
+  // tall levels: one warp per band of 32 rows, bands chained through tagged boundary rows (sor_band.cuh)
+  void (*sorb)(float*, const float4*, const float4*, float4*, float4*, unsigned*, unsigned, unsigned, Dims, int, float) = nullptr;
+  const int nbands = (g.h + 31) / 32;
+  const int sorb_rows = p.tv_solverit + (p.tv_solverit > 1 ? p.tv_solverit - 1 : 1);   // exchange rows per band
+  size_t sorb_smem = 0;
+  // (latency mode: measured 1.35-1.5x over the general wavefront while all bands of the batch are resident, 2 per
+  //  SM — one 4K pair: 27.6 -> 19.8 ms of SOR; with more bands than that the general wavefront, one CTA per
+  //  pair, has the better throughput: 64 4K pairs 33 vs 45 ms)
+  const char* sorb_max_env = getenv("DISB200_SORB_MAX");
+  const int sorb_max = sorb_max_env ? atoi(sorb_max_env) : 296;
+  if (!sorw && vb.sorb_ctl && g.h > 96 && g.w >= 8 && nbands <= 64 && p.tv_solverit <= 3 && n * nbands <= sorb_max &&
+      (size_t)nbands * g.w * sorb_rows * 4 <= vb.plane_cap * NOP && !(tv_path && tv_path[0] == 'o')) {
+    switch (p.tv_solverit) {
+      case 1: sorb = sor_band_kernel<OF, 1>; sorb_smem = SorbCfg<1>::BYTES; break;
+      case 2: sorb = sor_band_kernel<OF, 2>; sorb_smem = SorbCfg<2>::BYTES; break;
+      default: sorb = sor_band_kernel<OF, 3>; sorb_smem = SorbCfg<3>::BYTES; break;
+    }
+    cudaFuncSetAttribute(sorb, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sorb_smem);
+  }
+  float4* sorb_xt = reinterpret_cast<float4*>(vb.rhs);
+  float4* sorb_xb = sorb_xt + (size_t)n * nbands * p.tv_solverit * g.w;
   const size_t sorw_smem = sorw_smem_bytes(g.h, p.tv_solverit);
   if (sorw) cudaFuncSetAttribute(sorw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sorw_smem);
   int threads = pipelined ? g.h * p.tv_solverit : (g.h < 512 ? g.h : 512);
@@ -773,6 +798,11 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
         sor_redblack_kernel<OF><<<rgrd, rblk, 0, st>>>(vb.du, cA, cB, d, p.tv_sor, sw & 1);
       ls->launches += 2 * p.tv_solverit - 1;
     } else if (sorw) sorw<<<n, 32, sorw_smem, st>>>(vb.du, cA, cB, d, p.tv_sor);
+    else if (sorb) {
+      const unsigned epoch = ++vb.sorb_host[0], base = vb.sorb_host[1];
+      vb.sorb_host[1] += (unsigned)(n * nbands);
+      sorb<<<n * nbands, 32, sorb_smem, st>>>(vb.du, cA, cB, sorb_xt, sorb_xb, vb.sorb_ctl, base, epoch, d, nbands, p.tv_sor);
+    }
     else sor_wavefront_kernel<OF><<<n, threads, 0, st>>>(vb.du, cA, cB, d, p.tv_solverit, p.tv_sor, pipelined ? 1 : 0);
     if (ls->mark) ls->mark(ls->ctx, 5, 0);
     ls->launches += 3;
