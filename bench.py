@@ -52,12 +52,13 @@ def peaks():
 
 def make_inputs(mode, ch, w0, h0, n_distinct=N_DISTINCT):
     from of_dis_b200.synth import make_pair
-    As, Bs = [], []
+    As, Bs, Gs = [], [], []
     for s in range(n_distinct):
-        A, B, _ = make_pair(h0, w0, channels=ch, mode="OF" if mode == 1 else "DE", seed=s)
+        A, B, gt = make_pair(h0, w0, channels=ch, mode="OF" if mode == 1 else "DE", seed=s)
         As.append(A)
         Bs.append(B)
-    return np.stack(As), np.stack(Bs)
+        Gs.append(gt)
+    return np.stack(As), np.stack(Bs), np.stack(Gs)
 
 
 class ClockSampler(threading.Thread):
@@ -116,15 +117,13 @@ def to_orc(p):
     return q
 
 
-def cpu_reference_throughput(p, A, B, seconds_budget, threads):
-    """pairs/s of the reference's CPU code for the same path on `threads` host threads.
+def cpu_runner(p, A, B):
+    """(one, kind): one(i) -> full-resolution flow of pair i % len(A) from the reference's CPU code.
 
     OFClass comes from oracle/_ref (the reference's own sources) when that library travelled
     with the snapshot, else from the restatement; pyramid and final upsample are the OpenCV
-    restatement in both cases (OpenCV itself is unavailable).  ctypes releases the GIL, so
-    plain Python threads run the C code in parallel.
+    restatement in both cases (OpenCV itself is unavailable).
     """
-    from concurrent.futures import ThreadPoolExecutor
     from oracle import bindings as ob
     port = ob.Port()
     q = to_orc(p)
@@ -147,6 +146,36 @@ def cpu_reference_throughput(p, A, B, seconds_budget, threads):
         PB = port.pyramid(b, p.sc_f, p.sc_l, p.patchsz)
         low = ref.ofclass(q, PA, PB, W, H)
         return port.upsample_crop(low, p.sc_l, padl, padt, w0, h0)
+
+    return one, kind
+
+
+def epe_stats(a, b):
+    d = np.sqrt(((np.asarray(a, np.float64) - np.asarray(b, np.float64)) ** 2).sum(-1))
+    return float(d.mean()), float(d.max())
+
+
+def parity_report(p, A, B, G, hd):
+    """north_star: EPE(GPU, CPU reference) mean / max and EPE against the synthetic ground truth, on the
+    distinct pairs of the workload (the CPU flows come from the same code the cpu_baseline leg times)."""
+    one, kind = cpu_runner(p, A, B)
+    k = len(A)
+    gpu = hd.run_host(np.ascontiguousarray(A), np.ascontiguousarray(B))
+    cpu = np.stack([one(i).reshape(gpu.shape[1:]) for i in range(k)])
+    m, mx = epe_stats(gpu, cpu)
+    rep = {"pairs": k, "against": kind, "epe_gpu_vs_cpu_mean_px": m, "epe_gpu_vs_cpu_max_px": mx,
+           "bit_identical": bool(np.array_equal(gpu, cpu)), "tolerance_mean_px": 0.01}
+    if G is not None:
+        rep["epe_vs_ground_truth_gpu_px"] = epe_stats(gpu, G)[0]
+        rep["epe_vs_ground_truth_cpu_px"] = epe_stats(cpu, G)[0]
+    return rep
+
+
+def cpu_reference_throughput(p, A, B, seconds_budget, threads):
+    """pairs/s of the reference's CPU code for the same path on `threads` host threads (ctypes releases the
+    GIL, so plain Python threads run the C code in parallel)."""
+    from concurrent.futures import ThreadPoolExecutor
+    one, kind = cpu_runner(p, A, B)
 
     t = time.perf_counter()
     one(0)
@@ -191,11 +220,11 @@ def main():
     if seq:
         from of_dis_b200.synth import make_sequence
         fr = make_sequence(h0, w0, 5, seed=0)
-        A, B = np.stack(fr[:-1]), np.stack(fr[1:])
+        A, B, G = np.stack(fr[:-1]), np.stack(fr[1:]), None
         if args.batch == 1480:
             args.batch = 256          # BASELINE.json configs[4]: 256 consecutive pairs
     else:
-        A, B = make_inputs(mode, ch, w0, h0)
+        A, B, G = make_inputs(mode, ch, w0, h0)
     bytes_per_pair = 2 * w0 * h0 * ch + 4 * w0 * h0 * nop     # compulsory traffic of the whole path
     config = {"workload": "%s: %s, params %s" % (args.workload, desc, " ".join("%g" % v for v in p.cli_args())),
               "pairs_per_step_per_gpu": args.batch, "frame": [w0, h0, ch], "l2_policy": "inputs+outputs per step (%.0f MB) exceed the 126 MB L2" % (args.batch * bytes_per_pair / 1e6),
@@ -370,11 +399,12 @@ def main():
         e2e = {"value": pairs / dt, "unit": "pairs/s", "h2d_bytes_per_step": ((nb + 1) if seq else 2 * nb) * w0 * h0 * ch * world,
                "d2h_bytes_per_step": nb * w0 * h0 * nop * 4 * world, "checksum": float(hOut[0].double().abs().mean())}
 
-    cpu = None
+    cpu = parity = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
         v, kind, sample = cpu_reference_throughput(p, A, B, args.cpu_seconds / 4, threads)
         cpu = {"value": v, "unit": "pairs/s", "cores": threads, "kind": kind, "sample": sample}
+        parity = parity_report(p, A, B, G, hd)
 
     if rank == 0:
         line = {"metric": "frame_pairs_per_s", "value": value, "unit": "pairs/s", "mpix_per_s": value * w0 * h0 / 1e6,
@@ -382,7 +412,7 @@ def main():
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic warped-texture pairs (%d distinct seeds tiled over the batch)" % len(A),
                 "config": config, "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * args.steps,
-                "roofline": roof, "cpu_baseline": cpu}
+                "roofline": roof, "cpu_baseline": cpu, "parity": parity}
         print(json.dumps(line))
     hd.close()
     if world > 1:

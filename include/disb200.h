@@ -142,7 +142,21 @@ int disb200_save_pfm(const char* path, const float* disp, int w, int h);
 /* Binary PGM (P5) / PPM (P6) reader standing in for cv::imread (run_dense.cpp:209-210):
  * want_channels 1 -> grey, 3 -> BGR interleaved.  *data is malloc'ed; release with disb200_free. */
 int disb200_read_pnm(const char* path, int want_channels, uint8_t** data, int* w, int* h);
+/* The same for PGM / PPM / PNG, chosen by the file's magic (PNG: non-interlaced, any colour type and bit
+ * depth, inflated with zlib; colour -> grey as OpenCV's PNG decoder does it for IMREAD_GRAYSCALE). */
+int disb200_read_image(const char* path, int want_channels, uint8_t** data, int* w, int* h);
 void disb200_free(void* p);
+
+/* Asynchronous writers: SaveFlowFile / SavePFMFile (run_dense.cpp:17-82) on a pool of host threads, so
+ * that the thread driving the GPU never waits for the disk.  submit copies the array (it may be reused at
+ * once) and blocks only while more than max_queued_bytes (0 = 1 GiB) wait to be written; wait returns the
+ * first error of the files submitted since the last wait. */
+typedef struct DisWriter DisWriter;
+int disb200_writer_create(int threads, size_t max_queued_bytes, DisWriter** out);
+int disb200_writer_submit_flo(DisWriter* w, const char* path, const float* flow, int width, int height, int nc);
+int disb200_writer_submit_pfm(DisWriter* w, const char* path, const float* disp, int width, int height);
+int disb200_writer_wait(DisWriter* w);
+void disb200_writer_destroy(DisWriter* w);
 
 const char* disb200_last_error(void);
 const char* disb200_version(void);

@@ -69,6 +69,7 @@ def lib():
         L.disb200_last_error.restype = C.c_char_p
         L.disb200_version.restype = C.c_char_p
         L.disb200_free.restype = None
+        L.disb200_writer_destroy.restype = None
         _lib = L
     return _lib
 
@@ -259,9 +260,50 @@ def save_pfm(path: str, disp: np.ndarray):
 
 
 def read_pnm(path: str, channels: int) -> np.ndarray:
+    return _read(lib().disb200_read_pnm, path, channels)
+
+
+def read_image(path: str, channels: int) -> np.ndarray:
+    """cv::imread stand-in (run_dense.cpp:209-210) for PGM / PPM / PNG: uint8 (h, w) grey or (h, w, 3) BGR."""
+    return _read(lib().disb200_read_image, path, channels)
+
+
+class Writer:
+    """Pool of host threads writing .flo / .pfm files (disb200_writer_*); submit copies and returns."""
+
+    def __init__(self, threads: int = 4, max_queued_bytes: int = 0):
+        self.w = C.c_void_p()
+        _check(lib().disb200_writer_create(threads, C.c_size_t(max_queued_bytes), C.byref(self.w)))
+
+    def submit_flo(self, path: str, flow: np.ndarray):
+        flow = np.ascontiguousarray(flow, np.float32)
+        h, w = flow.shape[:2]
+        _check(lib().disb200_writer_submit_flo(self.w, path.encode(), _ptr(flow), w, h, 1 if flow.ndim == 2 else flow.shape[2]))
+
+    def submit_pfm(self, path: str, disp: np.ndarray):
+        disp = np.ascontiguousarray(disp, np.float32)
+        h, w = disp.shape[:2]
+        _check(lib().disb200_writer_submit_pfm(self.w, path.encode(), _ptr(disp), w, h))
+
+    def wait(self):
+        _check(lib().disb200_writer_wait(self.w))
+
+    def close(self):
+        if self.w:
+            lib().disb200_writer_destroy(self.w)
+            self.w = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+
+def _read(fn, path: str, channels: int) -> np.ndarray:
     data = C.POINTER(C.c_uint8)()
     w, h = C.c_int(), C.c_int()
-    _check(lib().disb200_read_pnm(path.encode(), channels, C.byref(data), C.byref(w), C.byref(h)))
+    _check(fn(path.encode(), channels, C.byref(data), C.byref(w), C.byref(h)))
     n = w.value * h.value * channels
     arr = np.ctypeslib.as_array(data, shape=(n,)).copy()
     lib().disb200_free(data)

@@ -61,7 +61,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     with ThreadPoolExecutor(max_workers=8) as ex:
         objs = list(ex.map(compile_one, KERNEL_SOURCES))
     if force or _stale(LIB, objs):
-        r = subprocess.run([nvcc, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"],
+        r = subprocess.run([nvcc, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lz"],
                            capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("link failed:\n" + r.stderr)
@@ -78,6 +78,15 @@ def build(force: bool = False, verbose: bool = False) -> str:
                                    capture_output=True, text=True)
                 if r.returncode != 0:
                     raise RuntimeError("CLI build failed:\n" + r.stderr)
+    batch_src = os.path.join(CSRC, "run_batch.cpp")
+    if os.path.exists(batch_src):
+        exe = os.path.join(HERE, "bin", "disb200_batch")
+        os.makedirs(os.path.dirname(exe), exist_ok=True)
+        if force or _stale(exe, [batch_src, LIB] + headers):
+            r = subprocess.run(["g++", "-O2", "-std=c++17", "-pthread", batch_src, "-o", exe, "-L" + HERE, "-ldisb200",
+                                "-Wl,-rpath,$ORIGIN/.."], capture_output=True, text=True)
+            if r.returncode != 0:
+                raise RuntimeError("disb200_batch build failed:\n" + r.stderr)
     if verbose:
         for k, v in logs.items():
             sys.stderr.write("== %s ==\n%s\n" % (k, v))

@@ -8,7 +8,7 @@
 //   run_*_* img1 img2 out p1 ... p20       sc_f sc_l max_iter min_iter dp_thresh dr_thresh res_thresh
 //                                          patchsz overlap usefbcon patnorm costfct usetvref tv_alpha
 //                                          tv_gamma tv_delta tv_innerit tv_solverit tv_sor verbosity
-// Inputs are binary PGM / PPM (there is no OpenCV here to decode PNG/JPG: SURVEY.md 2 #12);
+// Inputs are binary PGM / PPM or PNG (disb200_read_image; there is no OpenCV here: SURVEY.md 2 #12);
 // output is .flo for optical flow and .pfm for depth-from-stereo (run_dense.cpp:418-422).
 // Unlike the reference, a short or malformed argument list is an error (the reference reads past
 // argv for argc in 6..23, run_dense.cpp:272-292) and every failure returns a non-zero status.
@@ -40,7 +40,7 @@ int main(int argc, char** argv) {
   const auto t_all = std::chrono::steady_clock::now();
   if (argc != 4 && argc != 5 && argc != 24) {
     std::fprintf(stderr,
-                 "usage: %s img1.p[gp]m img2.p[gp]m out.%s [oppoint 1..4 | sc_f sc_l max_iter min_iter dp_thresh "
+                 "usage: %s img1.{pgm,ppm,png} img2.{pgm,ppm,png} out.%s [oppoint 1..4 | sc_f sc_l max_iter min_iter dp_thresh "
                  "dr_thresh res_thresh patchsz overlap usefbcon patnorm costfct usetvref tv_alpha tv_gamma tv_delta "
                  "tv_innerit tv_solverit tv_sor verbosity]\n",
                  argv[0], SELECTMODE == 1 ? "flo" : "pfm");
@@ -50,10 +50,10 @@ int main(int argc, char** argv) {
   auto t0 = std::chrono::steady_clock::now();
   uint8_t *A = nullptr, *B = nullptr;
   int w0 = 0, h0 = 0, w1 = 0, h1 = 0;
-  int rc = disb200_read_pnm(argv[1], channels, &A, &w0, &h0);
-  if (rc) { std::fprintf(stderr, "cannot read %s (binary PGM/PPM expected)\n", argv[1]); return rc; }
-  rc = disb200_read_pnm(argv[2], channels, &B, &w1, &h1);
-  if (rc) { std::fprintf(stderr, "cannot read %s (binary PGM/PPM expected)\n", argv[2]); return rc; }
+  int rc = disb200_read_image(argv[1], channels, &A, &w0, &h0);
+  if (rc) { std::fprintf(stderr, "cannot read %s (binary PGM / PPM or non-interlaced PNG expected)\n", argv[1]); return rc; }
+  rc = disb200_read_image(argv[2], channels, &B, &w1, &h1);
+  if (rc) { std::fprintf(stderr, "cannot read %s (binary PGM / PPM or non-interlaced PNG expected)\n", argv[2]); return rc; }
   if (w0 != w1 || h0 != h1) { std::fprintf(stderr, "image sizes differ: %dx%d vs %dx%d\n", w0, h0, w1, h1); return 1; }
   const double ms_load = ms_since(t0);
 

@@ -295,6 +295,66 @@ def test_cli_matches_library(gpu, tmp_path):
     assert subprocess.run([os.path.join(exe_dir, "run_OF_INT"), "x", "y", "z", "1", "2", "3"], capture_output=True).returncode != 0
 
 
+def _write_png_grey(path, img):
+    """Minimal 8-bit grey PNG (filter 0), enough to feed the CLIs."""
+    import struct
+    import zlib
+
+    def chunk(tag, body):
+        return struct.pack(">I", len(body)) + tag + body + struct.pack(">I", zlib.crc32(tag + body) & 0xFFFFFFFF)
+    h, w = img.shape
+    raw = b"".join(b"\0" + img[y].tobytes() for y in range(h))
+    with open(path, "wb") as f:
+        f.write(b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, 8, 0, 0, 0, 0))
+                + chunk(b"IDAT", zlib.compress(raw)) + chunk(b"IEND", b""))
+
+
+def _read_flo(path, w, h):
+    raw = open(path, "rb").read()
+    assert raw[:4] == b"PIEH" and np.frombuffer(raw[4:12], np.int32).tolist() == [w, h]
+    return np.frombuffer(raw[12:], np.float32).reshape(h, w, 2)
+
+
+def test_batch_cli_png_in_flo_out_matches_library(gpu, tmp_path):
+    """disb200_batch: PNG decode -> batched flow (batches of 2, the last one ragged) -> writer pool, and the
+    --video form (one pyramid per frame); both bit-identical with the library calls they wrap."""
+    import subprocess
+    from of_dis_b200.synth import make_sequence
+    exe = os.path.join(ROOT, "of_dis_b200", "bin", "disb200_batch")
+    w0, h0 = 200, 120
+    pairs = [make_pair(h0, w0, seed=s)[:2] for s in range(5)]
+    lines = []
+    for i, (A, B) in enumerate(pairs):
+        _write_png_grey(tmp_path / ("a%d.png" % i), A)
+        _write_png_grey(tmp_path / ("b%d.png" % i), B)
+        lines.append("%s %s %s" % (tmp_path / ("a%d.png" % i), tmp_path / ("b%d.png" % i), tmp_path / ("o%d.flo" % i)))
+    (tmp_path / "list.txt").write_text("# five pairs\n" + "\n".join(lines) + "\n")
+    r = subprocess.run([exe, "--batch", "2", "--threads", "3", str(tmp_path / "list.txt"), "2"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    p = gpu.operating_point(2, w0, 1, 1).copy(verbosity=0)
+    with gpu.Handle(p, w0, h0, 5) as hd:
+        want = hd.run_host(np.stack([a for a, _ in pairs]), np.stack([b for _, b in pairs]))
+    for i in range(5):
+        assert np.array_equal(_read_flo(tmp_path / ("o%d.flo" % i), w0, h0), want[i]), i
+    # video: 6 frames -> 5 flows, chunks of 3 pairs
+    fr = make_sequence(h0, w0, 6, seed=1)
+    vl = []
+    for i, f in enumerate(fr):
+        _write_png_grey(tmp_path / ("f%d.png" % i), f)
+        vl.append("%s %s" % (tmp_path / ("f%d.png" % i), tmp_path / ("v%d.flo" % i)))
+    (tmp_path / "video.txt").write_text("\n".join(vl) + "\n")
+    r = subprocess.run([exe, "--video", "--batch", "3", str(tmp_path / "video.txt")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    with gpu.Handle(p, w0, h0, 5) as hd:
+        want = hd.run_sequence(np.stack(fr))
+    for i in range(5):
+        assert np.array_equal(_read_flo(tmp_path / ("v%d.flo" % i), w0, h0), want[i]), i
+    assert not (tmp_path / "v5.flo").exists()
+    # a missing input is an error, not a silent skip
+    (tmp_path / "bad.txt").write_text("%s %s %s\n" % (tmp_path / "a0.png", tmp_path / "nope.png", tmp_path / "x.flo"))
+    assert subprocess.run([exe, str(tmp_path / "bad.txt")], capture_output=True).returncode != 0
+
+
 def test_ncc_is_gain_invariant(gpu):
     """Second frame darkened by 30 % (+ offset): the NCC flow barely moves, the L2 flow does."""
     A, B, gt = make_pair(218, 512, seed=4)
