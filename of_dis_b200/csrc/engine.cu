@@ -528,7 +528,9 @@ int disb200_create(const DisParams* params, int w0, int h0, int max_batch, int d
   h->max_batch = max_batch;
   {
     const char* ev = getenv("DISB200_STREAMS");
-    int want = ev ? atoi(ev) : 1;
+    // two sub-batches on two streams overlap the tail of each kernel with the head of the next one of the other
+    // half: +3 % at 1480 pairs (234.7 k -> 242.5 k pairs/s); more streams or smaller batches do not pay
+    int want = ev ? atoi(ev) : (max_batch >= 1184 ? 2 : 1);
     h->nsub = std::max(1, std::min(std::min(want, 16), max_batch));
   }
   h->cap = (max_batch + h->nsub - 1) / h->nsub;
