@@ -317,11 +317,12 @@ def main():
         for k, v in hd.stage_ms().items():
             acc[k] = acc.get(k, 0.0) + v / 3
     hd.set_stage_timing(False)
-    acc["varref_other"] = acc.get("varref", 0.0) - acc.get("sor", 0.0)
-    stage_share = {k: acc[k] for k in ("pyramid", "inverse_search", "densify", "varref_other", "sor", "upsample")}
+    fused_tv = acc.get("system", 0.0) == 0.0 and acc.get("sor", 0.0) > 0.0     # small batches: one kernel per level
+    acc["varref_prep"] = acc.get("varref", 0.0) - acc.get("sor", 0.0) - acc.get("system", 0.0) - acc.get("smooth", 0.0)
+    stage_share = {k: acc.get(k, 0.0) for k in ("pyramid", "inverse_search", "densify", "varref_prep", "smooth", "system", "sor", "upsample")}
     step_ms = sum(stage_share.values())
     peak, peak_src = peaks()
-    # algorithmic bytes of each stage per pair (DESIGN.md "Kernels and their rooflines")
+    # algorithmic bytes of each kernel group per pair
     W, H = hd.W, hd.H
     lv = [(W >> l, H >> l, l) for l in range(p.sc_l, p.sc_f + 1)]
     pad = p.patchsz
@@ -330,6 +331,8 @@ def main():
     npatch = [int(np.ceil(w / steps_)) * int(np.ceil(h / steps_)) for w, h, _ in lv]
     novals = C_ * pad * pad
     ndir = 2 if p.usefbcon else 1
+    tv = 1 if p.usetvref else 0
+    n_in = lambda l: p.tv_innerit * (l + 1)                       # fixed-point iterations at level l (refine_variational.cpp:36)
     alg = {
         # read both u8 frames, write image + dx + dy of every level for both frames
         "pyramid": 2 * w0 * h0 * ch + sum(2 * 3 * 4 * ch * (w + 2 * pad) * (h + 2 * pad) for w, h, _ in lv),
@@ -337,16 +340,27 @@ def main():
         "inverse_search": ndir * sum(4 * 4 * ch * (w + 2 * pad) * (h + 2 * pad) + npatch[k] * 4 * (nop + 2 + novals)
                                      for k, (w, h, _) in enumerate(lv)),
         # patch results in, dense flow out
-        "densify": sum(npatch[k] * 4 * (nop + novals) + 4 * nop * w * h for k, (w, h, _) in enumerate(lv)),
-        # warp + derivatives once per level (2 images + flow in, 9C+1 planes out), then per fixed-point iteration
-        # 8C derivative planes + mask + flow + increment in, diffusivity + two float4 coefficient packs out;
-        # finally flow + increment in, flow out
-        "varref_other": sum(4 * w * h * ((2 * ch + nop) + (9 * ch + 1) + p.tv_innerit * (l + 1) * ((8 * ch + 1 + 2 * nop + 1) + 1 + 8)
-                                         + 3 * nop) for w, h, l in lv) if p.usetvref else 0,
+        "densify": ndir * sum(npatch[k] * 4 * (nop + novals) + 4 * nop * w * h for k, (w, h, _) in enumerate(lv)),
+        # warp + derivatives once per level (2 images + flow in, 9C+1 planes out), finish: flow + increment in, flow out
+        "varref_prep": tv * ndir * sum(4 * w * h * ((2 * ch + nop) + (9 * ch + 1) + 3 * nop) for w, h, l in lv),
+        # per fixed-point iteration: flow + increment in, diffusivity {h, v} out
+        "smooth": tv * ndir * sum(n_in(l) * 4 * w * h * (2 * nop + 2) for w, h, l in lv),
+        # per fixed-point iteration: 8C derivative planes + mask + diffusivity + flow + increment in, two float4 packs out
+        "system": tv * ndir * sum(n_in(l) * 4 * w * h * (8 * ch + 1 + 2 + 2 * nop + 8) for w, h, l in lv),
         "upsample": 4 * nop * lv[0][0] * lv[0][1] + 4 * nop * w0 * h0,
         # per sweep read 9 planes (a11 a12 a22 b1 b2 h v du dv), write 2 (DE: 5 + 1)
-        "sor": sum(p.tv_innerit * (l + 1) * p.tv_solverit * (4 * w * h) * (11 if nop == 2 else 6) for w, h, l in lv) if p.usetvref else 0,
+        "sor": tv * ndir * sum(n_in(l) * p.tv_solverit * (4 * w * h) * (11 if nop == 2 else 6) for w, h, l in lv),
     }
+    nl = len(lv) * ndir
+    n_it = ndir * sum(n_in(l) for _, _, l in lv)
+    kernels = {"pyramid": "downscale_u8_kernel + halve_kernel + sobel_pad_kernel", "inverse_search": "patch_search_kernel (%d launches)" % nl,
+               "densify": "densify_kernel (%d launches)" % nl, "varref_prep": "warp_kernel, deriv1_kernel, deriv2_kernel, finish_kernel (%d launches each)" % nl,
+               "smooth": "smooth_kernel2 (%d launches)" % n_it, "system": "system_kernel (%d launches)" % n_it,
+               "sor": ("tv_fused_kernel (%d launches: diffusivity + system + SOR of a level in one CTA per pair)" % nl) if fused_tv
+                      else "sor_warp_kernel / sor_band_kernel / sor_wavefront_kernel (%d launches)" % n_it,
+               "upsample": "upsample_crop_kernel (1 launch)"}
+    if fused_tv:
+        alg["sor"] += alg["smooth"] + alg["system"]
     dom = max(stage_share, key=stage_share.get)
     dom_ms = stage_share[dom]
     dom_bytes = alg.get(dom)
@@ -356,7 +370,7 @@ def main():
     if args.workload == "C1" and os.path.exists(tpath):
         with open(tpath) as f:
             traffic = {k: v["dram_read_bytes_per_pair"] + v["dram_write_bytes_per_pair"] for k, v in json.load(f)["per_stage"].items()}
-    roof = {"bound": "hbm", "kernel": dom, "unit": "GB/s", "peak": peak, "peak_source": peak_src,
+    roof = {"bound": "hbm", "kernel": kernels[dom], "stage": dom, "unit": "GB/s", "peak": peak, "peak_source": peak_src,
             "share_of_step": dom_ms / step_ms if step_ms else None,
             "traffic": traffic[dom] * nb if dom in traffic else None}
     if dom_bytes:

@@ -112,8 +112,8 @@ int disb200_timer_end(DisHandle* h, float* elapsed_ms);
 /* Kernels launched by the most recent run_batch* call on this handle. */
 int disb200_last_launch_count(const DisHandle* h);
 /* Device time in ms the most recent run spent in stage s (0 pyramid, 1 inverse search,
- * 2 densification, 3 variational refinement incl. SOR, 4 upsample, 5 the SOR kernel alone);
- * only recorded while
+ * 2 densification, 3 variational refinement as a whole, 4 upsample, and inside 3: 5 the SOR kernel
+ * (or the fused per-level kernel of small batches), 6 system_kernel, 7 smooth_kernel2); only recorded while
  * disb200_set_stage_timing(h, 1) is on (it serialises the stream with events). */
 int disb200_set_stage_timing(DisHandle* h, int on);
 int disb200_stage_ms(const DisHandle* h, int stage, float* ms);

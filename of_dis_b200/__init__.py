@@ -16,7 +16,7 @@ LIB_PATH = os.path.join(HERE, "libdisb200.so")
 
 MODE_OF, MODE_DE = 1, 2
 SOR_LEXICOGRAPHIC, SOR_REDBLACK = 0, 1
-STAGES = ("pyramid", "inverse_search", "densify", "varref", "upsample", "sor")
+STAGES = ("pyramid", "inverse_search", "densify", "varref", "upsample", "sor", "system", "smooth")
 
 
 class DisError(RuntimeError):

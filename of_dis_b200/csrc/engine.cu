@@ -113,7 +113,7 @@ struct Engine {
   LaunchStats stats{0, nullptr, nullptr};
   // stage timing
   bool stage_timing = false;
-  float stage_ms[6] = {0, 0, 0, 0, 0, 0};
+  float stage_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   std::vector<cudaEvent_t> ev_pool;
   struct Mark { int stage; cudaEvent_t a, b; };
   std::vector<Mark> marks;
@@ -717,7 +717,7 @@ int disb200_set_stage_timing(DisHandle* h, int on) {
   return DISB200_OK;
 }
 int disb200_stage_ms(const DisHandle* h, int stage, float* ms) {
-  if (!h || !ms || stage < 0 || stage > 5) return fail(DISB200_EINVAL, "bad argument");
+  if (!h || !ms || stage < 0 || stage > 7) return fail(DISB200_EINVAL, "bad argument");
   *ms = h->e.stage_ms[stage];
   return DISB200_OK;
 }

@@ -789,8 +789,11 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
   for (int it = 0; it < n_inner; ++it) {
     // (a fused diffusivity + system kernel over shared-memory tiles was measured slower: 2.00 vs 1.88 ms per
     //  1480-pair step; the halo re-evaluation and the barrier cost more than the 8 B / pixel they save)
+    if (ls->mark) ls->mark(ls->ctx, 7, 1);
     smooth_kernel2<OF><<<grd, blk, 0, st>>>(flow, vb.du, d, camlr, qa, it == 0, vb.smooth);
+    if (ls->mark) { ls->mark(ls->ctx, 7, 0); ls->mark(ls->ctx, 6, 1); }
     system_kernel<C, OF><<<grd, blk, 0, st>>>(D, vb.mask, vb.smooth, flow, vb.du, d, hd3, hg3, cA, cB);
+    if (ls->mark) ls->mark(ls->ctx, 6, 0);
     if (ls->mark) ls->mark(ls->ctx, 5, 1);
     if (p.sor_mode == DISB200_SOR_REDBLACK) {
       dim3 rblk(32, 4), rgrd((g.w / 2 + 1 + 31) / 32, (g.h + 3) / 4, n);
