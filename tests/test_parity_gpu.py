@@ -355,6 +355,27 @@ def test_batch_cli_png_in_flo_out_matches_library(gpu, tmp_path):
     assert subprocess.run([exe, str(tmp_path / "bad.txt")], capture_output=True).returncode != 0
 
 
+def test_band_sor_many_pairs_matches_general_wavefront(gpu, monkeypatch):
+    """Several pairs x several bands in one sor_band_kernel launch (ticket-ordered CTAs, one exchange region per
+    pair): the whole path with tall levels (400 and 200 rows) equals the run that forces the general wavefront,
+    for every pair, and repeated runs reuse the exchange rows under a new epoch without cross-talk."""
+    w0, h0, n = 208, 400, 5
+    pairs = [make_pair(h0, w0, seed=20 + s)[:2] for s in range(n)]
+    A, B = np.stack([a for a, _ in pairs]), np.stack([b for _, b in pairs])
+    p = gpu.operating_point(2, w0).copy(verbosity=0, sc_f=2, sc_l=0, usefbcon=1)
+    monkeypatch.setenv("DISB200_TV_PATH", "old")
+    with gpu.Handle(p, w0, h0, n) as hd:
+        want = hd.run_host(A, B)
+    monkeypatch.delenv("DISB200_TV_PATH")
+    with gpu.Handle(p, w0, h0, n) as hd:
+        got1 = hd.run_host(A, B)
+        got2 = hd.run_host(A[::-1].copy(), B[::-1].copy())[::-1]
+        got3 = hd.run_host(A[:2], B[:2])
+    assert np.array_equal(got1, want)
+    assert np.array_equal(got2, want)
+    assert np.array_equal(got3, want[:2])
+
+
 def test_ncc_is_gain_invariant(gpu):
     """Second frame darkened by 30 % (+ offset): the NCC flow barely moves, the L2 flow does."""
     A, B, gt = make_pair(218, 512, seed=4)
