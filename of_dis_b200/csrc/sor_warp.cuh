@@ -235,11 +235,7 @@ __device__ __forceinline__ void sor_warp(float* __restrict__ du, unsigned smem, 
         }
         N[b][s] = act ? nw : R[b][s];
         hp[b][s] = a[b][s].x;   // stale (zero before the row starts) when the pixel is out of range: multiplies a zero / unused left
-#ifdef SORW_NOSTORE
-        if (s == NS - 1 && act && nw.x == 123.456f) {
-#else
         if (s == NS - 1 && act) {
-#endif
           if (OF) *reinterpret_cast<float2*>(gD[b] - 4 * (NS - 1)) = nw;
           else gD[b][-2 * (NS - 1)] = nw.x;
         }

@@ -7,11 +7,13 @@
 //   warp_kernel     image_warp + the avg/Iz part of get_derivatives   (opticalflow_aux.c:33-99)
 //   deriv1_kernel   Ix Iy Ixz Iyz   (5-tap [1,-8,0,8,-1]/12, replicate border; image.cpp:467-640)
 //   deriv2_kernel   Ixx Ixy Iyy
-//   smooth_kernel   per-pixel diffusivity s of compute_smoothness     (opticalflow_aux.c:138-159)
+//   smooth_kernel2  diffusivities {h, v} of compute_smoothness        (opticalflow_aux.c:138-187)
 //   system_kernel   compute_data / compute_data_DE + sub_laplacian + the 2x2 block inverse of
 //                   sor_coupled's first sweep                          (opticalflow_aux.c:194-223,
 //                   409-747; solver.c:122-128)
-//   sor_*_kernel    lexicographic SOR as an anti-diagonal wavefront    (solver.c:83-471)
+//   sor_*_kernel    lexicographic SOR as an anti-diagonal wavefront    (solver.c:83-471): one warp per pair
+//                   (sor_warp.cuh), one warp per 32-row band (sor_band.cuh), general CTA wavefront; plus the
+//                   fused per-level kernel of small batches and the red-black variant
 //   finish_kernel   flow += increment (with the DE sign clamp)         (refine_variational.cpp:208-227,301-323)
 // The planes read by the refinement are the unpadded interiors of the padded pyramid arrays,
 // addressed in place (the reference copies them out first, refine_variational.cpp:120-149).
@@ -121,34 +123,6 @@ __device__ __forceinline__ void load_uv(const float* flow, const float* du, size
     u = camlr == 0 ? fminf(t, 0.f) : fmaxf(t, 0.f);
     v = 0.f;
   }
-}
-
-// compute_smoothness, first half: s = (alpha/4) / sqrt(ux^2+uy^2+vx^2+vy^2 + eps)
-template <bool OF>
-__global__ void smooth_kernel(const float* __restrict__ flow, const float* __restrict__ du, Dims d, int camlr,
-                              float quarter_alpha, int first_iter, float* __restrict__ s) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y, pair = blockIdx.z;
-  if (i >= d.w || j >= d.h) return;
-  constexpr int NOP = OF ? 2 : 1;
-  const float* fl = flow + (size_t)pair * d.w * d.h * NOP;
-  const float* q = du + (size_t)pair * d.plane * NOP;
-  const int xm = clampi(i - 1, 0, d.w - 1), xp = clampi(i + 1, 0, d.w - 1), ym = clampi(j - 1, 0, d.h - 1), yp = clampi(j + 1, 0, d.h - 1);
-  float ul, vl, uc, vc, ur, vr, ut, vt, ub, vb;
-  // first_iter: uu = wx exactly (memcpy in the reference, no clamp: refine_variational.cpp:189,288)
-  auto ld = [&](int x, int y, float& u, float& v) {
-    const size_t pix = (size_t)y * d.w + x;
-    if (first_iter) {
-      u = fl[pix * NOP];
-      v = OF ? fl[pix * NOP + 1] : 0.f;
-    } else {
-      load_uv<OF>(fl, q, pix, camlr, u, v);
-    }
-  };
-  ld(xm, j, ul, vl); ld(i, j, uc, vc); ld(xp, j, ur, vr); ld(i, ym, ut, vt); ld(i, yp, ub, vb);
-  const float ux = tap3(ul, uc, ur), vx = tap3(vl, vc, vr), uy = tap3(ut, uc, ub), vy = tap3(vt, vc, vb);
-  const float eps = 0.001f * 0.001f;
-  const float t = eps + ((ux * ux + uy * uy) + (vx * vx + vy * vy));
-  s[(size_t)pair * d.plane + (size_t)j * d.w + i] = quarter_alpha / sqrtf(t);
 }
 
 }  // namespace
@@ -596,7 +570,6 @@ __device__ __forceinline__ void sor_wavefront(float* du, const float4* cA, const
   }
 }
 
-#include "sor_lean.cuh"
 #include "sor_warp.cuh"
 #include "sor_band.cuh"
 
