@@ -40,6 +40,7 @@ WORKLOADS = {
 }
 C4_OVERRIDE = dict(sc_f=7, sc_l=2, max_iter=16, min_iter=16, patchsz=8, patove=0.4, usefbcon=1, costfct=1)
 N_DISTINCT = 4  # distinct synthetic pairs, tiled over the batch
+DEFAULT_BATCH = 1776  # 2 sub-batch streams x 6 resident one-warp SORs x 148 SMs
 
 
 def peaks():
@@ -195,7 +196,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--batch", type=int, default=1480, help="frame pairs per step per GPU (1480 = 10 resident SOR warps on each of the 148 SMs)")
+    ap.add_argument("--batch", type=int, default=None, help="frame pairs per step per GPU (default 1776 = two sub-batches of 6 resident SOR warps on each of the 148 SMs; C4: 16, C5: 256)")
     ap.add_argument("--workload", default="C1", choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU baseline sample budget per thread")
@@ -214,17 +215,19 @@ def main():
     p = dis.operating_point(op, w0, mode, ch).copy(verbosity=0)
     if args.workload == "C4":
         p = p.copy(**C4_OVERRIDE)
-        if args.batch == 1480:
+        if args.batch is None:
             args.batch = 16
     seq = args.workload == "C5"       # video: consecutive frames, pair i = (i, i+1), pyramids shared
     if seq:
         from of_dis_b200.synth import make_sequence
         fr = make_sequence(h0, w0, 5, seed=0)
         A, B, G = np.stack(fr[:-1]), np.stack(fr[1:]), None
-        if args.batch == 1480:
+        if args.batch is None:
             args.batch = 256          # BASELINE.json configs[4]: 256 consecutive pairs
     else:
         A, B, G = make_inputs(mode, ch, w0, h0)
+    if args.batch is None:
+        args.batch = DEFAULT_BATCH
     bytes_per_pair = 2 * w0 * h0 * ch + 4 * w0 * h0 * nop     # compulsory traffic of the whole path
     config = {"workload": "%s: %s, params %s" % (args.workload, desc, " ".join("%g" % v for v in p.cli_args())),
               "pairs_per_step_per_gpu": args.batch, "frame": [w0, h0, ch], "l2_policy": "inputs+outputs per step (%.0f MB) exceed the 126 MB L2" % (args.batch * bytes_per_pair / 1e6),

@@ -41,10 +41,12 @@ struct SorwCfg {
   static constexpr int RPX = NCH * 8;                // ring pixels per row
   static constexpr int LEADPX = NS <= 3 ? 4 : 8;     // request distance in pixels
   static constexpr int WAITN = LEADPX - 2;           // cp.async groups that may stay in flight
-  static constexpr int BAND_BYTES = 32 * RPX * (16 + 16 + 8);
+  static constexpr int ROW_BYTES = RPX * (16 + 16 + 8);   // one row's rings: cA, cB (float4) and the increment
 };
+// Rings exist for the h rows of the level only (not for whole 32-row bands): three regions, [h][RPX] each.
+// A 56-row level needs 35 KB instead of 40, which is the difference between 5 and 6 resident pairs per SM.
 __host__ __device__ inline size_t sorw_smem_bytes(int h, int ns) {
-  return (size_t)((h + 31) / 32) * (ns <= 3 ? SorwCfg<3>::BAND_BYTES : SorwCfg<5>::BAND_BYTES);
+  return (size_t)h * (ns <= 3 ? SorwCfg<3>::ROW_BYTES : SorwCfg<5>::ROW_BYTES);
 }
 
 __device__ __forceinline__ void sorw_cp16(unsigned smem_dst, const void* gsrc) {
@@ -117,6 +119,7 @@ __device__ __forceinline__ void sor_warp(float* __restrict__ du, unsigned smem, 
   constexpr int NOP = OF ? 2 : 1, RPX = Cfg::RPX, LEADPX = Cfg::LEADPX;
   const int lane = threadIdx.x & 31;
   const unsigned uw = (unsigned)w;
+  const unsigned offB = (unsigned)h * (RPX * 16u);       // cB region; the increment region starts at 2 offB
   const int T = w + h - 1 + 2 * (NS - 1);
   const int up = (lane + 31) & 31, dn = (lane + 1) & 31;
   const int cg = lane >> 3, ce = lane & 7;           // cooperative copies: row group, pixel in chunk
@@ -135,8 +138,8 @@ __device__ __forceinline__ void sor_warp(float* __restrict__ du, unsigned smem, 
     const bool row = j < h;
     i0[b] = row ? -j : -(1 << 28);
     mid[b] = j > 0 && j < h - 1;
-    rA[b] = smem + (unsigned)(b * Cfg::BAND_BYTES) + lane * (RPX * 16u);
-    rD[b] = smem + (unsigned)(b * Cfg::BAND_BYTES) + 32u * RPX * 32u + lane * (RPX * 8u);
+    rA[b] = smem + (unsigned)j * (RPX * 16u);            // rows >= h own no ring and never touch one
+    rD[b] = smem + 2u * offB + (unsigned)j * (RPX * 8u);
     const int jr = row ? j : 0;
     gD[b] = du + ((size_t)jr * w - jr) * NOP;
     cur0[b] = nr0[b] = make_float2(0.f, 0.f);
@@ -152,12 +155,11 @@ __device__ __forceinline__ void sor_warp(float* __restrict__ du, unsigned smem, 
     const int j = b * 32 + r, px = 8 * q + ce;
     if (q >= 0 && j < h && px < w) {
       const size_t g = (size_t)j * w + px;
-      const unsigned slot = (unsigned)(r * RPX + (px & (RPX - 1)));
-      const unsigned base = smem + (unsigned)(b * Cfg::BAND_BYTES);
-      sorw_cp16(base + slot * 16u, cA + g);
-      sorw_cp16(base + 32u * RPX * 16u + slot * 16u, cB + g);
-      if (OF) sorw_cp8(base + 32u * RPX * 32u + slot * 8u, du + g * 2);
-      else sorw_cp4(base + 32u * RPX * 32u + slot * 8u, du + g);
+      const unsigned slot = (unsigned)(j * RPX + (px & (RPX - 1)));
+      sorw_cp16(smem + slot * 16u, cA + g);
+      sorw_cp16(smem + offB + slot * 16u, cB + g);
+      if (OF) sorw_cp8(smem + 2u * offB + slot * 8u, du + g * 2);
+      else sorw_cp4(smem + 2u * offB + slot * 8u, du + g);
     }
   };
   // rows whose sweep-0 pixel is at a request point when the step counter is tn
@@ -176,7 +178,7 @@ __device__ __forceinline__ void sor_warp(float* __restrict__ du, unsigned smem, 
       if ((unsigned)i < uw) {
         const unsigned sc = rA[b] + ((unsigned)i & (RPX - 1)) * 16u;
         a[b][s] = sorw_lds128(sc);
-        c[b][s] = sorw_lds128(sc + 32u * RPX * 16u);
+        c[b][s] = sorw_lds128(sc + offB);
       }
     }
     // sweep 0: right neighbour (j, i0 + 1); pixel 0 also seeds the centre carry
@@ -196,6 +198,7 @@ __device__ __forceinline__ void sor_warp(float* __restrict__ du, unsigned smem, 
 #pragma unroll
   for (int b = 0; b < NB; ++b) fetch(b);
 
+#pragma unroll 2
   for (int t = 0; t < T; ++t) {
     // ---- neighbour exchange: results of step t-1 (sweep 0: the streamed increment) ----
     float2 top[NB][NS], bot[NB][NS];
