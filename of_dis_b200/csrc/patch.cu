@@ -7,10 +7,12 @@
 //   getPatchStaticBil / LossComputeErrorImage                           (patch.cpp:221-273,346-413)
 // A sub-warp of G lanes owns one patch; value n of the patch (row-major, channels
 // interleaved) lives in lane n % G, slot n / G, so that a load instruction of the group
-// touches consecutive floats of the target image.  When a patch row is exactly G values
-// (8x8 grey with G = 8) slot k is patch row k and the two lower bilinear taps of row k are
-// the two upper taps of row k+1, so each iteration loads 2 (PSZ + 1) values per lane instead
-// of 4 PSZ.  Template and gradients stay in registers; the residual is consumed on the fly
+// touches consecutive floats of the target image.  8x8 grey patches (op1 / op2) use the
+// column-pair mapping instead: 4 lanes per patch, a lane owns two adjacent columns, three
+// taps per row serve both of them and the lower taps of one row are the upper taps of the
+// next, so an iteration loads 3 (PSZ + 1) values for 16 results (a plain mapping loads 64)
+// and the scalar part of the iteration (solve, bounds, bookkeeping) is shared by 8 patches
+// per warp instead of 4: 31 % fewer warp instructions per patch than the 8-lane row mapping.  Template and gradients stay in registers; the residual is consumed on the fly
 // (its projections on the steepest-descent images and its weight sum are all the next
 // iteration needs) and the per-pixel weights are written once, by the evaluation that ends
 // the search.  Reductions are xor-butterflies, which leave every lane with the bit-identical
@@ -35,6 +37,29 @@ __device__ __forceinline__ float gsum(float v) {
   return v;
 }
 
+// Partial sums of one lane and their reduction over the group.  CP (column-pair mapping: a lane owns two
+// adjacent columns of the patch, slot k = 2 * row + parity) keeps one accumulator per column and combines
+// them in the order of the 8-lane butterfly — (c, c^4), then (c, c^2), then even + odd — so that a
+// 4-lane group produces the same bits as the 8-lane mapping it replaces (and as the reference's packet sums).
+template <int G, bool CP>
+struct PSum {
+  float a0 = 0.f, a1 = 0.f;
+  __device__ __forceinline__ void add(int k, float v) {
+    if (CP && (k & 1)) a1 += v;
+    else a0 += v;
+  }
+  __device__ __forceinline__ float total() const {
+    if (!CP) return gsum<G>(a0);
+    float r0 = a0, r1 = a1;
+#pragma unroll
+    for (int m = G / 2; m > 0; m >>= 1) {
+      r0 += __shfl_xor_sync(0xffffffffu, r0, m);
+      r1 += __shfl_xor_sync(0xffffffffu, r1, m);
+    }
+    return r0 + r1;
+  }
+};
+
 // LossComputeErrorImage for one value (patch.cpp:221-273): d = query - template
 template <int COST>
 __device__ __forceinline__ void loss(float d, float bsq, float bsq2, float& pd, float& pw) {
@@ -51,7 +76,7 @@ __device__ __forceinline__ void loss(float d, float bsq, float bsq2, float& pd, 
 }
 
 template <int PSZ, int C, int G, bool OF>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128)   // (capping the column-pair variant at 96 registers for 5 CTAs per SM spills inside the loop: 1.60 -> 2.00 ms)
 patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
   constexpr int NV = PSZ * PSZ * C;
   constexpr int VPL = (NV + G - 1) / G;
@@ -60,6 +85,8 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
   constexpr int NOP = OF ? 2 : 1;
   constexpr bool FULL = (NV % G) == 0;       // every slot of every lane holds a value
   constexpr bool ROWMAP = ROWLEN == G;       // slot k == patch row k
+  constexpr bool CP = C == 1 && ROWLEN == 2 * G && FULL;   // slot k == (row k / 2, column 2 lane + k % 2)
+  typedef PSum<G, CP> Sum;
 
   const int lane = threadIdx.x % G;
   const int ip_raw = blockIdx.x * (blockDim.x / G) + threadIdx.x / G;
@@ -86,7 +113,7 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
     val[k] = FULL || n < NV;
     const int nn = val[k] ? n : 0;
     const int row = nn / ROWLEN;
-    off[k] = ROWMAP ? k * rowstride + lane : row * rowstride + (nn - row * ROWLEN);
+    off[k] = ROWMAP ? k * rowstride + lane : CP ? (k >> 1) * rowstride + 2 * lane + (k & 1) : row * rowstride + (nn - row * ROWLEN);
   }
 
   // ---- template, gradients, Hessian (patch.cpp:298-343, 69-86) ----
@@ -94,16 +121,16 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
   {
     const int px = (int)ptrx + g.pad + LB, py = (int)ptry + g.pad + LB;
     const int base = (py * g.tw + px) * C;
-    float s = 0.f;
+    Sum s;
 #pragma unroll
     for (int k = 0; k < VPL; ++k) {
       t[k] = val[k] ? __ldg(timg + base + off[k]) : 0.f;
       dx[k] = val[k] ? __ldg(tdxp + base + off[k]) : 0.f;
       dy[k] = (OF && val[k]) ? __ldg(tdyp + base + off[k]) : 0.f;
-      s += t[k];
+      s.add(k, t[k]);
     }
     if (o.patnorm > 0 || o.costfct == 10) {
-      const float m = mean_of<NV>(gsum<G>(s));
+      const float m = mean_of<NV>(s.total());
 #pragma unroll
       for (int k = 0; k < VPL; ++k) t[k] = val[k] ? t[k] - m : 0.f;
     }
@@ -111,22 +138,24 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
   // NCC (costfct 10; defined by this build, the reference has no branch for it: DESIGN.md "NCC"): |t^|
   float tnorm = 0.f;
   if (o.costfct == 10) {
-    float s2 = 0.f;
+    Sum s2;
 #pragma unroll
-    for (int k = 0; k < VPL; ++k) s2 += t[k] * t[k];
-    tnorm = sqrtf(gsum<G>(s2));
+    for (int k = 0; k < VPL; ++k) s2.add(k, t[k] * t[k]);
+    tnorm = sqrtf(s2.total());
   }
-  float H00 = 0.f, H01 = 0.f, H11 = 0.f;
+  float H00, H01 = 0.f, H11 = 0.f;
+  {
+    Sum h00, h01, h11;
 #pragma unroll
-  for (int k = 0; k < VPL; ++k) {
-    H00 += dx[k] * dx[k];
-    if (OF) { H01 += dx[k] * dy[k]; H11 += dy[k] * dy[k]; }
+    for (int k = 0; k < VPL; ++k) {
+      h00.add(k, dx[k] * dx[k]);
+      if (OF) { h01.add(k, dx[k] * dy[k]); h11.add(k, dy[k] * dy[k]); }
+    }
+    H00 = h00.total();
+    if (OF) { H01 = h01.total(); H11 = h11.total(); }
   }
-  H00 = gsum<G>(H00);
   float l00, l10 = 0.f, l11 = 1.f;
   if (OF) {
-    H01 = gsum<G>(H01);
-    H11 = gsum<G>(H11);
     if (H00 * H11 - H01 * H01 == 0.f) { H00 = (float)((double)H00 + 1e-10); H11 = (float)((double)H11 + 1e-10); }
     // Eigen LLT, unblocked: stop at the first non-positive pivot, rest left unfactored
     l00 = H00; l10 = H01; l11 = H11;
@@ -167,7 +196,7 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
     // defined as 0
 #pragma unroll
     for (int k = 0; k < VPL; ++k)
-      if (val[k]) wout[k * G + lane] = 0.f;
+      if (val[k]) wout[CP ? (k >> 1) * ROWLEN + 2 * lane + (k & 1) : k * G + lane] = 0.f;
   }
 
   const float bsq = o.normoutlier * o.normoutlier, bsq2 = bsq * 2.0f;
@@ -211,15 +240,28 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
     const float w0 = rx * ry, w1 = (1.f - rx) * ry, w2 = rx * (1.f - ry), w3 = (1.f - rx) * (1.f - ry);
     const float* qb = qimg + ((iy1 + g.pad + LB) * g.tw + (ix1 + g.pad + LB)) * C;
     float q[VPL];
-    float qs = 0.f;
-    if (ROWMAP) {
+    Sum qs;
+    if (CP) {
+      // three taps per row serve both columns of the lane; the lower row of one step is the upper row of the next
+      const float* p = qb + 2 * lane;
+      float u0 = __ldg(p - rowstride - 1), u1 = __ldg(p - rowstride), u2 = __ldg(p - rowstride + 1);
+#pragma unroll
+      for (int r = 0; r < VPL / 2; ++r) {
+        const float l0 = __ldg(p + r * rowstride - 1), l1 = __ldg(p + r * rowstride), l2 = __ldg(p + r * rowstride + 1);
+        q[2 * r] = w0 * l1 + w1 * l0 + w2 * u1 + w3 * u0;
+        q[2 * r + 1] = w0 * l2 + w1 * l1 + w2 * u2 + w3 * u1;
+        qs.add(2 * r, q[2 * r]);
+        qs.add(2 * r + 1, q[2 * r + 1]);
+        u0 = l0; u1 = l1; u2 = l2;
+      }
+    } else if (ROWMAP) {
       const float* p = qb + lane;
       float vc = __ldg(p - rowstride), vd = __ldg(p - rowstride - C);
 #pragma unroll
       for (int k = 0; k < VPL; ++k) {
         const float va = __ldg(p + k * rowstride), vb = __ldg(p + k * rowstride - C);
         q[k] = w0 * va + w1 * vb + w2 * vc + w3 * vd;
-        qs += q[k];
+        qs.add(k, q[k]);
         vc = va;
         vd = vb;
       }
@@ -229,12 +271,12 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
         const float* p = qb + off[k];
         const float va = __ldg(p), vb = __ldg(p - C), vc = __ldg(p - rowstride), vd = __ldg(p - rowstride - C);
         q[k] = val[k] ? w0 * va + w1 * vb + w2 * vc + w3 * vd : 0.f;
-        qs += q[k];
+        qs.add(k, q[k]);
       }
     }
     float m = 0.f;
-    if (o.patnorm > 0 || o.costfct == 10) m = mean_of<NV>(gsum<G>(qs));
-    float ns0 = 0.f, ns1 = 0.f, wsum = 0.f;
+    if (o.patnorm > 0 || o.costfct == 10) m = mean_of<NV>(qs.total());
+    Sum as0, as1, aws;
     float npw[VPL];
 #define DISB200_RESIDUAL(COST, QV)                                 \
   _Pragma("unroll") for (int k = 0; k < VPL; ++k) {              \
@@ -242,16 +284,16 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
     loss<COST>(QV - t[k], bsq, bsq2, vpd, vpw);                  \
     if (!FULL && !val[k]) { vpd = 0.f; vpw = 0.f; }              \
     npw[k] = vpw;                                                \
-    ns0 += dx[k] * vpd;                                          \
-    if (OF) ns1 += dy[k] * vpd;                                  \
-    wsum += fabsf(vpw);                                          \
+    as0.add(k, dx[k] * vpd);                                     \
+    if (OF) as1.add(k, dy[k] * vpd);                             \
+    aws.add(k, fabsf(vpw));                                      \
   }
     float qscale = 1.0f;
     if (o.costfct == 10) {           // r = q^ * (|t^| / |q^|) - t^
-      float s2 = 0.f;
+      Sum s2;
 #pragma unroll
-      for (int k = 0; k < VPL; ++k) s2 += val[k] ? (q[k] - m) * (q[k] - m) : 0.f;
-      const float qn = sqrtf(gsum<G>(s2));
+      for (int k = 0; k < VPL; ++k) s2.add(k, val[k] ? (q[k] - m) * (q[k] - m) : 0.f);
+      const float qn = sqrtf(s2.total());
       qscale = qn > 0.f ? tnorm / qn : 0.f;
     }
     if (o.costfct == 0) { DISB200_RESIDUAL(0, (q[k] - m)) }
@@ -259,9 +301,9 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
     else if (o.costfct == 1) { DISB200_RESIDUAL(1, (q[k] - m)) }
     else { DISB200_RESIDUAL(2, (q[k] - m)) }
 #undef DISB200_RESIDUAL
-    ns0 = gsum<G>(ns0);
-    if (OF) ns1 = gsum<G>(ns1);
-    wsum = gsum<G>(wsum);
+    const float ns0 = as0.total();
+    const float ns1 = OF ? as1.total() : 0.f;
+    const float wsum = aws.total();
     if (upd) {
       // OptimizeComputeErrImg bookkeeping (patch.cpp:283-293)
       const float dpsq = OF ? ndp0 * ndp0 + ndp1 * ndp1 : ndp0 * ndp0;
@@ -280,7 +322,7 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
       if (nconv && active) {   // this evaluation is the patch's last one: its weights are the result
 #pragma unroll
         for (int k = 0; k < VPL; ++k)
-          if (val[k]) wout[k * G + lane] = npw[k];
+          if (val[k]) wout[CP ? (k >> 1) * ROWLEN + 2 * lane + (k & 1) : k * G + lane] = npw[k];
       }
     }
     first = false;
@@ -309,7 +351,7 @@ bool launch_patch_search(const PatchArgs& a, const LevelGeom& g, const OptConst&
   const int key = o.psz * 10 + o.noc;
   switch (key) {
     case 41: launch_one<4, 1, 8>(a, g, o, n, s); break;
-    case 81: launch_one<8, 1, 8>(a, g, o, n, s); break;
+    case 81: launch_one<8, 1, 4>(a, g, o, n, s); break;
     case 121: launch_one<12, 1, 16>(a, g, o, n, s); break;
     case 161: launch_one<16, 1, 32>(a, g, o, n, s); break;
     case 43: launch_one<4, 3, 8>(a, g, o, n, s); break;
