@@ -44,7 +44,19 @@ downscale_u8_kernel(const uint8_t* __restrict__ framesA, const uint8_t* __restri
   const bool fast = C == 1 && k >= 4 && xs >= 0 && xs + k <= w0 && ((xs & 3) == 0) && ((w0 & 3) == 0) &&
                     ((((size_t)f) & 3) == 0);
   const bool fast8 = fast && k >= 8 && ((xs & 7) == 0) && ((w0 & 7) == 0) && ((((size_t)f) & 7) == 0);
-  if (fast8) {                     // 64-bit loads: one per 8 source pixels
+  if (fast8 && k == 8) {           // the 8x8 block of level 3: all eight 64-bit loads in flight at once
+    uint2 v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      v[j] = __ldg(reinterpret_cast<const uint2*>(f + (size_t)clampi(y * 8 + j - padt, 0, h0 - 1) * w0 + xs));
+    unsigned s1 = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      sum[0] = __dp4a(v[j].x, 0x01010101u, sum[0]);
+      s1 = __dp4a(v[j].y, 0x01010101u, s1);
+    }
+    sum[0] += s1;
+  } else if (fast8) {              // 64-bit loads: one per 8 source pixels
     unsigned s1 = 0;
 #pragma unroll 4
     for (int j = 0; j < k; ++j) {

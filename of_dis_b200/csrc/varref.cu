@@ -616,6 +616,81 @@ __global__ void sor_redblack_kernel(float* __restrict__ du_all, const float4* __
   st_du<OF>(du, pix, sor_update<OF>(cA, cB, hl, i > 0, rowtype, omega, left, cur, r, t, bt));
 }
 
+// The same diffusivity for four consecutive pixels of a row per thread (rows whose width is a multiple of 4):
+// the centre row is read once for the six horizontal neighbours, vector loads replace ten scalar ones per
+// pixel, and the per-pixel arithmetic is literally smooth_pixel's.
+template <bool OF>
+__global__ void smooth_kernel4(const float* __restrict__ flow, const float* __restrict__ du, Dims d, int camlr,
+                               float quarter_alpha, int first_iter, float* __restrict__ s) {
+  constexpr int NOP = OF ? 2 : 1;
+  const int i0 = 4 * (blockIdx.x * blockDim.x + threadIdx.x), j = blockIdx.y * blockDim.y + threadIdx.y, pair = blockIdx.z;
+  if (i0 >= d.w || j >= d.h) return;
+  const float* fl = flow + (size_t)pair * d.w * d.h * NOP;
+  const float* q = du + (size_t)pair * d.plane * NOP;
+  const bool fi = first_iter != 0;
+  // uu / vv of the four pixels starting at (x, y); x is a multiple of 4
+  auto ld4 = [&](int x, int y, float (&u)[4], float (&v)[4]) {
+    const size_t pix = (size_t)y * d.w + x;
+    if (OF) {
+      const float4 a = *reinterpret_cast<const float4*>(fl + pix * 2), b = *reinterpret_cast<const float4*>(fl + pix * 2 + 4);
+      u[0] = a.x; v[0] = a.y; u[1] = a.z; v[1] = a.w; u[2] = b.x; v[2] = b.y; u[3] = b.z; v[3] = b.w;
+      if (!fi) {
+        const float4 c = *reinterpret_cast<const float4*>(q + pix * 2), e = *reinterpret_cast<const float4*>(q + pix * 2 + 4);
+        u[0] = u[0] + c.x; v[0] = v[0] + c.y; u[1] = u[1] + c.z; v[1] = v[1] + c.w;
+        u[2] = u[2] + e.x; v[2] = v[2] + e.y; u[3] = u[3] + e.z; v[3] = v[3] + e.w;
+      }
+    } else {
+      const float4 a = *reinterpret_cast<const float4*>(fl + pix);
+      u[0] = a.x; u[1] = a.y; u[2] = a.z; u[3] = a.w;
+      if (!fi) {
+        const float4 c = *reinterpret_cast<const float4*>(q + pix);
+        const float t0 = u[0] + c.x, t1 = u[1] + c.y, t2 = u[2] + c.z, t3 = u[3] + c.w;
+        u[0] = camlr == 0 ? fminf(t0, 0.f) : fmaxf(t0, 0.f);
+        u[1] = camlr == 0 ? fminf(t1, 0.f) : fmaxf(t1, 0.f);
+        u[2] = camlr == 0 ? fminf(t2, 0.f) : fmaxf(t2, 0.f);
+        u[3] = camlr == 0 ? fminf(t3, 0.f) : fmaxf(t3, 0.f);
+      }
+      v[0] = v[1] = v[2] = v[3] = 0.f;
+    }
+  };
+  auto ld1 = [&](int x, int y, float& u, float& v) {
+    const int pix = y * d.w + x;
+    if (OF) {
+      const float2 a = *reinterpret_cast<const float2*>(fl + (size_t)pix * 2);
+      u = a.x; v = a.y;
+      if (!fi) { const float2 c = *reinterpret_cast<const float2*>(q + (size_t)pix * 2); u = u + c.x; v = v + c.y; }
+    } else {
+      u = fl[pix];
+      if (!fi) { const float t = u + q[pix]; u = camlr == 0 ? fminf(t, 0.f) : fmaxf(t, 0.f); }
+      v = 0.f;
+    }
+  };
+  float uc[6], vc[6], ut[4], vt[4], ub[4], vb[4];
+  {
+    float u4[4], v4[4];
+    ld4(i0, j, u4, v4);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { uc[k + 1] = u4[k]; vc[k + 1] = v4[k]; }
+  }
+  if (i0 > 0) ld1(i0 - 1, j, uc[0], vc[0]);
+  else { uc[0] = uc[1]; vc[0] = vc[1]; }                    // xm = max(i - 1, 0)
+  if (i0 + 4 < d.w) ld1(i0 + 4, j, uc[5], vc[5]);
+  else { uc[5] = uc[4]; vc[5] = vc[4]; }                    // xp = min(i + 1, w - 1)
+  ld4(i0, max(j - 1, 0), ut, vt);
+  ld4(i0, min(j + 1, d.h - 1), ub, vb);
+  const float eps = 0.001f * 0.001f;
+  float4 out;
+  float* o = &out.x;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const float ux = tap3(uc[k], uc[k + 1], uc[k + 2]), vx = tap3(vc[k], vc[k + 1], vc[k + 2]);
+    const float uy = tap3(ut[k], uc[k + 1], ub[k]), vy = tap3(vt[k], vc[k + 1], vb[k]);
+    const float t = eps + ((ux * ux + uy * uy) + (vx * vx + vy * vy));
+    o[k] = quarter_alpha / sqrtf(t);
+  }
+  *reinterpret_cast<float4*>(s + (size_t)pair * d.plane + (size_t)j * d.w + i0) = out;
+}
+
 template <bool OF>
 __global__ void smooth_kernel2(const float* __restrict__ flow, const float* __restrict__ du, Dims d, int camlr,
                                float quarter_alpha, int first_iter, float* __restrict__ s) {
@@ -759,11 +834,15 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
   if (sorw) cudaFuncSetAttribute(sorw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sorw_smem);
   int threads = pipelined ? g.h * p.tv_solverit : (g.h < 512 ? g.h : 512);
   threads = ((threads + 31) / 32) * 32;
+  // four pixels per thread need 16-byte aligned rows in every plane: w % 4 == 0 (plane_cap is a multiple of 4)
+  const bool smooth4 = (g.w & 3) == 0 && (vb.plane_cap & 3) == 0;
+  const dim3 grd4((g.w / 4 + 31) / 32, (g.h + 3) / 4, n);
   for (int it = 0; it < n_inner; ++it) {
     // (a fused diffusivity + system kernel over shared-memory tiles was measured slower: 2.00 vs 1.88 ms per
     //  1480-pair step; the halo re-evaluation and the barrier cost more than the 8 B / pixel they save)
     if (ls->mark) ls->mark(ls->ctx, 7, 1);
-    smooth_kernel2<OF><<<grd, blk, 0, st>>>(flow, vb.du, d, camlr, qa, it == 0, vb.smooth);
+    if (smooth4) smooth_kernel4<OF><<<grd4, blk, 0, st>>>(flow, vb.du, d, camlr, qa, it == 0, vb.smooth);
+    else smooth_kernel2<OF><<<grd, blk, 0, st>>>(flow, vb.du, d, camlr, qa, it == 0, vb.smooth);
     if (ls->mark) { ls->mark(ls->ctx, 7, 0); ls->mark(ls->ctx, 6, 1); }
     system_kernel<C, OF><<<grd, blk, 0, st>>>(D, vb.mask, vb.smooth, flow, vb.du, d, hd3, hg3, cA, cB);
     if (ls->mark) ls->mark(ls->ctx, 6, 0);
