@@ -416,6 +416,37 @@ def main():
         e2e = {"value": pairs / dt, "unit": "pairs/s", "h2d_bytes_per_step": ((nb + 1) if seq else 2 * nb) * w0 * h0 * ch * world,
                "d2h_bytes_per_step": nb * w0 * h0 * nop * 4 * world, "checksum": float(hOut[0].double().abs().mean())}
 
+    # The same call through the OFClass cut (u8 frames in, level-sc_l flow out: what OFC::OFClass writes to `outflow`,
+    # oflow.h:105; the x 2^sc_l resize of run_dense.cpp:407-415 is left to the consumer).  Not the headline: it shows
+    # what is left of the end-to-end cost once the full-resolution f32 flow (80 % of the compulsory bytes) does not
+    # have to cross PCIe.
+    e2e_low = None
+    if not args.no_e2e:
+        hl, wl, _ = hd.lowres_dims()
+        hLow = torch.empty((nb, hl, wl, nop), dtype=torch.float32).pin_memory()
+
+        def host_call_low():
+            if seq:
+                hd.run_sequence_host_lowres_ptr(hF.data_ptr(), nb + 1, hLow.data_ptr())
+            else:
+                hd.run_host_lowres_ptr(hA.data_ptr(), hB.data_ptr(), nb, hLow.data_ptr())
+
+        for _ in range(2):
+            host_call_low()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            host_call_low()
+        barrier()
+        dt = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([dt], device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        e2e_low = {"value": pairs / dt, "unit": "pairs/s", "what": "u8 frames in, level-sc_l flow out (OFClass outflow, %dx%dx%d f32 per pair)" % (wl, hl, nop),
+                   "h2d_bytes_per_step": e2e["h2d_bytes_per_step"], "d2h_bytes_per_step": nb * hl * wl * nop * 4 * world,
+                   "checksum": float(hLow[0].double().abs().mean())}
+
     cpu = parity = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
@@ -428,7 +459,7 @@ def main():
                 "n_gpus": world, "steps": args.steps, "warmup": W_, "ms_per_step": ms / args.steps,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic warped-texture pairs (%d distinct seeds tiled over the batch)" % len(A),
-                "config": config, "clocks": clocks, "e2e": e2e, "gpu_launches": launches_per_step * args.steps,
+                "config": config, "clocks": clocks, "e2e": e2e, "e2e_ofclass_cut": e2e_low, "gpu_launches": launches_per_step * args.steps,
                 "roofline": roof, "cpu_baseline": cpu, "parity": parity}
         print(json.dumps(line))
     hd.close()

@@ -63,6 +63,9 @@ typedef struct DisParams {
   int mode;          /* DISB200_MODE_OF | DISB200_MODE_DE  (SELECTMODE)        */
   int channels;      /* 1 grey | 3 BGR interleaved        (SELECTCHANNEL)     */
   int sor_mode;      /* DISB200_SOR_LEXICOGRAPHIC (parity with solver.c:83-433) | _REDBLACK */
+  int gradmag;       /* 1: SELECTCHANNEL == 2 — the grey frame is replaced by the magnitude of its Sobel/8
+                        gradient before the pyramid is built (run_dense.cpp:139-148); needs channels == 1.
+                        0: the frame is used as given (SELECTCHANNEL 1 | 3) */
 } DisParams;
 
 typedef struct DisHandle DisHandle;
@@ -94,6 +97,15 @@ int disb200_run_batch(DisHandle* h, const uint8_t* const* imgA, const uint8_t* c
  * overlap compute. */
 int disb200_run_batch_host(DisHandle* h, const uint8_t* A, const uint8_t* B, int n, float* out);
 
+/* The OFClass cut with u8 frames in: same pipeline, but the result is what OFC::OFClass writes to
+ * `outflow` (oflow.h:105, run_dense.cpp:385-401) — the flow of level sc_l, (H >> sc_l) x (W >> sc_l) x nop
+ * f32 per pair in level-sc_l pixel units — i.e. without the `flow *= 2^sc_l; cv::resize; crop` of
+ * run_dense.cpp:407-415.  For consumers that keep working on the GPU grid or upsample on their side: at
+ * op2 it moves 64 x fewer bytes to the host than the full-resolution flow, which is what bounds
+ * disb200_run_batch_host (PCIe).  disb200_lowres_dims reports the per-pair shape. */
+int disb200_run_batch_host_lowres(DisHandle* h, const uint8_t* A, const uint8_t* B, int n, float* out_low);
+int disb200_lowres_dims(const DisHandle* h, int* w_l, int* h_l, int* nop);
+
 /* Device-resident batch (n <= max_batch): dA, dB, dOut are device pointers laid out as above.
  * Asynchronous on the handle's stream; call disb200_sync before reading dOut. */
 int disb200_run_batch_device(DisHandle* h, const uint8_t* dA, const uint8_t* dB, int n, float* dOut);
@@ -105,6 +117,7 @@ int disb200_sync(DisHandle* h);
  * run_batch* on the explicit pairs.  _device: nframes-1 <= max_batch, asynchronous like run_batch_device. */
 int disb200_run_sequence_device(DisHandle* h, const uint8_t* dFrames, int nframes, float* dOut);
 int disb200_run_sequence_host(DisHandle* h, const uint8_t* frames, int nframes, float* out);
+int disb200_run_sequence_host_lowres(DisHandle* h, const uint8_t* frames, int nframes, float* out_low);
 
 /* CUDA-event stopwatch on the handle's stream (the stream every kernel is launched on). */
 int disb200_timer_begin(DisHandle* h);

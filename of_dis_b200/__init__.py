@@ -34,7 +34,7 @@ class DisParams(C.Structure):
         ("usefbcon", C.c_int), ("patnorm", C.c_int), ("costfct", C.c_int), ("usetvref", C.c_int),
         ("tv_alpha", C.c_float), ("tv_gamma", C.c_float), ("tv_delta", C.c_float),
         ("tv_innerit", C.c_int), ("tv_solverit", C.c_int), ("tv_sor", C.c_float),
-        ("verbosity", C.c_int), ("mode", C.c_int), ("channels", C.c_int), ("sor_mode", C.c_int),
+        ("verbosity", C.c_int), ("mode", C.c_int), ("channels", C.c_int), ("sor_mode", C.c_int), ("gradmag", C.c_int),
     ]
 
     def copy(self, **kw):
@@ -145,6 +145,36 @@ class Handle:
             out = np.empty((nf - 1, self.h0, self.w0, self.p.nop), np.float32)
         _check(lib().disb200_run_sequence_host(self.h, _ptr(frames, C.c_uint8), nf, _ptr(out)))
         return out
+
+    def lowres_dims(self):
+        """(h_l, w_l, nop) of the level-sc_l flow that the *_lowres entry points return (OFClass's outflow, oflow.h:105)."""
+        w, h, nop = C.c_int(), C.c_int(), C.c_int()
+        _check(lib().disb200_lowres_dims(self.h, C.byref(w), C.byref(h), C.byref(nop)))
+        return h.value, w.value, nop.value
+
+    def run_host_lowres(self, A: np.ndarray, B: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
+        """Like run_host, but returns the flow of level sc_l (n, H >> sc_l, W >> sc_l, nop) in level pixel units."""
+        n = A.shape[0]
+        assert A.dtype == np.uint8 and B.dtype == np.uint8 and A.flags.c_contiguous and B.flags.c_contiguous
+        assert A.size == n * self.h0 * self.w0 * self.p.channels and B.shape == A.shape
+        if out is None:
+            out = np.empty((n,) + self.lowres_dims(), np.float32)
+        _check(lib().disb200_run_batch_host_lowres(self.h, _ptr(A, C.c_uint8), _ptr(B, C.c_uint8), n, _ptr(out)))
+        return out
+
+    def run_sequence_lowres(self, frames: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
+        nf = frames.shape[0]
+        assert frames.dtype == np.uint8 and frames.flags.c_contiguous and frames.size == nf * self.h0 * self.w0 * self.p.channels
+        if out is None:
+            out = np.empty((nf - 1,) + self.lowres_dims(), np.float32)
+        _check(lib().disb200_run_sequence_host_lowres(self.h, _ptr(frames, C.c_uint8), nf, _ptr(out)))
+        return out
+
+    def run_host_lowres_ptr(self, a_ptr: int, b_ptr: int, n: int, out_ptr: int):
+        _check(lib().disb200_run_batch_host_lowres(self.h, C.c_void_p(a_ptr), C.c_void_p(b_ptr), n, C.c_void_p(out_ptr)))
+
+    def run_sequence_host_lowres_ptr(self, frames_ptr: int, nframes: int, out_ptr: int):
+        _check(lib().disb200_run_sequence_host_lowres(self.h, C.c_void_p(frames_ptr), nframes, C.c_void_p(out_ptr)))
 
     def run_sequence_host_ptr(self, frames_ptr: int, nframes: int, out_ptr: int):
         _check(lib().disb200_run_sequence_host(self.h, C.c_void_p(frames_ptr), nframes, C.c_void_p(out_ptr)))

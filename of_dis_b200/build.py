@@ -22,7 +22,9 @@ NVCC_FLAGS = [
 # Files whose results are compared with a tolerance (the inverse search differs from the CPU code by the
 # order of its reductions anyway) may contract a*b+c into FMA; everything bit-compared may not.
 FMA_OK = set()   # measured: FMA in patch.cu gains 2 % of that kernel; not worth the drift from the CPU code
-CLI_VARIANTS = {"run_OF_INT": (1, 1), "run_OF_RGB": (1, 3), "run_DE_INT": (2, 1), "run_DE_RGB": (2, 3)}
+CLI_VARIANTS = {"run_OF_INT": (1, 1), "run_OF_RGB": (1, 3), "run_DE_INT": (2, 1), "run_DE_RGB": (2, 3),
+                # SELECTCHANNEL == 2 (gradient-magnitude input): in the reference's sources, without a CMake target
+                "run_OF_GRAD": (1, 2), "run_DE_GRAD": (2, 2)}
 
 
 def _nvcc() -> str:

@@ -54,6 +54,10 @@ struct PyrLevelPtrs {
 void launch_downscale_u8(const uint8_t* framesA, const uint8_t* framesB, int nA, int nB, int w0, int h0, int C, int padl,
                          int padt, int lvl, const LevelGeom& g, float* imgA, float* imgB, cudaStream_t s,
                          LaunchStats* st);
+// SELECTCHANNEL == 2: level `lvl` of the gradient-magnitude pyramid straight from the u8 frames
+void launch_downscale_gradmag(const uint8_t* framesA, const uint8_t* framesB, int nA, int nB, int w0, int h0, int W, int H,
+                              int padl, int padt, int lvl, const LevelGeom& g, float* imgA, float* imgB, cudaStream_t s,
+                              LaunchStats* st);
 // level image (padded array, interior valid) -> next coarser level image interior (2x2 mean)
 void launch_halve(const float* srcA, const float* srcB, const LevelGeom& gs, float* dstA, float* dstB,
                   const LevelGeom& gd, int nA, int nB, int C, cudaStream_t s, LaunchStats* st);

@@ -74,6 +74,8 @@ LevelGeom make_levelgeom(const DisParams& p, int W, int H, int level) {
 static int validate(const DisParams& p) {
   if (p.mode != DISB200_MODE_OF && p.mode != DISB200_MODE_DE) return fail(DISB200_EINVAL, "mode must be 1 (OF) or 2 (DE)");
   if (p.channels != 1 && p.channels != 3) return fail(DISB200_EINVAL, "channels must be 1 or 3");
+  if (p.gradmag != 0 && p.gradmag != 1) return fail(DISB200_EINVAL, "gradmag must be 0 or 1");
+  if (p.gradmag && p.channels != 1) return fail(DISB200_EINVAL, "gradmag (SELECTCHANNEL 2) is a single-band mode: channels must be 1");
   if (p.sc_l < 0 || p.sc_f < p.sc_l || p.sc_f > 8) return fail(DISB200_EINVAL, "need 0 <= sc_l <= sc_f <= 8");
   if (p.patove < 0.f || p.patove >= 1.f) return fail(DISB200_EINVAL, "patove must be in [0,1)");
   if (p.patchsz != 4 && p.patchsz != 8 && p.patchsz != 12 && p.patchsz != 16)
@@ -277,7 +279,10 @@ struct Engine {
     StageScope sc(this, 0);
     seq = dB == nullptr;
     const int nA = seq ? n + 1 : n, nB = seq ? 0 : n;
-    launch_downscale_u8(dA, dB, nA, nB, w0, h0, C, padl, padt, p.sc_l, geom[p.sc_l], pyr[0][0][p.sc_l], pyr[1][0][p.sc_l], stream, &stats);
+    if (p.gradmag)   // SELECTCHANNEL == 2: level 0 is the gradient magnitude, the cascade runs on arbitrary floats
+      launch_downscale_gradmag(dA, dB, nA, nB, w0, h0, W, H, padl, padt, p.sc_l, geom[p.sc_l], pyr[0][0][p.sc_l], pyr[1][0][p.sc_l], stream, &stats);
+    else
+      launch_downscale_u8(dA, dB, nA, nB, w0, h0, C, padl, padt, p.sc_l, geom[p.sc_l], pyr[0][0][p.sc_l], pyr[1][0][p.sc_l], stream, &stats);
     for (int l = p.sc_l + 1; l <= p.sc_f; ++l)
       launch_halve(pyr[0][0][l - 1], pyr[1][0][l - 1], geom[l - 1], pyr[0][0][l], pyr[1][0][l], geom[l], nA, nB, C, stream, &stats);
     PyrLevelPtrs lv[9];
@@ -370,13 +375,15 @@ struct DisHandle {
   cudaEvent_t t0 = nullptr, t1 = nullptr;
   bool staging = false;
   size_t in_bytes = 0, out_bytes = 0;   // per pair
+  size_t low_bytes = 0;                 // per pair, flow at level sc_l (what OFClass writes to outflow, oflow.h:105)
+  bool lowres = false;                  // the current call returns the sc_l flow instead of the upsampled one
 
   int ensure_staging() {
     if (staging) return DISB200_OK;
     for (int k = 0; k < 2; ++k) {
       int rc = e.dalloc(&dA[k], in_bytes * (max_batch + 1));   // + 1: a sequence chunk of m pairs is m + 1 frames
       if (!rc) rc = e.dalloc(&dB[k], in_bytes * max_batch);
-      if (!rc) rc = e.dalloc(&dOut[k], out_bytes / sizeof(float) * max_batch);
+      if (!rc) rc = e.dalloc(&dOut[k], std::max(out_bytes, low_bytes) / sizeof(float) * max_batch);   // sc_l = 0: the padded level exceeds the crop
       if (rc) return rc;
       CU(cudaEventCreateWithFlags(&ev_h2d[k], cudaEventDisableTiming));
       CU(cudaEventCreateWithFlags(&ev_comp[k], cudaEventDisableTiming));
@@ -406,7 +413,9 @@ struct DisHandle {
     E.build_pyramids(a, b, n, w0, h0, padl, padt);
     int rc = E.run_levels(n);
     if (rc) return rc;
-    {
+    if (lowres) {   // OFClass cut: hand out the level-sc_l flow as it is (no x 2^sc_l, no resize, no crop)
+      CU(cudaMemcpyAsync(out, E.flow[0][E.p.sc_l], low_bytes * n, cudaMemcpyDeviceToDevice, E.stream));
+    } else {
       Engine::StageScope sc(&E, 4);
       launch_upsample_crop(E.flow[0][E.p.sc_l], E.geom[E.p.sc_l], E.nop, E.p.sc_l, padl, padt, w0, h0, out, n, E.stream, &E.stats);
     }
@@ -429,7 +438,7 @@ struct DisHandle {
       if (rc) return rc;
       CU(cudaEventRecord(ev_fork, e.stream));
     }
-    const size_t out_elems = out_bytes / sizeof(float);
+    const size_t out_elems = (lowres ? low_bytes : out_bytes) / sizeof(float);
     for (int i = 0; i < S; ++i) {
       const int lo = i * per, m = std::min(per, n - lo);
       if (m <= 0) break;
@@ -539,6 +548,7 @@ int disb200_create(const DisParams* params, int w0, int h0, int max_batch, int d
     h->w0 = w0; h->h0 = h0;
     h->in_bytes = (size_t)w0 * h0 * params->channels;
     h->out_bytes = (size_t)w0 * h0 * h->e.nop * sizeof(float);
+    h->low_bytes = (size_t)(W >> params->sc_l) * (H >> params->sc_l) * h->e.nop * sizeof(float);
     if (cudaEventCreate(&h->t0) != cudaSuccess || cudaEventCreate(&h->t1) != cudaSuccess) rc = fail(DISB200_ECUDA, "cudaEventCreate failed");
   }
   if (rc) { h->e.destroy(); delete h; return rc; }
@@ -579,9 +589,18 @@ int disb200_sync(DisHandle* h) {
   return h->check_overflow();
 }
 
-int disb200_run_batch_host(DisHandle* h, const uint8_t* A, const uint8_t* B, int n, float* out) {
+// clears DisHandle::lowres when the entry point returns, whatever the path
+struct LowresScope {
+  DisHandle* h;
+  LowresScope(DisHandle* h_, bool on) : h(h_) { if (h) h->lowres = on; }
+  ~LowresScope() { if (h) h->lowres = false; }
+};
+
+static int run_batch_host_impl(DisHandle* h, const uint8_t* A, const uint8_t* B, int n, float* out, bool lowres) {
   if (!h || !A || !B || !out) return fail(DISB200_EINVAL, "null argument");
   if (n < 1) return fail(DISB200_EINVAL, "n must be >= 1");
+  LowresScope ls(h, lowres);
+  const size_t obytes = lowres ? h->low_bytes : h->out_bytes;
   CU(cudaSetDevice(h->e.device));
   int rc = h->ensure_staging();
   if (rc) return rc;
@@ -613,7 +632,7 @@ int disb200_run_batch_host(DisHandle* h, const uint8_t* A, const uint8_t* B, int
     total_launches += h->launches;
     CU(cudaEventRecord(h->ev_comp[b], h->e.stream));
     CU(cudaStreamWaitEvent(h->s_d2h, h->ev_comp[b], 0));
-    CU(cudaMemcpyAsync(out + (size_t)i0 * (h->out_bytes / sizeof(float)), h->dOut[b], h->out_bytes * m, cudaMemcpyDeviceToHost, h->s_d2h));
+    CU(cudaMemcpyAsync(out + (size_t)i0 * (obytes / sizeof(float)), h->dOut[b], obytes * m, cudaMemcpyDeviceToHost, h->s_d2h));
     CU(cudaEventRecord(h->ev_d2h[b], h->s_d2h));
   }
   CU(cudaStreamSynchronize(h->s_d2h));
@@ -621,6 +640,22 @@ int disb200_run_batch_host(DisHandle* h, const uint8_t* A, const uint8_t* B, int
   h->launches = total_launches;
   h->e.collect_stage_times();
   return h->check_overflow();
+}
+
+int disb200_run_batch_host(DisHandle* h, const uint8_t* A, const uint8_t* B, int n, float* out) {
+  return run_batch_host_impl(h, A, B, n, out, false);
+}
+int disb200_run_batch_host_lowres(DisHandle* h, const uint8_t* A, const uint8_t* B, int n, float* out_low) {
+  return run_batch_host_impl(h, A, B, n, out_low, true);
+}
+
+int disb200_lowres_dims(const DisHandle* h, int* w_l, int* h_l, int* nop) {
+  if (!h) return fail(DISB200_EINVAL, "null handle");
+  const LevelGeom& g = h->e.geom[h->e.p.sc_l];
+  if (w_l) *w_l = g.w;
+  if (h_l) *h_l = g.h;
+  if (nop) *nop = h->e.nop;
+  return DISB200_OK;
 }
 
 int disb200_run_sequence_device(DisHandle* h, const uint8_t* dFrames, int nframes, float* dOut) {
@@ -631,9 +666,11 @@ int disb200_run_sequence_device(DisHandle* h, const uint8_t* dFrames, int nframe
   return h->enqueue(dFrames, nullptr, nframes - 1, dOut);
 }
 
-int disb200_run_sequence_host(DisHandle* h, const uint8_t* frames, int nframes, float* out) {
+static int run_sequence_host_impl(DisHandle* h, const uint8_t* frames, int nframes, float* out, bool lowres) {
   if (!h || !frames || !out) return fail(DISB200_EINVAL, "null argument");
   if (nframes < 2) return fail(DISB200_EINVAL, "a sequence needs at least two frames");
+  LowresScope ls(h, lowres);
+  const size_t obytes = lowres ? h->low_bytes : h->out_bytes;
   CU(cudaSetDevice(h->e.device));
   int rc = h->ensure_staging();
   if (rc) return rc;
@@ -659,7 +696,7 @@ int disb200_run_sequence_host(DisHandle* h, const uint8_t* frames, int nframes, 
     total_launches += h->launches;
     CU(cudaEventRecord(h->ev_comp[b], h->e.stream));
     CU(cudaStreamWaitEvent(h->s_d2h, h->ev_comp[b], 0));
-    CU(cudaMemcpyAsync(out + (size_t)i0 * (h->out_bytes / sizeof(float)), h->dOut[b], h->out_bytes * m, cudaMemcpyDeviceToHost, h->s_d2h));
+    CU(cudaMemcpyAsync(out + (size_t)i0 * (obytes / sizeof(float)), h->dOut[b], obytes * m, cudaMemcpyDeviceToHost, h->s_d2h));
     CU(cudaEventRecord(h->ev_d2h[b], h->s_d2h));
   }
   CU(cudaStreamSynchronize(h->s_d2h));
@@ -667,6 +704,13 @@ int disb200_run_sequence_host(DisHandle* h, const uint8_t* frames, int nframes, 
   h->launches = total_launches;
   h->e.collect_stage_times();
   return h->check_overflow();
+}
+
+int disb200_run_sequence_host(DisHandle* h, const uint8_t* frames, int nframes, float* out) {
+  return run_sequence_host_impl(h, frames, nframes, out, false);
+}
+int disb200_run_sequence_host_lowres(DisHandle* h, const uint8_t* frames, int nframes, float* out_low) {
+  return run_sequence_host_impl(h, frames, nframes, out_low, true);
 }
 
 int disb200_run_batch(DisHandle* h, const uint8_t* const* imgA, const uint8_t* const* imgB, int n, float* const* out) {

@@ -104,8 +104,64 @@ __global__ void halve_kernel(const float* __restrict__ srcA, const float* __rest
   float* o = (frame ? dstB : dstA) + (size_t)pair * d_elems + ((size_t)(y + pad) * tw + (x + pad)) * C;
   const float* r0 = s + ((size_t)(2 * y + spad) * stw + (2 * x + spad)) * C;
   const float* r1 = r0 + (size_t)stw * C;
+  // OpenCV's own 2x2 mean takes four output pixels per 128-bit step as (a+b)+(d+e) and sums the w % 4 tail
+  // columns of a row one by one; the order only shows on non-dyadic data (gradient-magnitude pyramid).
+  const bool tail = C == 1 && x >= (w & ~3);
 #pragma unroll
-  for (int c = 0; c < C; ++c) o[c] = ((r0[c] + r0[C + c]) + (r1[c] + r1[C + c])) * 0.25f;
+  for (int c = 0; c < C; ++c) {
+    const float ab = r0[c] + r0[C + c];
+    o[c] = (tail ? (ab + r1[c]) + r1[C + c] : ab + (r1[c] + r1[C + c])) * 0.25f;
+  }
+}
+
+// SELECTCHANNEL == 2 (run_dense.cpp:139-148): level 0 is sqrt(dx^2 + dy^2) of the Sobel/8 gradients (REFLECT_101
+// at the borders of the dimension-padded frame) and every coarser level a cv::resize(.5) of the previous one.
+// One thread per pixel of level `lvl` walks its 2^lvl x 2^lvl block of level 0 in Morton order and folds the
+// cascade on the fly (three pending values per cascade level), so no finer level is ever written.  The gradients
+// are integers / 8: 8 gx = 2 r1 + r0 + r2, (8 gx)^2 + (8 gy)^2 < 2^24 is exact in fp32 and sqrt(s / 64) =
+// sqrt(s) / 8 exactly, which leaves cv::sqrt's correct rounding as the only rounding of level 0.
+__global__ void __launch_bounds__(128)
+downscale_gradmag_kernel(const uint8_t* __restrict__ framesA, const uint8_t* __restrict__ framesB, int w0, int h0, int W,
+                         int H, int padl, int padt, int lvl, int w, int h, int pad, int tw, size_t img_elems,
+                         float* __restrict__ imgA, float* __restrict__ imgB, int nA) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  const int y = blockIdx.y;
+  const int frame = (int)blockIdx.z >= nA, pair = frame ? blockIdx.z - nA : blockIdx.z;
+  if (x >= w) return;
+  const uint8_t* f = (frame ? framesB : framesA) + (size_t)pair * w0 * h0;
+  float* img = frame ? imgB : imgA;
+  float acc[8][3];
+  float v = 0.f;
+  const int total = 1 << (2 * lvl);
+  for (int m = 0; m < total; ++m) {
+    int ix = 0, iy = 0;
+    for (int b = 0; b < lvl; ++b) { ix |= ((m >> (2 * b)) & 1) << b; iy |= ((m >> (2 * b + 1)) & 1) << b; }
+    const int X = (x << lvl) + ix, Y = (y << lvl) + iy;
+    int col[3], row[3];
+#pragma unroll
+    for (int d = 0; d < 3; ++d) {
+      col[d] = clampi(reflect101(X + d - 1, W) - padl, 0, w0 - 1);
+      row[d] = clampi(reflect101(Y + d - 1, H) - padt, 0, h0 - 1) * w0;
+    }
+    int s[3][3];
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+#pragma unroll
+      for (int i = 0; i < 3; ++i) s[j][i] = __ldg(f + row[j] + col[i]);
+    const int gx = 2 * (s[1][2] - s[1][0]) + (s[0][2] - s[0][0]) + (s[2][2] - s[2][0]);
+    const int gy = 2 * (s[2][1] - s[0][1]) + (s[2][0] - s[0][0]) + (s[2][2] - s[0][2]);
+    v = sqrtf((float)(gx * gx + gy * gy)) * 0.125f;
+    int mm = m;
+    for (int j = 0; j < lvl; ++j, mm >>= 2) {
+      const int q = mm & 3;
+      if (q < 3) { acc[j][q] = v; break; }
+      const int wj = W >> (j + 1);
+      const bool tail = (X >> (j + 1)) >= (wj & ~3);
+      const float ab = acc[j][0] + acc[j][1];
+      v = (tail ? (ab + acc[j][2]) + v : ab + (acc[j][2] + v)) * 0.25f;
+    }
+  }
+  img[(size_t)pair * img_elems + (size_t)(y + pad) * tw + (x + pad)] = v;
 }
 
 struct SobelLevels {
@@ -201,6 +257,15 @@ void launch_downscale_u8(const uint8_t* framesA, const uint8_t* framesB, int nA,
     downscale_u8_kernel<1><<<grd, blk, 0, s>>>(framesA, framesB, w0, h0, padl, padt, lvl, g.w, g.h, g.pad, g.tw, g.img_elems, imgA, imgB, nA);
   else
     downscale_u8_kernel<3><<<grd, blk, 0, s>>>(framesA, framesB, w0, h0, padl, padt, lvl, g.w, g.h, g.pad, g.tw, g.img_elems, imgA, imgB, nA);
+  st->launches++;
+}
+
+void launch_downscale_gradmag(const uint8_t* framesA, const uint8_t* framesB, int nA, int nB, int w0, int h0, int W, int H,
+                              int padl, int padt, int lvl, const LevelGeom& g, float* imgA, float* imgB, cudaStream_t s,
+                              LaunchStats* st) {
+  dim3 blk(128), grd((g.w + 127) / 128, g.h, nA + nB);
+  downscale_gradmag_kernel<<<grd, blk, 0, s>>>(framesA, framesB, w0, h0, W, H, padl, padt, lvl, g.w, g.h, g.pad, g.tw,
+                                               g.img_elems, imgA, imgB, nA);
   st->launches++;
 }
 

@@ -58,13 +58,14 @@ static void decode_chunk(const std::vector<Job>& jobs, size_t lo, int n, bool vi
 }
 
 int main(int argc, char** argv) {
-  int mode = DISB200_MODE_OF, channels = 1, batch = 64, threads = 8, device = 0;
+  int mode = DISB200_MODE_OF, channels = 1, batch = 64, threads = 8, device = 0, gradmag = 0;
   bool video = false;
   int ai = 1;
   for (; ai < argc && argv[ai][0] == '-' && argv[ai][1] == '-'; ++ai) {
     const std::string f = argv[ai];
     if (f == "--de") mode = DISB200_MODE_DE;
     else if (f == "--rgb") channels = 3;
+    else if (f == "--gradmag") gradmag = 1;   // SELECTCHANNEL == 2 (run_dense.cpp:139-148)
     else if (f == "--video") video = true;
     else if (f == "--batch" && ai + 1 < argc) batch = std::atoi(argv[++ai]);
     else if (f == "--threads" && ai + 1 < argc) threads = std::atoi(argv[++ai]);
@@ -73,7 +74,7 @@ int main(int argc, char** argv) {
   }
   const int rest = argc - ai;
   if ((rest != 1 && rest != 2 && rest != 21) || batch < 1 || threads < 1) {
-    std::fprintf(stderr, "usage: %s [--de] [--rgb] [--video] [--batch B] [--threads T] [--device D] list.txt "
+    std::fprintf(stderr, "usage: %s [--de] [--rgb] [--gradmag] [--video] [--batch B] [--threads T] [--device D] list.txt "
                          "[oppoint 1..4 | 20 parameters in the order of run_*_*]\n", argv[0]);
     return 1;
   }
@@ -102,7 +103,7 @@ int main(int argc, char** argv) {
     disb200_free(px);
     if (rc) { std::fprintf(stderr, "cannot read %s\n", jobs[0].a.c_str()); return rc; }
   }
-  DisParams p;
+  DisParams p{};
   int rc;
   if (rest == 21) {
     char** a = argv + ai + 1;
@@ -118,6 +119,7 @@ int main(int argc, char** argv) {
     rc = disb200_operating_point(rest == 2 ? std::atoi(argv[ai + 1]) : 2, w0, mode, channels, &p);
     if (rc) { std::fprintf(stderr, "operating point: %s\n", disb200_last_error()); return rc; }
   }
+  p.gradmag = gradmag;
   if ((size_t)batch > npairs) batch = (int)npairs;
   DisHandle* h = nullptr;
   rc = disb200_create(&p, w0, h0, batch, device, &h);

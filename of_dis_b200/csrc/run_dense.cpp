@@ -76,6 +76,7 @@ int main(int argc, char** argv) {
     p.tv_innerit = std::atoi(argv[a++]); p.tv_solverit = std::atoi(argv[a++]); p.tv_sor = (float)std::atof(argv[a++]);
     p.verbosity = std::atoi(argv[a++]);
   }
+  p.gradmag = SELECTCHANNEL == 2;   // gradient-magnitude input (run_dense.cpp:139-148)
   if (const char* e = std::getenv("DISB200_SOR")) p.sor_mode = (e[0] == 'r') ? DISB200_SOR_REDBLACK : DISB200_SOR_LEXICOGRAPHIC;
 
   if (p.verbosity > 1) {

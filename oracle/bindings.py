@@ -32,7 +32,7 @@ class OrcParams(C.Structure):
         ("usefbcon", C.c_int), ("patnorm", C.c_int), ("costfct", C.c_int), ("usetvref", C.c_int),
         ("tv_alpha", C.c_float), ("tv_gamma", C.c_float), ("tv_delta", C.c_float),
         ("tv_innerit", C.c_int), ("tv_solverit", C.c_int), ("tv_sor", C.c_float),
-        ("verbosity", C.c_int), ("mode", C.c_int), ("noc", C.c_int),
+        ("verbosity", C.c_int), ("mode", C.c_int), ("noc", C.c_int), ("gradmag", C.c_int),
     ]
 
     def copy(self, **kw):
@@ -55,12 +55,12 @@ def build(port: bool = True, ref: bool = True) -> None:
         subprocess.check_call(["make", "-C", HERE, "ref"], stdout=subprocess.DEVNULL)
 
 
-def variant_name(mode: int, noc: int) -> str:
-    return ("OF" if mode == 1 else "DE") + "_" + ("INT" if noc == 1 else "RGB")
+def variant_name(mode: int, noc: int, gradmag: bool = False) -> str:
+    return ("OF" if mode == 1 else "DE") + "_" + ("GRAD" if gradmag else "INT" if noc == 1 else "RGB")
 
 
-def have_ref(mode: int = 1, noc: int = 1) -> bool:
-    return os.path.exists(os.path.join(HERE, "_ref", "libref_%s.so" % variant_name(mode, noc)))
+def have_ref(mode: int = 1, noc: int = 1, gradmag: bool = False) -> bool:
+    return os.path.exists(os.path.join(HERE, "_ref", "libref_%s.so" % variant_name(mode, noc, gradmag)))
 
 
 def pyr_ptrs(levels: dict, sc_f: int):
@@ -95,7 +95,13 @@ class Port:
         self.lib.orc_pad_dims(w0, h0, sc_f, C.byref(W), C.byref(H), C.byref(pl), C.byref(pt))
         return W.value, H.value, pl.value, pt.value
 
-    def pyramid_level(self, img_u8, sc_f, level, pad):
+    def gradient_magnitude(self, src):
+        src = np.ascontiguousarray(src, np.float32)
+        dst = np.empty_like(src)
+        self.lib.orc_gradient_magnitude(_p(src), src.shape[1], src.shape[0], _p(dst))
+        return dst
+
+    def pyramid_level(self, img_u8, sc_f, level, pad, gradmag=False):
         h0, w0 = img_u8.shape[:2]
         Cn = 1 if img_u8.ndim == 2 else img_u8.shape[2]
         W, H, _, _ = self.pad_dims(w0, h0, sc_f)
@@ -103,14 +109,18 @@ class Port:
         shp = (hl + 2 * pad, wl + 2 * pad, Cn)
         out = [np.empty(shp, np.float32) for _ in range(3)]
         img_u8 = np.ascontiguousarray(img_u8)
-        self.lib.orc_pyramid_level(_p(img_u8, u8p), w0, h0, Cn, sc_f, level, pad, *[_p(o) for o in out])
+        self.lib.orc_set_pyramid_gradmag(int(bool(gradmag)))
+        try:
+            self.lib.orc_pyramid_level(_p(img_u8, u8p), w0, h0, Cn, sc_f, level, pad, *[_p(o) for o in out])
+        finally:
+            self.lib.orc_set_pyramid_gradmag(0)
         return out
 
-    def pyramid(self, img_u8, sc_f, sc_l, pad):
+    def pyramid(self, img_u8, sc_f, sc_l, pad, gradmag=False):
         """-> ({level: img}, {level: dx}, {level: dy})"""
         I, X, Y = {}, {}, {}
         for l in range(sc_l, sc_f + 1):
-            I[l], X[l], Y[l] = self.pyramid_level(img_u8, sc_f, l, pad)
+            I[l], X[l], Y[l] = self.pyramid_level(img_u8, sc_f, l, pad, gradmag)
         return I, X, Y
 
     def halve(self, src):
@@ -204,14 +214,15 @@ def _patchgrid(fn, is_port, p, A, B, w_l, h_l, level, prev_fw, prev_bw):
 
 
 class Ref:
-    """The reference's own code (oracle/_ref), one variant per (mode, noc)."""
+    """The reference's own code (oracle/_ref), one variant per (SELECTMODE, SELECTCHANNEL); gradmag selects the
+    SELECTCHANNEL == 2 build (single band like 1; only the driver's pyramid differs, run_dense.cpp:139-148)."""
 
-    def __init__(self, mode: int = 1, noc: int = 1):
-        path = os.path.join(HERE, "_ref", "libref_%s.so" % variant_name(mode, noc))
+    def __init__(self, mode: int = 1, noc: int = 1, gradmag: bool = False):
+        path = os.path.join(HERE, "_ref", "libref_%s.so" % variant_name(mode, noc, gradmag))
         if not os.path.exists(path):
             raise FileNotFoundError(path + " (run `make -C oracle ref` where /root/reference exists)")
         self.lib = C.CDLL(path)
-        assert self.lib.ref_mode() == mode and self.lib.ref_channels() == noc
+        assert self.lib.ref_mode() == mode and self.lib.ref_channels() == (2 if gradmag else noc)
         self.mode, self.noc = mode, noc
 
     def ofclass(self, p: OrcParams, A, B, W, H, initflow=None, verbosity=0):

@@ -35,7 +35,8 @@ struct OrcParams {
   float tv_sor;
   int verbosity;
   int mode;  // 1 optical flow (SELECTMODE 1), 2 depth from stereo (SELECTMODE 2)
-  int noc;   // 1 grey (SELECTCHANNEL 1), 3 BGR (SELECTCHANNEL 3)
+  int noc;   // 1 grey (SELECTCHANNEL 1 or 2), 3 BGR (SELECTCHANNEL 3)
+  int gradmag;  // 1: the grey frame is replaced by its gradient magnitude (SELECTCHANNEL 2, run_dense.cpp:139-148)
 };
 }
 
@@ -113,7 +114,11 @@ void halve(const fvec& src, int w, int h, int C, fvec& dst) {
       for (int c = 0; c < C; ++c) {
         const float a = src[((size_t)(2 * y) * w + 2 * x) * C + c], b = src[((size_t)(2 * y) * w + 2 * x + 1) * C + c];
         const float d = src[((size_t)(2 * y + 1) * w + 2 * x) * C + c], e = src[((size_t)(2 * y + 1) * w + 2 * x + 1) * C + c];
-        dst[((size_t)y * w2 + x) * C + c] = ((a + b) + (d + e)) * 0.25f;
+        // OpenCV's own code (ResizeAreaFast, which INTER_LINEAR at exactly .5 dispatches to): four output pixels
+        // per 128-bit step as (a+b)+(d+e), the w2 % 4 tail columns of a row summed one by one.  Only visible
+        // on data that is not dyadic (the gradient-magnitude pyramid); pinned by tests/golden/gradmag.npz.
+        const bool tail = C == 1 && x >= (w2 & ~3);
+        dst[((size_t)y * w2 + x) * C + c] = (tail ? ((a + b) + d) + e : (a + b) + (d + e)) * 0.25f;
       }
 }
 
@@ -135,6 +140,16 @@ void sobel(const fvec& src, int w, int h, int C, fvec& dx, fvec& dy) {
         float s2 = 0.25f * S(x, y + 1, c) + 0.125f * (S(x + 1, y + 1, c) + S(x - 1, y + 1, c));
         dy[((size_t)y * w + x) * C + c] = s2 - s0;
       }
+}
+
+// a2, SELECTCHANNEL == 2 (run_dense.cpp:139-148): level 0 = sqrt(dx*dx + dy*dy) of the Sobel/8
+// gradients of the padded float frame.  dx, dy are multiples of 1/8 below 2^7, so the squares and
+// their sum are exact and the only rounding is cv::sqrt's (correctly rounded, like sqrtf).
+void gradient_magnitude(const fvec& src, int w, int h, fvec& dst) {
+  fvec gx, gy;
+  sobel(src, w, h, 1, gx, gy);
+  dst.resize(src.size());
+  for (size_t i = 0; i < src.size(); ++i) dst[i] = std::sqrt(gx[i] * gx[i] + gy[i] * gy[i]);
 }
 
 // a2  copyMakeBorder by `pad` on all sides (run_dense.cpp:165-178)
@@ -859,6 +874,7 @@ void compute_data_DE(const Derivs& D, const Plane& mask, const Plane& du, float 
 // reference; the restatement of the product's DISB200_SOR_REDBLACK mode (all pixels with even i + j, then all
 // with odd i + j, same update formulas), so that mode too has a CPU oracle.
 int g_sor_order = 0;
+bool g_pyr_gradmag = false;
 template <class F>
 inline void sweep_pixels(int w, int h, F f) {
   if (g_sor_order == 0) {
@@ -1039,12 +1055,13 @@ struct Pyramid {
 
 // a1 + a2  (run_dense.cpp:299-312,131-179).  Only levels sc_l..sc_f are kept; finer
 // levels are built by the reference but never read (oflow.cpp:182).
-void build_pyramid(const uint8_t* im, int w0, int h0, int C, int sc_f, int sc_l, int pad, Pyramid& P) {
+void build_pyramid(const uint8_t* im, int w0, int h0, int C, int sc_f, int sc_l, int pad, Pyramid& P, bool gradmag = false) {
   pad_dims(w0, h0, sc_f, &P.W, &P.H, &P.padl, &P.padt);
   P.img.assign(sc_f + 1, fvec()); P.dx.assign(sc_f + 1, fvec()); P.dy.assign(sc_f + 1, fvec());
   fvec cur, nxt, gx, gy;
   pad_to_float(im, w0, h0, C, P.W, P.H, P.padl, P.padt, cur);
   int w = P.W, h = P.H;
+  if (gradmag && C == 1) { gradient_magnitude(cur, w, h, nxt); cur.swap(nxt); }
   for (int l = 0; l <= sc_f; ++l) {
     if (l > 0) { halve(cur, w, h, C, nxt); cur.swap(nxt); w /= 2; h /= 2; }
     if (l >= sc_l) {
@@ -1070,7 +1087,7 @@ void orc_operating_point(int op, int width, int mode, int noc, OrcParams* p) {
   p->usefbcon = 0; p->patnorm = 1; p->costfct = 0;
   p->tv_alpha = 10.0f; p->tv_gamma = 10.0f; p->tv_delta = 5.0f;
   p->tv_innerit = 1; p->tv_solverit = 3; p->tv_sor = 1.6f;
-  p->verbosity = 2; p->mode = mode; p->noc = noc;
+  p->verbosity = 2; p->mode = mode; p->noc = noc; p->gradmag = 0;
   const int fratio = 5;
   auto first = [&](int psz) { return std::max(0, (int)std::floor(log2((2.0f * (float)width) / ((float)fratio * (float)psz)))); };
   switch (op) {
@@ -1083,12 +1100,19 @@ void orc_operating_point(int op, int width, int mode, int noc, OrcParams* p) {
 
 // 0 raster order (reference), 1 red-black (product's throughput mode); process-global, tests reset it to 0
 void orc_set_sor_order(int order) { g_sor_order = order ? 1 : 0; }
+// SELECTCHANNEL == 2 for the stage-level entry points orc_pyramid_level (run_dense entry points read OrcParams::gradmag).
+void orc_set_pyramid_gradmag(int on) { g_pyr_gradmag = on != 0; }
+void orc_gradient_magnitude(const float* src, int w, int h, float* dst) {
+  fvec s(src, src + (size_t)w * h), d;
+  gradient_magnitude(s, w, h, d);
+  std::memcpy(dst, d.data(), d.size() * sizeof(float));
+}
 void orc_pad_dims(int w0, int h0, int sc_f, int* W, int* H, int* padl, int* padt) { pad_dims(w0, h0, sc_f, W, H, padl, padt); }
 
 // One padded pyramid level (img, dx, dy) from a u8 image; out arrays hold (h_l+2pad)*(w_l+2pad)*C floats.
 void orc_pyramid_level(const uint8_t* im, int w0, int h0, int C, int sc_f, int level, int pad, float* img, float* dx, float* dy) {
   Pyramid P;
-  build_pyramid(im, w0, h0, C, std::max(sc_f, level), level, pad, P);
+  build_pyramid(im, w0, h0, C, std::max(sc_f, level), level, pad, P, g_pyr_gradmag);
   // note: padding is decided by sc_f, levels by `level`
   std::memcpy(img, P.img[level].data(), P.img[level].size() * sizeof(float));
   std::memcpy(dx, P.dx[level].data(), P.dx[level].size() * sizeof(float));
@@ -1158,8 +1182,8 @@ void orc_varref_level(const OrcParams* p, const float* a, const float* b, int w_
 // out holds h0*w0*nop floats.  If lowres != null it also receives the sc_l flow (H/2^sc_l x W/2^sc_l x nop).
 void orc_run_dense(const OrcParams* p, const uint8_t* A, const uint8_t* B, int w0, int h0, float* out, float* lowres) {
   Pyramid PA, PB;
-  build_pyramid(A, w0, h0, p->noc, p->sc_f, p->sc_l, p->psz, PA);
-  build_pyramid(B, w0, h0, p->noc, p->sc_f, p->sc_l, p->psz, PB);
+  build_pyramid(A, w0, h0, p->noc, p->sc_f, p->sc_l, p->psz, PA, p->gradmag != 0);
+  build_pyramid(B, w0, h0, p->noc, p->sc_f, p->sc_l, p->psz, PB, p->gradmag != 0);
   const int nop = p->mode == 1 ? 2 : 1, k = 1 << p->sc_l;
   const int wl = PA.W / k, hl = PA.H / k;
   fvec flow((size_t)wl * hl * nop);
@@ -1178,8 +1202,8 @@ extern "C" void orc_run_dense_timed(const OrcParams* p, const uint8_t* A, const 
   typedef std::chrono::steady_clock clk;
   auto t0 = clk::now();
   Pyramid PA, PB;
-  build_pyramid(A, w0, h0, p->noc, p->sc_f, p->sc_l, p->psz, PA);
-  build_pyramid(B, w0, h0, p->noc, p->sc_f, p->sc_l, p->psz, PB);
+  build_pyramid(A, w0, h0, p->noc, p->sc_f, p->sc_l, p->psz, PA, p->gradmag != 0);
+  build_pyramid(B, w0, h0, p->noc, p->sc_f, p->sc_l, p->psz, PB, p->gradmag != 0);
   const int nop = p->mode == 1 ? 2 : 1, k = 1 << p->sc_l;
   const int wl = PA.W / k, hl = PA.H / k;
   fvec flow((size_t)wl * hl * nop);

@@ -28,6 +28,11 @@ def cv2_golden():
 
 
 @pytest.fixture(scope="session")
+def gradmag_golden():
+    return np.load(os.path.join(GOLDEN, "gradmag.npz"))
+
+
+@pytest.fixture(scope="session")
 def ref_golden():
     return np.load(os.path.join(GOLDEN, "ref_flows.npz"))
 

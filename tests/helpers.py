@@ -29,5 +29,5 @@ def epe(a, b):
 def base_orc(mode, noc, **kw):
     p = ob.OrcParams(sc_f=3, sc_l=1, max_iter=12, min_iter=12, dp_thresh=.05, dr_thresh=.95, res_thresh=0., psz=8,
                      patove=.4, usefbcon=0, patnorm=1, costfct=0, usetvref=1, tv_alpha=10., tv_gamma=10., tv_delta=5.,
-                     tv_innerit=1, tv_solverit=3, tv_sor=1.6, verbosity=0, mode=mode, noc=noc)
+                     tv_innerit=1, tv_solverit=3, tv_sor=1.6, verbosity=0, mode=mode, noc=noc, gradmag=0)
     return p.copy(**kw)

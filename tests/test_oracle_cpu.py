@@ -107,6 +107,46 @@ def test_port_matches_reference_live(port, mode, noc):
                               ref.varref_level(p, a[0], b[0], wl, hl, p.sc_l, 0, fl)), kw
 
 
+# ---------------------------------------------------------------- SELECTCHANNEL == 2 (gradient-magnitude input)
+def test_gradmag_pyramid_steps_match_cv2(port, gradmag_golden):
+    """run_dense.cpp:139-148 on arbitrary floats: level 0 and the .5 cascade (OpenCV's own summation order, including
+    the w % 4 tail columns: levels of 40, 20 and 10 columns) bit for bit; the IPP dispatch of the same wheel is
+    within one ulp of it."""
+    g = gradmag_golden
+    f = np.pad(g["g_u8"], ((2, 2), (4, 4)), mode="edge").astype(np.float32)
+    lv = port.gradient_magnitude(f)
+    assert np.array_equal(lv, g["g_l0"])
+    for l in (1, 2, 3):
+        lv = port.halve(lv)
+        dx, dy = port.sobel(lv)
+        assert np.array_equal(lv, g["g_l%d" % l]) and np.array_equal(dx, g["g_dx%d" % l]) and np.array_equal(dy, g["g_dy%d" % l]), l
+        assert np.abs(g["g_ipp_l%d" % l] - lv).max() <= np.spacing(np.float32(lv.max()))
+        I, X, Y = port.pyramid_level(g["g_u8"], 4, l, 8, gradmag=True)
+        assert np.array_equal(I[8:-8, 8:-8, 0], g["g_l%d" % l]) and np.array_equal(X[8:-8, 8:-8, 0], g["g_dx%d" % l])
+        assert np.array_equal(Y[8:-8, 8:-8, 0], g["g_dy%d" % l])
+    # the intensity pyramid is not touched by the switch being off again
+    assert np.array_equal(port.pyramid_level(g["g_u8"], 4, 0, 8)[0][8:-8, 8:-8, 0], f)
+
+
+@pytest.mark.parametrize("mode,name", [(1, "of_grad_op2like"), (2, "de_grad_op2like")])
+def test_port_matches_reference_golden_gradmag(port, gradmag_golden, mode, name):
+    """Flow of the reference's own sources compiled with -DSELECTCHANNEL=2 on the gradient-magnitude pyramid."""
+    g = gradmag_golden
+    A, B = g[name + "_A"], g[name + "_B"]
+    p = base_orc(mode, 1, gradmag=1)
+    W, H, _, _ = port.pad_dims(150, 90, p.sc_f)
+    PA, PB = port.pyramid(A, p.sc_f, p.sc_l, p.psz, gradmag=True), port.pyramid(B, p.sc_f, p.sc_l, p.psz, gradmag=True)
+    assert np.array_equal(port.ofclass(p, PA, PB, W, H), g[name + "_low"])
+    if ob.have_ref(mode, 1, gradmag=True):
+        assert np.array_equal(ob.Ref(mode, 1, gradmag=True).ofclass(p, PA, PB, W, H), g[name + "_low"])
+    # the driver entry point builds the same pyramid from the parameter block
+    out, low = port.run_dense(p, A, B, want_lowres=True)
+    assert np.array_equal(low, g[name + "_low"])
+    assert not np.array_equal(low, port.run_dense(p.copy(gradmag=0), A, B, want_lowres=True)[1])
+    gt = g[name + "_gt"]
+    assert epe(out, gt)[0] < 1.5      # a flow, if a worse one than on intensities (texture edges only)
+
+
 def test_port_flow_is_sane(port):
     """EPE against the synthetic ground truth (not a parity check, a sanity check of the generator + oracle)."""
     from of_dis_b200.synth import make_pair
@@ -156,8 +196,8 @@ def test_cabi_exports_every_declared_symbol(dis):
 
 
 def test_struct_layout_matches_header(dis):
-    # 23 four-byte fields in CLI order + mode, channels, sor_mode
-    assert ctypes.sizeof(dis.DisParams) == 23 * 4
+    # 20 four-byte fields in CLI order + mode, channels, sor_mode, gradmag
+    assert ctypes.sizeof(dis.DisParams) == 24 * 4
     hdr = open(os.path.join(ROOT, "include", "disb200.h")).read()
     body = hdr[hdr.index("typedef struct DisParams {"):hdr.index("} DisParams;")]
     fields = re.findall(r"^\s*(?:int|float)\s+([a-z_]+);", body, re.M)
@@ -175,7 +215,8 @@ def test_compute_entry_points_fail_loudly_without_gpu(dis):
 
 def test_invalid_parameters_are_rejected(dis):
     p = dis.operating_point(2, 256)
-    for kw in (dict(mode=3), dict(channels=2), dict(sc_l=4, sc_f=3), dict(patove=1.0), dict(patchsz=7), dict(costfct=3), dict(sor_mode=2)):
+    for kw in (dict(mode=3), dict(channels=2), dict(sc_l=4, sc_f=3), dict(patove=1.0), dict(patchsz=7), dict(costfct=3), dict(sor_mode=2), dict(gradmag=2),
+               dict(gradmag=1, channels=3)):
         with pytest.raises(dis.DisError) as e:
             dis.Handle(p.copy(**kw), 256, 128, 1)
         assert e.value.code in (1, 4), kw

@@ -49,6 +49,54 @@ def test_pyramid_bit_exact(gpu, port, ch, w0, h0, sc_f, sc_l):
                     assert np.array_equal(got[k], want[k]), (l, which, pair, k)
 
 
+@pytest.mark.parametrize("w0,h0,sc_f,sc_l", [(150, 90, 3, 1), (1024, 436, 5, 3), (96, 64, 2, 0), (333, 217, 4, 2), (150, 90, 2, 2),
+                                            (100, 60, 3, 3), (1280, 720, 6, 4)])
+def test_pyramid_gradmag_bit_exact(gpu, port, w0, h0, sc_f, sc_l):
+    """SELECTCHANNEL == 2 (run_dense.cpp:139-148): the cascade runs on arbitrary floats, so OpenCV's summation order
+    shows (pinned by tests/golden/gradmag.npz); sizes cover tail columns (w % 4 != 0) inside the fused cascade
+    (sc_l >= sc_f - 1) and in the level-to-level halving."""
+    A, B, _ = make_pair(h0, w0, channels=1, seed=4)
+    p = to_dis(gpu, base_orc(1, 1, sc_f=sc_f, sc_l=sc_l, gradmag=1))
+    with gpu.Handle(p, w0, h0, max_batch=2) as hd:
+        hd.run_host(np.stack([A, B]), np.stack([B, A]))
+        for l in range(sc_l, sc_f + 1):
+            want_a, want_b = port.pyramid_level(A, sc_f, l, 8, gradmag=True), port.pyramid_level(B, sc_f, l, 8, gradmag=True)
+            for which, pair, want in ((0, 0, want_a), (1, 0, want_b), (0, 1, want_b), (1, 1, want_a)):
+                got = hd.fetch_pyramid(which, l, pair)
+                for k in range(3):
+                    assert np.array_equal(got[k], want[k]), (l, which, pair, k)
+        # the video front end builds each frame's gradient-magnitude pyramid once
+        seq = hd.run_sequence(np.stack([A, B, A]))
+        assert np.array_equal(seq[0], hd.run_host(A[None], B[None])[0]) and np.array_equal(seq[1], hd.run_host(B[None], A[None])[0])
+
+
+@pytest.mark.parametrize("mode,name", [(1, "of_grad_op2like"), (2, "de_grad_op2like")])
+def test_gradmag_against_reference_golden(gpu, gradmag_golden, mode, name):
+    """u8 frames in, against the flow of the reference's own sources built with -DSELECTCHANNEL=2."""
+    g = gradmag_golden
+    A, B = g[name + "_A"], g[name + "_B"]
+    p = to_dis(gpu, base_orc(mode, 1, gradmag=1))
+    with gpu.Handle(p, 150, 90, max_batch=1) as hd:
+        hd.run_host(A[None], B[None])
+        low = hd.fetch_flow(0, p.sc_l, pair=0)
+    m, mx = epe(low, g[name + "_low"])
+    assert m <= MEAN_TOL and mx <= 0.05, (m, mx)
+
+
+@pytest.mark.parametrize("mode,w0,h0", [(1, 1024, 436), (2, 1280, 720)])
+def test_gradmag_run_dense_parity(gpu, port, mode, w0, h0):
+    A, B, gt = make_pair(h0, w0, channels=1, mode="OF" if mode == 1 else "DE", seed=0)
+    p = gpu.operating_point(2, w0, mode, 1).copy(verbosity=0, gradmag=1)
+    want = port.run_dense(to_orc(p), A, B)
+    with gpu.Handle(p, w0, h0, max_batch=2) as hd:
+        out = hd.run_host(np.stack([A, B]), np.stack([B, A]))
+    m, mx = epe(out[0], want)
+    assert m <= MEAN_TOL and mx <= MAX_TOL_FINE, "EPE(GPU,CPU) mean %g max %g" % (m, mx)
+    assert epe(out[1], port.run_dense(to_orc(p), B, A))[0] <= MEAN_TOL
+    assert abs(epe(out[0], gt)[0] - epe(want, gt)[0]) < 5e-3
+    assert not np.array_equal(out[0], port.run_dense(to_orc(p.copy(gradmag=0)), A, B))
+
+
 # ------------------------------------------------------------------------------ stage 4 alone
 @pytest.mark.parametrize("mode,ch", [(1, 1), (1, 3), (2, 1), (2, 3)])
 @pytest.mark.parametrize("w0,h0,level", [(1024, 436, 3), (500, 218, 1), (130, 70, 0)])
@@ -269,7 +317,7 @@ def test_cli_matches_library(gpu, tmp_path):
     """run_OF_INT / run_DE_INT (reference argv grammar, PGM in, .flo / .pfm out) against the batch entry point."""
     import subprocess
     exe_dir = os.path.join(ROOT, "of_dis_b200", "bin")
-    for mode, exe, ext in ((1, "run_OF_INT", "flo"), (2, "run_DE_INT", "pfm")):
+    for mode, exe, ext in ((1, "run_OF_INT", "flo"), (2, "run_DE_INT", "pfm"), (1, "run_OF_GRAD", "flo")):
         A, B, _ = make_pair(120, 200, mode="OF" if mode == 1 else "DE", seed=2)
         for name, img in (("a.pgm", A), ("b.pgm", B)):
             with open(tmp_path / name, "wb") as f:
@@ -279,7 +327,7 @@ def test_cli_matches_library(gpu, tmp_path):
                            capture_output=True, text=True)
         assert r.returncode == 0, r.stderr
         assert "O.Flow Run-Time" in r.stdout
-        p = gpu.operating_point(2, 200, mode, 1)
+        p = gpu.operating_point(2, 200, mode, 1).copy(gradmag=int(exe.endswith("GRAD")))
         with gpu.Handle(p, 200, 120, 1) as hd:
             want = hd.run_host(A[None], B[None])[0]
         raw = open(out, "rb").read()
@@ -404,6 +452,33 @@ def test_video_sequence_reuses_pyramids_and_matches_explicit_pairs(gpu):
             assert hd.launch_count() > 0 and l_pairs > 0
         assert np.array_equal(got, want)
         assert np.array_equal(got3, want[:3])
+
+
+@pytest.mark.parametrize("mode,ch,op,w0,h0", [(1, 1, 2, 1024, 436), (2, 1, 2, 640, 360), (1, 3, 2, 320, 136), (1, 1, 4, 150, 90)])
+def test_lowres_entry_points_return_the_ofclass_outflow(gpu, port, mode, ch, op, w0, h0):
+    """disb200_run_batch_host_lowres / run_sequence_host_lowres: the level-sc_l flow (what OFClass writes to outflow,
+    oflow.h:105), chunked like the full-resolution calls; upsampling it with the oracle's restatement of
+    run_dense.cpp:407-415 gives exactly the full-resolution result.  op4 on 150x90 has sc_l = 0 (padded level larger
+    than the cropped output)."""
+    A, B, _ = make_pair(h0, w0, channels=ch, mode="OF" if mode == 1 else "DE", seed=6)
+    p = gpu.operating_point(op, w0, mode, ch).copy(verbosity=0)
+    W, H, padl, padt = port.pad_dims(w0, h0, p.sc_f)
+    As, Bs = np.stack([A, B, A, B, A]), np.stack([B, A, B, A, B])
+    with gpu.Handle(p, w0, h0, max_batch=2) as hd:          # 5 pairs, max_batch 2 -> three chunks
+        assert hd.lowres_dims() == (H >> p.sc_l, W >> p.sc_l, p.nop)
+        full = hd.run_host(As, Bs)
+        low = hd.run_host_lowres(As, Bs)
+        assert hd.launch_count() > 0
+        assert np.array_equal(low[0], hd.fetch_flow(0, p.sc_l, pair=0))    # last chunk holds pair 4 == pair 0
+        assert np.array_equal(hd.run_host(As, Bs), full)                   # the mode does not stick to the handle
+        frames = np.stack([A, B, A, B])
+        seq_low = hd.run_sequence_lowres(frames)
+    assert low.shape == (5, H >> p.sc_l, W >> p.sc_l, p.nop)
+    for i in range(5):
+        assert np.array_equal(port.upsample_crop(low[i], p.sc_l, padl, padt, w0, h0), full[i]), i
+    assert np.array_equal(seq_low, low[:3])
+    want_low = port.run_dense(to_orc(p), A, B, want_lowres=True)[1]
+    assert epe(low[0], want_low)[0] <= MEAN_TOL
 
 
 def test_identical_frames_give_exactly_zero(gpu):
