@@ -75,7 +75,12 @@ __device__ __forceinline__ void loss(float d, float bsq, float bsq2, float& pd, 
   }
 }
 
-template <int PSZ, int C, int G, bool OF>
+// LPR > 0 selects the block mapping (12 x 12 patches, op3 / op4): the G lanes of a patch form LPR columns x G / LPR
+// row groups and a lane owns a block of RPL rows x CW consecutive floats of a row (channels interleaved).  The
+// bilinear taps of a block row are CW + C consecutive floats and the lower taps of one row are the upper taps of the
+// next, so an iteration loads (RPL + 1)(CW + C) values for RPL CW results instead of four per result:
+// 28 for 18 (12 x 12 grey, 8 lanes) and 48 for 27 (12 x 12 BGR, 16 lanes).
+template <int PSZ, int C, int G, bool OF, int LPR = 0>
 __global__ void __launch_bounds__(128)   // (capping the column-pair variant at 96 registers for 5 CTAs per SM spills inside the loop: 1.60 -> 2.00 ms)
 patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
   constexpr int NV = PSZ * PSZ * C;
@@ -86,9 +91,15 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
   constexpr bool FULL = (NV % G) == 0;       // every slot of every lane holds a value
   constexpr bool ROWMAP = ROWLEN == G;       // slot k == patch row k
   constexpr bool CP = C == 1 && ROWLEN == 2 * G && FULL;   // slot k == (row k / 2, column 2 lane + k % 2)
+  constexpr bool BLK = LPR > 0;
+  constexpr int CW = BLK ? ROWLEN / LPR : 1;            // floats of a row per lane
+  constexpr int RPL = BLK ? PSZ / (G / LPR) : 1;        // rows per lane
+  static_assert(!BLK || (FULL && !CP && !ROWMAP && CW * LPR == ROWLEN && RPL * (G / LPR) == PSZ && CW * RPL == VPL),
+                "block mapping must tile the patch exactly");
   typedef PSum<G, CP> Sum;
 
   const int lane = threadIdx.x % G;
+  const int blk_col = BLK ? (lane % LPR) * CW : 0, blk_row = BLK ? (lane / LPR) * RPL : 0;   // first float / row of the lane's block
   const int ip_raw = blockIdx.x * (blockDim.x / G) + threadIdx.x / G;
   const bool active = ip_raw < g.npatch;
   const int ip = active ? ip_raw : g.npatch - 1;
@@ -113,8 +124,13 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
     val[k] = FULL || n < NV;
     const int nn = val[k] ? n : 0;
     const int row = nn / ROWLEN;
-    off[k] = ROWMAP ? k * rowstride + lane : CP ? (k >> 1) * rowstride + 2 * lane + (k & 1) : row * rowstride + (nn - row * ROWLEN);
+    off[k] = ROWMAP ? k * rowstride + lane : CP ? (k >> 1) * rowstride + 2 * lane + (k & 1)
+           : BLK ? (blk_row + k / CW) * rowstride + blk_col + k % CW : row * rowstride + (nn - row * ROWLEN);
   }
+  // index of slot k in the row-major patch (pweight layout)
+  auto slot_index = [&](int k) {
+    return CP ? (k >> 1) * ROWLEN + 2 * lane + (k & 1) : BLK ? (blk_row + k / CW) * ROWLEN + blk_col + k % CW : k * G + lane;
+  };
 
   // ---- template, gradients, Hessian (patch.cpp:298-343, 69-86) ----
   float t[VPL], dx[VPL], dy[VPL];
@@ -196,7 +212,7 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
     // defined as 0
 #pragma unroll
     for (int k = 0; k < VPL; ++k)
-      if (val[k]) wout[CP ? (k >> 1) * ROWLEN + 2 * lane + (k & 1) : k * G + lane] = 0.f;
+      if (val[k]) wout[slot_index(k)] = 0.f;
   }
 
   const float bsq = o.normoutlier * o.normoutlier, bsq2 = bsq * 2.0f;
@@ -253,6 +269,24 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
         qs.add(2 * r, q[2 * r]);
         qs.add(2 * r + 1, q[2 * r + 1]);
         u0 = l0; u1 = l1; u2 = l2;
+      }
+    } else if (BLK) {
+      const float* p = qb + blk_row * rowstride + blk_col - C;   // left tap of the block's first value
+      float u[CW + C];
+#pragma unroll
+      for (int i = 0; i < CW + C; ++i) u[i] = __ldg(p - rowstride + i);
+#pragma unroll
+      for (int r = 0; r < RPL; ++r) {
+        float l[CW + C];
+#pragma unroll
+        for (int i = 0; i < CW + C; ++i) l[i] = __ldg(p + r * rowstride + i);
+#pragma unroll
+        for (int c = 0; c < CW; ++c) {
+          q[r * CW + c] = w0 * l[c + C] + w1 * l[c] + w2 * u[c + C] + w3 * u[c];
+          qs.add(r * CW + c, q[r * CW + c]);
+        }
+#pragma unroll
+        for (int i = 0; i < CW + C; ++i) u[i] = l[i];
       }
     } else if (ROWMAP) {
       const float* p = qb + lane;
@@ -322,7 +356,7 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
       if (nconv && active) {   // this evaluation is the patch's last one: its weights are the result
 #pragma unroll
         for (int k = 0; k < VPL; ++k)
-          if (val[k]) wout[CP ? (k >> 1) * ROWLEN + 2 * lane + (k & 1) : k * G + lane] = npw[k];
+          if (val[k]) wout[slot_index(k)] = npw[k];
       }
     }
     first = false;
@@ -336,27 +370,34 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
   }
 }
 
-template <int PSZ, int C, int G>
+template <int PSZ, int C, int G, int LPR = 0>
 static void launch_one(const PatchArgs& a, const LevelGeom& g, const OptConst& o, int n, cudaStream_t s) {
   const int threads = 128, per_block = threads / G;
   dim3 grd((g.npatch + per_block - 1) / per_block, n);
   if (o.mode == DISB200_MODE_OF)
-    patch_search_kernel<PSZ, C, G, true><<<grd, threads, 0, s>>>(a, g, o);
+    patch_search_kernel<PSZ, C, G, true, LPR><<<grd, threads, 0, s>>>(a, g, o);
   else
-    patch_search_kernel<PSZ, C, G, false><<<grd, threads, 0, s>>>(a, g, o);
+    patch_search_kernel<PSZ, C, G, false, LPR><<<grd, threads, 0, s>>>(a, g, o);
 }
 
 bool launch_patch_search(const PatchArgs& a, const LevelGeom& g, const OptConst& o, int n, cudaStream_t s,
                          LaunchStats* st) {
   const int key = o.psz * 10 + o.noc;
+  static const bool blockmap = !(getenv("DISB200_PATCH_MAP") && getenv("DISB200_PATCH_MAP")[0] == 'v');   // 'v': value-interleaved mapping (A/B switch)
   switch (key) {
     case 41: launch_one<4, 1, 8>(a, g, o, n, s); break;
     case 81: launch_one<8, 1, 4>(a, g, o, n, s); break;
-    case 121: launch_one<12, 1, 16>(a, g, o, n, s); break;
+    case 121:
+      if (blockmap) launch_one<12, 1, 8, 4>(a, g, o, n, s);     // 4 columns x 2 row groups: 6 rows x 3 floats per lane
+      else launch_one<12, 1, 16>(a, g, o, n, s);
+      break;
     case 161: launch_one<16, 1, 32>(a, g, o, n, s); break;
     case 43: launch_one<4, 3, 8>(a, g, o, n, s); break;
     case 83: launch_one<8, 3, 32>(a, g, o, n, s); break;
-    case 123: launch_one<12, 3, 32>(a, g, o, n, s); break;
+    case 123:
+      if (blockmap) launch_one<12, 3, 16, 4>(a, g, o, n, s);    // 4 columns x 4 row groups: 3 rows x 9 floats per lane
+      else launch_one<12, 3, 32>(a, g, o, n, s);
+      break;
     case 163: launch_one<16, 3, 32>(a, g, o, n, s); break;
     default: return false;
   }
