@@ -31,6 +31,7 @@ WORKLOADS = {
     "C1": (1, 1, 2, 1024, 436, "run_OF_INT op2 1024x436 grey"),
     "C2": (1, 3, 4, 1024, 436, "run_OF_RGB op4 1024x436 BGR"),
     "C3": (2, 1, 2, 1280, 720, "run_DE_INT op2 1280x720 grey stereo"),
+    "rgb2": (1, 3, 2, 1024, 436, "run_OF_RGB op2 1024x436 BGR"),
     "op1": (1, 1, 1, 1024, 436, "run_OF_INT op1 1024x436 grey"),
     "op3": (1, 1, 3, 1024, 436, "run_OF_INT op3 1024x436 grey"),
     "op4": (1, 1, 4, 1024, 436, "run_OF_INT op4 1024x436 grey"),

@@ -48,6 +48,12 @@ struct PSum {
     if (CP && (k & 1)) a1 += v;
     else a0 += v;
   }
+  // a0 += x * y; FM: as one fused multiply-add (only where the result is compared with a tolerance)
+  template <bool FM>
+  __device__ __forceinline__ void mad(int k, float x, float y) {
+    if (FM && !CP) a0 = fmaf(x, y, a0);
+    else add(k, x * y);
+  }
   __device__ __forceinline__ float total() const {
     if (!CP) return gsum<G>(a0);
     float r0 = a0, r1 = a1;
@@ -80,7 +86,7 @@ __device__ __forceinline__ void loss(float d, float bsq, float bsq2, float& pd, 
 // bilinear taps of a block row are CW + C consecutive floats and the lower taps of one row are the upper taps of the
 // next, so an iteration loads (RPL + 1)(CW + C) values for RPL CW results instead of four per result:
 // 28 for 18 (12 x 12 grey, 8 lanes) and 48 for 27 (12 x 12 BGR, 16 lanes).
-template <int PSZ, int C, int G, bool OF, int LPR = 0>
+template <int PSZ, int C, int G, bool OF, int LPR = 0, bool FM = false>
 __global__ void __launch_bounds__(128)   // (capping the column-pair variant at 96 registers for 5 CTAs per SM spills inside the loop: 1.60 -> 2.00 ms)
 patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
   constexpr int NV = PSZ * PSZ * C;
@@ -282,7 +288,8 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
         for (int i = 0; i < CW + C; ++i) l[i] = __ldg(p + r * rowstride + i);
 #pragma unroll
         for (int c = 0; c < CW; ++c) {
-          q[r * CW + c] = w0 * l[c + C] + w1 * l[c] + w2 * u[c + C] + w3 * u[c];
+          q[r * CW + c] = FM ? fmaf(w0, l[c + C], fmaf(w1, l[c], fmaf(w2, u[c + C], w3 * u[c])))
+                             : w0 * l[c + C] + w1 * l[c] + w2 * u[c + C] + w3 * u[c];
           qs.add(r * CW + c, q[r * CW + c]);
         }
 #pragma unroll
@@ -318,8 +325,8 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
     loss<COST>(QV - t[k], bsq, bsq2, vpd, vpw);                  \
     if (!FULL && !val[k]) { vpd = 0.f; vpw = 0.f; }              \
     npw[k] = vpw;                                                \
-    as0.add(k, dx[k] * vpd);                                     \
-    if (OF) as1.add(k, dy[k] * vpd);                             \
+    as0.template mad<FM>(k, dx[k], vpd);                         \
+    if (OF) as1.template mad<FM>(k, dy[k], vpd);                 \
     aws.add(k, fabsf(vpw));                                      \
   }
     float qscale = 1.0f;
@@ -370,32 +377,39 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
   }
 }
 
-template <int PSZ, int C, int G, int LPR = 0>
+template <int PSZ, int C, int G, int LPR = 0, bool FM = false>
 static void launch_one(const PatchArgs& a, const LevelGeom& g, const OptConst& o, int n, cudaStream_t s) {
   const int threads = 128, per_block = threads / G;
   dim3 grd((g.npatch + per_block - 1) / per_block, n);
   if (o.mode == DISB200_MODE_OF)
-    patch_search_kernel<PSZ, C, G, true, LPR><<<grd, threads, 0, s>>>(a, g, o);
+    patch_search_kernel<PSZ, C, G, true, LPR, FM><<<grd, threads, 0, s>>>(a, g, o);
   else
-    patch_search_kernel<PSZ, C, G, false, LPR><<<grd, threads, 0, s>>>(a, g, o);
+    patch_search_kernel<PSZ, C, G, false, LPR, FM><<<grd, threads, 0, s>>>(a, g, o);
 }
 
 bool launch_patch_search(const PatchArgs& a, const LevelGeom& g, const OptConst& o, int n, cudaStream_t s,
                          LaunchStats* st) {
   const int key = o.psz * 10 + o.noc;
-  static const bool blockmap = !(getenv("DISB200_PATCH_MAP") && getenv("DISB200_PATCH_MAP")[0] == 'v');   // 'v': value-interleaved mapping (A/B switch)
+  // A/B switch: DISB200_PATCH_MAP=v selects the value-interleaved mapping (value n in lane n % G) wherever the block
+  // mapping is the default.  The 12 x 12 kernels (op3 / op4, compared with a tolerance anyway: different reduction
+  // order) also contract the interpolation and the two projections into FMAs: op4 588 -> 728 pairs/s.  8 x 8 BGR
+  // (op2 of run_*_RGB) keeps separate multiplies and adds: FMA gains 3 % of that kernel there.
+  static const bool blockmap = !(getenv("DISB200_PATCH_MAP") && getenv("DISB200_PATCH_MAP")[0] == 'v');
   switch (key) {
     case 41: launch_one<4, 1, 8>(a, g, o, n, s); break;
     case 81: launch_one<8, 1, 4>(a, g, o, n, s); break;
-    case 121:
-      if (blockmap) launch_one<12, 1, 8, 4>(a, g, o, n, s);     // 4 columns x 2 row groups: 6 rows x 3 floats per lane
+    case 121:   // 4 columns x 2 row groups: 6 rows x 3 floats per lane (4 x 1 with 12 rows per lane: 233 registers, 6 % slower)
+      if (blockmap) launch_one<12, 1, 8, 4, true>(a, g, o, n, s);
       else launch_one<12, 1, 16>(a, g, o, n, s);
       break;
     case 161: launch_one<16, 1, 32>(a, g, o, n, s); break;
     case 43: launch_one<4, 3, 8>(a, g, o, n, s); break;
-    case 83: launch_one<8, 3, 32>(a, g, o, n, s); break;
-    case 123:
-      if (blockmap) launch_one<12, 3, 16, 4>(a, g, o, n, s);    // 4 columns x 4 row groups: 3 rows x 9 floats per lane
+    case 83:    // 4 columns x 2 row groups: 4 rows x 6 floats per lane
+      if (blockmap) launch_one<8, 3, 8, 4, false>(a, g, o, n, s);
+      else launch_one<8, 3, 32>(a, g, o, n, s);
+      break;
+    case 123:   // 4 columns x 4 row groups: 3 rows x 9 floats per lane
+      if (blockmap) launch_one<12, 3, 16, 4, true>(a, g, o, n, s);
       else launch_one<12, 3, 32>(a, g, o, n, s);
       break;
     case 163: launch_one<16, 3, 32>(a, g, o, n, s); break;
