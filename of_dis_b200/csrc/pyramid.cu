@@ -75,6 +75,41 @@ downscale_u8_kernel(const uint8_t* __restrict__ framesA, const uint8_t* __restri
       const unsigned* row = reinterpret_cast<const unsigned*>(f + (size_t)sy * w0 + xs);
       for (int i = 0; i < k / 4; ++i) sum[0] = __dp4a(__ldg(row + i), 0x01010101u, sum[0]);
     }
+  } else if (C == 3 && k >= 4 && xs >= 0 && xs + k <= w0 && ((xs & 3) == 0) && ((w0 & 3) == 0) && ((((size_t)f) & 3) == 0)) {
+    // BGR: a block row is 3 k consecutive bytes starting on a pixel boundary, read as 32-bit words; byte i of word
+    // wi belongs to channel (4 wi + i) % 3 = (wi + i) % 3, so one dp4a per word and channel with the selector
+    // {b0 + b3, b1, b2} rotated by wi % 3 sums it.
+    const unsigned sel[3] = {0x01000001u, 0x00000100u, 0x00010000u};
+    if (k == 8) {
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {   // 4 rows x 6 words in flight
+        unsigned v[4][6];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const unsigned* row = reinterpret_cast<const unsigned*>(f + ((size_t)clampi(y * 8 + half * 4 + j - padt, 0, h0 - 1) * w0 + xs) * 3);
+#pragma unroll
+          for (int wi = 0; wi < 6; ++wi) v[j][wi] = __ldg(row + wi);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+          for (int wi = 0; wi < 6; ++wi)
+#pragma unroll
+            for (int c = 0; c < 3; ++c) sum[c] = __dp4a(v[j][wi], sel[(c + 3 - wi % 3) % 3], sum[c]);
+      }
+    } else {
+      for (int j = 0; j < k; ++j) {
+        const unsigned* row = reinterpret_cast<const unsigned*>(f + ((size_t)clampi(y * k + j - padt, 0, h0 - 1) * w0 + xs) * 3);
+        for (int w3 = 0; w3 < 3 * k / 4; w3 += 3) {   // three words = four pixels
+#pragma unroll
+          for (int wi = 0; wi < 3; ++wi) {
+            const unsigned v = __ldg(row + w3 + wi);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) sum[c] = __dp4a(v, sel[(c + 3 - wi) % 3], sum[c]);
+          }
+        }
+      }
+    }
   } else {
     for (int j = 0; j < k; ++j) {
       const int sy = clampi(y * k + j - padt, 0, h0 - 1);
