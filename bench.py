@@ -203,6 +203,8 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU baseline sample budget per thread")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--sor", default="lexicographic", choices=["lexicographic", "redblack"],
+                    help="redblack: the throughput variant (a different iterate: ~0.04 px mean from the parity result, never the headline)")
     args = ap.parse_args()
     W_ = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -218,6 +220,8 @@ def main():
         p = p.copy(**C4_OVERRIDE)
         if args.batch is None:
             args.batch = 148          # one CTA per SM in the general wavefront SOR; 570 pairs/s at 16, 1305 at 96
+    if args.sor == "redblack":
+        p = p.copy(sor_mode=dis.SOR_REDBLACK)
     seq = args.workload == "C5"       # video: consecutive frames, pair i = (i, i+1), pyramids shared
     if seq:
         from of_dis_b200.synth import make_sequence
@@ -232,7 +236,8 @@ def main():
     bytes_per_pair = 2 * w0 * h0 * ch + 4 * w0 * h0 * nop     # compulsory traffic of the whole path
     config = {"workload": "%s: %s, params %s" % (args.workload, desc, " ".join("%g" % v for v in p.cli_args())),
               "pairs_per_step_per_gpu": args.batch, "frame": [w0, h0, ch], "l2_policy": "inputs+outputs per step (%.0f MB) exceed the 126 MB L2" % (args.batch * bytes_per_pair / 1e6),
-              "sor": "lexicographic wavefront (parity mode, bit-exact with solver.c sor_coupled)"}
+              "sor": "lexicographic wavefront (parity mode, bit-exact with solver.c sor_coupled)" if args.sor == "lexicographic"
+                     else "red-black (NOT the parity mode: a different iterate of the same system; `parity` below is against the lexicographic CPU reference)"}
 
     # ------------------------------------------------------------------ reference arm (CPU)
     if args.impl == "reference":
