@@ -335,3 +335,24 @@ def test_oracle_ncc_definition(port):
     e2 = np.sqrt(((port.run_dense(q, A, B2) - gt) ** 2).sum(-1)).mean()
     e2_l2 = np.sqrt(((port.run_dense(q.copy(costfct=0), A, B2) - gt) ** 2).sum(-1)).mean()
     assert e < 1.5 and e2 < e + 0.1 and e2 < e2_l2
+
+
+# ---------------------------------------------------------------- bench.py, reference arm (runs on host cores only)
+def test_bench_reference_arm_prints_the_contract_line():
+    """`bench.py --impl reference` times the reference's CPU code (oracle/_ref, else the restatement) and needs no GPU:
+    one JSON line with the contract's keys, the same metric / unit / config as the GPU arm."""
+    import json
+    import subprocess
+    import sys
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "2", "--warmup", "1"],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [l for l in r.stdout.splitlines() if l.startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["metric"] == "frame_pairs_per_s" and d["unit"] == "pairs/s"
+    assert d["value"] > 0 and d["higher_is_better"] is True and d["n_gpus"] == 1 and d["steps"] == 2 and d["warmup"] == 1
+    assert d["config"]["workload"].startswith("C1: run_OF_INT op2 1024x436 grey")
+    assert d["cpu_baseline"]["kind"] in ("reference", "port") and d["cpu_baseline"]["cores"] >= 1
+    assert d["cpu_baseline"]["value"] == d["value"] == d["e2e"]["value"]
+    assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
