@@ -229,6 +229,16 @@ def test_flo_and_pfm_writers_use_the_reference_framing(dis, tmp_path):
     raw = open(f, "rb").read()
     assert raw[:4] == b"PIEH" and struct.unpack("<ii", raw[4:12]) == (5, 3)          # run_dense.cpp:29-32
     assert np.array_equal(np.frombuffer(raw[12:], np.float32).reshape(3, 5, 2), fl)
+    # SaveFlowFile writes img.channels() floats per pixel: depth (1) and scene flow (4) share the framing (run_dense.cpp:37-51)
+    for nc in (1, 4):
+        x = (np.arange(3 * 5 * nc, dtype=np.float32).reshape(3, 5, nc) * 0.5 - 3)
+        f = str(tmp_path / ("c%d.flo" % nc))
+        dis.save_flo(f, x[..., 0] if nc == 1 else x)
+        raw = open(f, "rb").read()
+        assert raw[:4] == b"PIEH" and struct.unpack("<ii", raw[4:12]) == (5, 3) and len(raw) == 12 + 3 * 5 * nc * 4
+        assert np.array_equal(np.frombuffer(raw[12:], np.float32).reshape(3, 5, nc), x)
+    with pytest.raises(dis.DisError):
+        dis.save_flo(str(tmp_path / "bad.flo"), np.zeros((3, 5, 3), np.float32))
     d = fl[..., 0]
     f = str(tmp_path / "a.pfm")
     dis.save_pfm(f, d)
