@@ -1,7 +1,7 @@
 """TEST INFRASTRUCTURE ONLY - ctypes bindings to the parity oracles.
 
 * ``Port``  -> oracle/libdisoracle.so  (CPU restatement, oracle/dis_oracle.cpp)
-* ``Ref``   -> oracle/_ref/libref_{OF,DE}_{INT,RGB}.so (the reference's own sources compiled
+* ``Ref``   -> oracle/_ref/libref_{OF,DE}_{INT,RGB,GRAD}.so (the reference's own sources compiled
                unmodified by oracle/Makefile; exists only where /root/reference was present at
                build time or the prebuilt .so travelled with the snapshot)
 

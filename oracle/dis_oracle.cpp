@@ -11,8 +11,9 @@
 // and (b) for the OpenCV steps the reference delegates (resize, Sobel,
 // copyMakeBorder, final resize; run_dense.cpp:131-179,299-312,407-415) against
 // python-cv2 4.13 golden vectors in tests/golden/ (made by
-// tests/golden/make_golden.py).  The reference itself ships no test vectors
-// (SURVEY.md 4).
+// tests/golden/make_golden.py; the gradient-magnitude input of SELECTCHANNEL == 2,
+// whose pyramid runs on arbitrary floats, by tests/golden/make_gradmag_golden.py).
+// The reference itself ships no test vectors.
 //
 // Build: make -C oracle port   (g++ -O2 -ffp-contract=off, no FMA).
 #include <algorithm>
