@@ -152,6 +152,9 @@ int disb200_varref_level(const DisParams* params, const float* im_a, const float
 /* File writers with the reference's framing (run_dense.cpp:17-82). */
 int disb200_save_flo(const char* path, const float* flow, int w, int h, int nc);
 int disb200_save_pfm(const char* path, const float* disp, int w, int h);
+/* ReadFlowFile (run_dense.cpp:84-128): the caller states nc (1 depth, 2 flow, 4 scene flow; the file does not store
+ * it); *data is malloc'ed (release with disb200_free).  Short, long or mistagged files give DISB200_EIO. */
+int disb200_read_flo(const char* path, int nc, float** data, int* w, int* h);
 /* Binary PGM (P5) / PPM (P6) reader standing in for cv::imread (run_dense.cpp:209-210):
  * want_channels 1 -> grey, 3 -> BGR interleaved.  *data is malloc'ed; release with disb200_free. */
 int disb200_read_pnm(const char* path, int want_channels, uint8_t** data, int* w, int* h);

@@ -283,6 +283,18 @@ def save_flo(path: str, flow: np.ndarray):
     _check(lib().disb200_save_flo(path.encode(), _ptr(flow), w, h, nc))
 
 
+def read_flo(path: str, nc: int = 2) -> np.ndarray:
+    """ReadFlowFile (run_dense.cpp:84-128): (h, w, nc) float32, or (h, w) for nc == 1."""
+    data = C.POINTER(C.c_float)()
+    w, h = C.c_int(), C.c_int()
+    _check(lib().disb200_read_flo(path.encode(), nc, C.byref(data), C.byref(w), C.byref(h)))
+    try:
+        arr = np.ctypeslib.as_array(data, shape=(h.value * w.value * nc,)).copy()
+    finally:
+        lib().disb200_free(data)
+    return arr.reshape((h.value, w.value) if nc == 1 else (h.value, w.value, nc))
+
+
 def save_pfm(path: str, disp: np.ndarray):
     disp = np.ascontiguousarray(disp, np.float32)
     h, w = disp.shape[:2]

@@ -32,6 +32,34 @@ int disb200_save_flo(const char* path, const float* flow, int w, int h, int nc) 
   return ok ? DISB200_OK : DISB200_EIO;
 }
 
+// ReadFlowFile, run_dense.cpp:84-128 (the reader of the disabled warm-start block, run_dense.cpp:356-379): 4-byte tag,
+// int32 width, int32 height, then width * height * nc f32.  The file does not store nc: like the reference
+// (img.channels()) the caller says what it expects.  Where the reference only prints ("problem reading", "file is too
+// short", "file is too long") this returns DISB200_EIO; the tag is checked against "PIEH" as well.
+int disb200_read_flo(const char* path, int nc, float** data, int* w, int* h) {
+  if (!path || !data || !w || !h || (nc != 1 && nc != 2 && nc != 4)) return DISB200_EINVAL;
+  *data = nullptr;
+  FILE* f = std::fopen(path, "rb");
+  if (!f) return DISB200_EIO;
+  char tag[4];
+  int ww = 0, hh = 0;
+  bool ok = std::fread(tag, 1, 4, f) == 4 && std::memcmp(tag, "PIEH", 4) == 0;
+  ok = ok && std::fread(&ww, sizeof(int), 1, f) == 1 && std::fread(&hh, sizeof(int), 1, f) == 1;
+  ok = ok && ww > 0 && hh > 0 && (size_t)ww * hh <= ((size_t)1 << 31);
+  float* buf = nullptr;
+  if (ok) {
+    const size_t n = (size_t)ww * hh * nc;
+    buf = static_cast<float*>(std::malloc(n * sizeof(float)));
+    if (!buf) { std::fclose(f); return DISB200_ENOMEM; }
+    ok = std::fread(buf, sizeof(float), n, f) == n;        // "file is too short"
+    ok = ok && std::fgetc(f) == EOF;                        // "file is too long"
+  }
+  std::fclose(f);
+  if (!ok) { std::free(buf); return DISB200_EIO; }
+  *data = buf; *w = ww; *h = hh;
+  return DISB200_OK;
+}
+
 // SavePFMFile, run_dense.cpp:61-82: "Pf\n<w> <h>\n-1.000000\n", rows bottom-up, value = -disparity.
 int disb200_save_pfm(const char* path, const float* disp, int w, int h) {
   if (!path || !disp || w <= 0 || h <= 0) return DISB200_EINVAL;

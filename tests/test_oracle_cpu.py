@@ -249,6 +249,36 @@ def test_flo_and_pfm_writers_use_the_reference_framing(dis, tmp_path):
     assert np.array_equal(body, -d[::-1])                                              # bottom-up, negated (:72-79)
 
 
+def test_flo_reader_round_trip_and_error_paths(dis, tmp_path):
+    """ReadFlowFile (run_dense.cpp:84-128): what SaveFlowFile wrote comes back bit for bit for depth, flow and scene
+    flow; where the reference only prints (short / long file) the library returns DISB200_EIO."""
+    rng = np.random.default_rng(3)
+    for nc in (1, 2, 4):
+        x = rng.standard_normal((7, 11, nc)).astype(np.float32)
+        f = str(tmp_path / ("r%d.flo" % nc))
+        dis.save_flo(f, x[..., 0] if nc == 1 else x)
+        got = dis.read_flo(f, nc)
+        assert got.shape == ((7, 11) if nc == 1 else (7, 11, nc)) and np.array_equal(got.reshape(7, 11, nc), x)
+    f2 = str(tmp_path / "r2.flo")
+    raw = open(f2, "rb").read()
+    with pytest.raises(dis.DisError) as e:          # a flow file read as scene flow is too short
+        dis.read_flo(f2, 4)
+    assert e.value.code == 5
+    with pytest.raises(dis.DisError):               # ... and too long when read as depth
+        dis.read_flo(f2, 1)
+    open(tmp_path / "trunc.flo", "wb").write(raw[:-4])
+    open(tmp_path / "long.flo", "wb").write(raw + b"\0")
+    open(tmp_path / "tag.flo", "wb").write(b"XXXX" + raw[4:])
+    open(tmp_path / "hdr.flo", "wb").write(raw[:10])
+    for name in ("trunc.flo", "long.flo", "tag.flo", "hdr.flo", "missing.flo"):
+        with pytest.raises(dis.DisError) as e:
+            dis.read_flo(str(tmp_path / name), 2)
+        assert e.value.code == 5, name
+    with pytest.raises(dis.DisError) as e:
+        dis.read_flo(f2, 3)
+    assert e.value.code == 1
+
+
 def test_pnm_reader(dis, tmp_path):
     rng = np.random.default_rng(0)
     g = rng.integers(0, 256, (7, 9), dtype=np.uint8)
