@@ -213,6 +213,28 @@ def test_compute_entry_points_fail_loudly_without_gpu(dis):
     assert e.value.code == 2 and "no CPU path" in str(e.value)
 
 
+def test_clis_fail_loudly_without_gpu(dis, tmp_path):
+    """The run_* binaries (all six SELECTMODE x SELECTCHANNEL builds) have no CPU path either: usage on bad argv,
+    a clear error and a non-zero exit code when no device is present."""
+    exe_dir = os.path.join(ROOT, "of_dis_b200", "bin")
+    names = ["run_OF_INT", "run_OF_RGB", "run_DE_INT", "run_DE_RGB", "run_OF_GRAD", "run_DE_GRAD"]
+    for n in names + ["disb200_batch"]:
+        assert os.access(os.path.join(exe_dir, n), os.X_OK), n
+    r = subprocess.run([os.path.join(exe_dir, "run_OF_INT")], capture_output=True, text=True)
+    assert r.returncode != 0 and "usage" in (r.stderr + r.stdout)
+    if dis.device_count() > 0:
+        pytest.skip("a GPU is present")
+    img = np.random.default_rng(0).integers(0, 256, (60, 100), dtype=np.uint8)
+    for name, data, hdr in (("a.pgm", img, b"P5\n100 60\n255\n"), ("a.ppm", np.repeat(img[..., None], 3, -1), b"P6\n100 60\n255\n")):
+        with open(tmp_path / name, "wb") as f:
+            f.write(hdr + data.tobytes())
+    for n in names:
+        src = str(tmp_path / ("a.ppm" if n.endswith("RGB") else "a.pgm"))
+        r = subprocess.run([os.path.join(exe_dir, n), src, src, str(tmp_path / "o.flo")], capture_output=True, text=True)
+        assert r.returncode == 2 and "no CPU path" in (r.stderr + r.stdout), (n, r.stdout, r.stderr)
+        assert not os.path.exists(tmp_path / "o.flo")
+
+
 def test_invalid_parameters_are_rejected(dis):
     p = dis.operating_point(2, 256)
     for kw in (dict(mode=3), dict(channels=2), dict(sc_l=4, sc_f=3), dict(patove=1.0), dict(patchsz=7), dict(costfct=3), dict(sor_mode=2), dict(gradmag=2),
