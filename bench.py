@@ -38,8 +38,12 @@ WORKLOADS = {
     "C5": (1, 1, 2, 1920, 1080, "run_OF_INT op2 1920x1080 grey video pairs"),
     # SURVEY.md 8(d) C4, lighter explicit line: fwd/bwd consistency, L1 cost, finest level 960x544
     "C4": (1, 1, 2, 3840, 2160, "run_OF_INT explicit params 3840x2160 grey, fb consistency + L1"),
+    "C4h": (1, 1, 2, 3840, 2160, "run_OF_INT explicit params 3840x2160 grey, fb consistency + L1, 12x12 patches to level 1"),
 }
-C4_OVERRIDE = dict(sc_f=7, sc_l=2, max_iter=16, min_iter=16, patchsz=8, patove=0.4, usefbcon=1, costfct=1)
+# BASELINE.json does not pin C4's 20 parameters.  "C4" is the survey's lighter line (87 k patches, finest
+# level 960x544), "C4h" its proposed heavy one (12x12 patches at overlap .75 down to level 1: 620 k patches fwd + bwd).
+C4_LINES = {"C4": dict(sc_f=7, sc_l=2, max_iter=16, min_iter=16, patchsz=8, patove=0.4, usefbcon=1, costfct=1),
+            "C4h": dict(sc_f=7, sc_l=1, max_iter=16, min_iter=16, patchsz=12, patove=0.75, usefbcon=1, costfct=1)}
 N_DISTINCT = 4  # distinct synthetic pairs, tiled over the batch
 DEFAULT_BATCH = 1776  # 2 sub-batch streams x 6 resident one-warp SORs x 148 SMs
 
@@ -119,37 +123,169 @@ def to_orc(p):
     return q
 
 
-def cpu_runner(p, A, B):
-    """(one, kind): one(i) -> full-resolution flow of pair i % len(A) from the reference's CPU code.
-
-    OFClass comes from oracle/_ref (the reference's own sources) when that library travelled
-    with the snapshot, else from the restatement; pyramid and final upsample are the OpenCV
-    restatement in both cases (OpenCV itself is unavailable).
-    """
+def orc_workload_params(workload):
+    """The workload's parameters as the oracle's struct, built WITHOUT touching libdisb200.so (the reference arm
+    must not load the product library)."""
     from oracle import bindings as ob
-    port = ob.Port()
-    q = to_orc(p)
-    kind = "port"
-    ref = None
-    if ob.have_ref(p.mode, p.channels):
-        try:
-            ref = ob.Ref(p.mode, p.channels)
-            kind = "reference"
-        except Exception:
-            ref = None
-    h0, w0 = A.shape[1:3]
-    W, H, padl, padt = port.pad_dims(w0, h0, p.sc_f)
+    mode, ch, op, w0, h0, _ = WORKLOADS[workload]
+    q = ob.Port().operating_point(op, w0, mode, ch).copy(verbosity=0)
+    if workload in C4_LINES:
+        q = q.copy(**{{"patchsz": "psz"}.get(k, k): v for k, v in C4_LINES[workload].items()})
+    return q
 
-    def one(i):
-        a, b = A[i % len(A)], B[i % len(B)]
-        if ref is None:
-            return port.run_dense(q, a, b)
-        PA = port.pyramid(a, p.sc_f, p.sc_l, p.patchsz)
-        PB = port.pyramid(b, p.sc_f, p.sc_l, p.patchsz)
-        low = ref.ofclass(q, PA, PB, W, H)
-        return port.upsample_crop(low, p.sc_l, padl, padt, w0, h0)
 
-    return one, kind
+def repo_libs_loaded():
+    """Shared objects under the repository mapped into this process (the reference arm must list oracle/ only)."""
+    libs = set()
+    try:
+        with open("/proc/self/maps") as f:
+            for ln in f:
+                path = ln.split()[-1]
+                if path.startswith(ROOT) and ".so" in path:
+                    libs.add(os.path.relpath(path, ROOT))
+    except OSError:
+        pass
+    return sorted(libs)
+
+
+def orc_cli_args(q):
+    return [q.sc_f, q.sc_l, q.max_iter, q.min_iter, q.dp_thresh, q.dr_thresh, q.res_thresh, q.psz, q.patove, q.usefbcon,
+            q.patnorm, q.costfct, q.usetvref, q.tv_alpha, q.tv_gamma, q.tv_delta, q.tv_innerit, q.tv_solverit, q.tv_sor, q.verbosity]
+
+
+class CpuArm:
+    """The reference's CPU implementation of the path, split the way SURVEY 8(d) asks for it:
+
+      core     = the OFC::OFClass constructor (oflow.cpp:31-338, the reference's own "O.Flow Run-Time"), from
+                 oracle/_ref (the reference's sources compiled unmodified) when that library travelled with the
+                 snapshot (kind "reference"), else the restatement (kind "port")
+      pre/post = dimension padding + ConstructImgPyramide for both frames + resize/crop (run_dense.cpp:131-179,
+                 299-312,407-415): python-cv2 (the same OpenCV the reference links, SIMD build; kind_prepost "cv2"),
+                 else the scalar restatement ("port")
+    """
+
+    def __init__(self, q, A, B, force_port_prepost=False):
+        from oracle import bindings as ob
+        from oracle import cv2_prepost as cp
+        self.q, self.A, self.B = q, A, B
+        self.port = ob.Port()
+        self.kind, self.ref = "port", None
+        if ob.have_ref(q.mode, q.noc, bool(q.gradmag)):
+            try:
+                self.ref = ob.Ref(q.mode, q.noc, bool(q.gradmag))
+                self.kind = "reference"
+            except Exception:
+                self.ref = None
+        self.cp = cp if (cp.HAVE_CV2 and not force_port_prepost) else None
+        self.kind_prepost = "cv2" if self.cp else "port"
+        self.h0, self.w0 = A.shape[1:3]
+        self.W, self.H, self.padl, self.padt = self.port.pad_dims(self.w0, self.h0, q.sc_f)
+
+    def pre(self, i):
+        a, b = self.A[i % len(self.A)], self.B[i % len(self.B)]
+        q = self.q
+        if self.cp:
+            return (self.cp.pyramid(self.cp.pad_frame(a, q.sc_f)[0], q.sc_f, q.psz, bool(q.gradmag)),
+                    self.cp.pyramid(self.cp.pad_frame(b, q.sc_f)[0], q.sc_f, q.psz, bool(q.gradmag)))
+        return (self.port.pyramid(a, q.sc_f, q.sc_l, q.psz, bool(q.gradmag)), self.port.pyramid(b, q.sc_f, q.sc_l, q.psz, bool(q.gradmag)))
+
+    def core(self, PA, PB):
+        return (self.ref or self.port).ofclass(self.q, PA, PB, self.W, self.H)
+
+    def post(self, low):
+        if self.cp:
+            return self.cp.upsample_crop(low, self.q.sc_l, self.padl, self.padt, self.w0, self.h0)
+        return self.port.upsample_crop(low, self.q.sc_l, self.padl, self.padt, self.w0, self.h0)
+
+    def one(self, i):
+        return self.post(self.core(*self.pre(i)))
+
+    def measure(self, seconds_budget, workers, windows=1, warm_windows=0):
+        """-> dict.  Single-threaded worker PROCESSES ("N independent pairs on N host cores, one
+        process-level worker per core"), all counting the pairs they finish inside common fixed windows: first ONE
+        worker (the reference's default build has no OpenMP: per-pair ms of the core and of pre/post), then `workers`
+        of them = the whole host.  `value` = core + pre/post on all cores, median over `windows` windows."""
+        w1 = max(1.0, seconds_budget * 0.08)
+        a1, c1 = run_cpu_workers(self, 1, w1, 1)
+        core1 = w1 / max(c1[0], 1)
+        all1 = w1 / max(a1[0], 1)
+        nwin = windows + warm_windows
+        wN = max(0.5, seconds_budget * 0.3 / nwin)
+        aN, cN = run_cpu_workers(self, workers, wN, nwin)
+        v_all = statistics.median(aN[warm_windows:]) / wN
+        v_core = statistics.median(cN[warm_windows:]) / wN
+        return {"value": v_all, "unit": "pairs/s", "cores": workers, "kind": self.kind, "kind_prepost": self.kind_prepost,
+                "core_ms_1t": core1 * 1e3, "prepost_ms_1t": (all1 - core1) * 1e3, "pairs_per_s_1t": 1.0 / all1, "core_pairs_per_s_1t": 1.0 / core1,
+                "core_pairs_per_s": v_core, "core_plus_prepost_pairs_per_s": v_all,
+                "per_window_pairs_per_s": [round(x / wN, 1) for x in aN],
+                "sample": "%d single-threaded worker processes, %d windows of %.2f s each for (core + pre/post) and for (core only), median "
+                          "of the last %d: %d and %d pairs per window; one worker alone: %d and %d pairs in %.1f s"
+                          % (workers, nwin, wN, windows, statistics.median(aN[warm_windows:]), statistics.median(cN[warm_windows:]), a1[0], c1[0], w1)}
+
+
+def run_cpu_workers(arm, workers, window, nwin):
+    """Spawn `workers` fresh single-threaded processes of this script (--cpu-worker); all start at the same wall-clock
+    instant and count the pairs they finish inside `nwin` consecutive `window`-second slots, first of the whole step
+    (pyramids + OFClass + resize), then of OFClass alone.  -> (per-window totals whole step, per-window totals core)."""
+    import subprocess
+    import tempfile
+    with tempfile.TemporaryDirectory() as td:
+        npz = os.path.join(td, "in.npz")
+        np.savez(npz, A=arm.A, B=arm.B, q=np.frombuffer(bytes(arm.q), np.uint8), port_prepost=np.array(arm.cp is None))
+        start = time.time() + 4.0 + 0.05 * workers       # interpreter + library start-up of the workers
+        env = dict(os.environ, OMP_NUM_THREADS="1", OPENBLAS_NUM_THREADS="1",
+                   # steady-state allocator: keep the multi-MB image buffers on the heap instead of mmap/munmap + page
+                   # faults per call - what a long-running host process sees (measured: 326 -> 635 pairs/s on 8 cores)
+                   MALLOC_MMAP_THRESHOLD_="33554432", MALLOC_TRIM_THRESHOLD_="1073741824", MALLOC_TOP_PAD_="268435456")
+        procs = [subprocess.Popen([sys.executable, os.path.abspath(__file__), "--cpu-worker", npz, repr(start), repr(window), str(nwin)],
+                                  stdout=subprocess.PIPE, env=env) for _ in range(workers)]
+        n_all, n_core = [0] * nwin, [0] * nwin
+        for pr in procs:
+            out = pr.communicate()[0].decode().strip().splitlines()
+            if pr.returncode != 0 or not out:
+                raise RuntimeError("CPU baseline worker failed")
+            r = json.loads(out[-1])
+            if r["late"]:
+                raise RuntimeError("CPU baseline worker started after the common start time; raise the start-up margin")
+            n_all = [x + y for x, y in zip(n_all, r["n_all"])]
+            n_core = [x + y for x, y in zip(n_core, r["n_core"])]
+    return n_all, n_core
+
+
+def cpu_worker_main(npz, start, window, nwin):
+    from oracle.bindings import OrcParams
+    d = np.load(npz)
+    q = OrcParams.from_buffer_copy(d["q"].tobytes())
+    arm = CpuArm(q, d["A"], d["B"], force_port_prepost=bool(d["port_prepost"]))
+    pyrs = [arm.pre(i) for i in range(len(arm.A))]
+    arm.one(0)                                           # warm-up
+    late = time.time() > start
+    res = {}
+    i = 0
+    for name, fn in (("n_all", arm.one), ("n_core", lambda k: arm.core(*pyrs[k % len(pyrs)]))):
+        while time.time() < start:
+            pass
+        cnt = [0] * nwin
+        end = start + nwin * window
+        while True:
+            fn(i); i += 1
+            t = time.time()
+            if t >= end:
+                break
+            cnt[int((t - start) / window)] += 1          # a pair counts for the window it finishes in
+        res[name] = cnt
+        start = end + 0.5
+    res["late"] = late
+    print(json.dumps(res))
+    return 0
+
+
+def cpu_runner(p, A, B):
+    """(one, kind): one(i) -> full-resolution flow of pair i % len(A), the PARITY checker: the reference's OFClass
+    (oracle/_ref when present) between the restatement's pyramid and upsample (bit-identical to cv2's on u8 frames,
+    tests/test_oracle_cpu.py; cv2's own resize differs from it by <= 1e-5 px in the last step)."""
+    arm = CpuArm(to_orc(p), A, B, force_port_prepost=True)
+    return arm.one, arm.kind
 
 
 def epe_stats(a, b):
@@ -173,26 +309,9 @@ def parity_report(p, A, B, G, hd):
     return rep
 
 
-def cpu_reference_throughput(p, A, B, seconds_budget, threads):
-    """pairs/s of the reference's CPU code for the same path on `threads` host threads (ctypes releases the
-    GIL, so plain Python threads run the C code in parallel)."""
-    from concurrent.futures import ThreadPoolExecutor
-    one, kind = cpu_runner(p, A, B)
-
-    t = time.perf_counter()
-    one(0)
-    t1 = time.perf_counter() - t
-    per_thread = max(2, min(64, int(seconds_budget / max(t1, 1e-4))))
-    n = per_thread * threads
-    with ThreadPoolExecutor(threads) as ex:
-        list(ex.map(one, range(threads)))  # warm-up
-        t = time.perf_counter()
-        list(ex.map(one, range(n)))
-        dt = time.perf_counter() - t
-    return n / dt, kind, "%d pairs on %d threads, %.1f s wall (1 pair single-thread %.1f ms)" % (n, threads, dt, t1 * 1e3)
-
-
 def main():
+    if len(sys.argv) == 6 and sys.argv[1] == "--cpu-worker":
+        return cpu_worker_main(sys.argv[2], float(sys.argv[3]), float(sys.argv[4]), int(sys.argv[5]))
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -200,7 +319,8 @@ def main():
     ap.add_argument("--batch", type=int, default=None, help="frame pairs per step per GPU (default 1776 = two sub-batches of 6 resident SOR warps on each of the 148 SMs; C4: 16, C5: 256)")
     ap.add_argument("--workload", default="C1", choices=sorted(WORKLOADS))
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="CPU baseline sample budget per thread")
+    ap.add_argument("--cpu-seconds", type=float, default=20.0, help="CPU baseline sample budget (seconds of measuring windows)")
+    ap.add_argument("--ref-seconds", type=float, default=150.0, help="--impl reference: total budget of the measuring windows")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--sor", default="lexicographic", choices=["lexicographic", "redblack"],
@@ -214,14 +334,9 @@ def main():
     mode, ch, op, w0, h0, desc = WORKLOADS[args.workload]
     nop = 2 if mode == 1 else 1
 
-    import of_dis_b200 as dis   # raises if libdisb200.so is missing: there is no fallback
-    p = dis.operating_point(op, w0, mode, ch).copy(verbosity=0)
-    if args.workload == "C4":
-        p = p.copy(**C4_OVERRIDE)
-        if args.batch is None:
-            args.batch = 148          # one CTA per SM in the general wavefront SOR; 570 pairs/s at 16, 1305 at 96
-    if args.sor == "redblack":
-        p = p.copy(sor_mode=dis.SOR_REDBLACK)
+    q_orc = orc_workload_params(args.workload)     # oracle-side struct: the reference arm never loads libdisb200.so
+    if args.workload in C4_LINES and args.batch is None:
+        args.batch = 148 if args.workload == "C4" else 8   # C4: one CTA per SM in the general wavefront SOR; 570 pairs/s at 16, 1305 at 96
     seq = args.workload == "C5"       # video: consecutive frames, pair i = (i, i+1), pyramids shared
     if seq:
         from of_dis_b200.synth import make_sequence
@@ -230,11 +345,11 @@ def main():
         if args.batch is None:
             args.batch = 256          # BASELINE.json configs[4]: 256 consecutive pairs
     else:
-        A, B, G = make_inputs(mode, ch, w0, h0)
+        A, B, G = make_inputs(mode, ch, w0, h0, 1 if args.workload in C4_LINES else N_DISTINCT)
     if args.batch is None:
         args.batch = DEFAULT_BATCH
     bytes_per_pair = 2 * w0 * h0 * ch + 4 * w0 * h0 * nop     # compulsory traffic of the whole path
-    config = {"workload": "%s: %s, params %s" % (args.workload, desc, " ".join("%g" % v for v in p.cli_args())),
+    config = {"workload": "%s: %s, params %s" % (args.workload, desc, " ".join("%g" % v for v in orc_cli_args(q_orc))),
               "pairs_per_step_per_gpu": args.batch, "frame": [w0, h0, ch], "l2_policy": "inputs+outputs per step (%.0f MB) exceed the 126 MB L2" % (args.batch * bytes_per_pair / 1e6),
               "sor": "lexicographic wavefront (parity mode, bit-exact with solver.c sor_coupled)" if args.sor == "lexicographic"
                      else "red-black (NOT the parity mode: a different iterate of the same system; `parity` below is against the lexicographic CPU reference)"}
@@ -244,22 +359,27 @@ def main():
         if rank != 0:
             return 0
         threads = os.cpu_count() or 1
-        vals = []
-        sample = ""
-        kind = "port"
-        for s in range(max(args.warmup, 0) + max(args.steps, 1)):
-            v, kind, sample = cpu_reference_throughput(p, A, B, max(0.5, 60.0 / max(args.steps + args.warmup, 1) / 4), threads)
-            if s >= args.warmup:
-                vals.append(v)
-        v = statistics.median(vals)
+        arm = CpuArm(q_orc, A, B)
+        # every "step" is one window of the worker processes' run: a bounded sample of the workload (whole run ~ 2 min)
+        cpu = arm.measure(args.ref_seconds, threads, windows=max(args.steps, 1), warm_windows=max(args.warmup, 0))
+        v = cpu["value"]
+        config["pairs_per_step_per_gpu"] = None          # the CPU arm has no batch: a step is a bounded sample of pairs
+        config["sample_per_step"] = cpu["sample"]
         line = {"impl": "reference", "metric": "frame_pairs_per_s", "value": v, "unit": "pairs/s", "mpix_per_s": v * w0 * h0 / 1e6,
-                "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / v,
+                "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_pair_all_cores": 1e3 / v,
+                "ms_per_step": 1e3 * args.batch / v, "ms_per_step_note": "time the host cores need for one %d-pair step of the GPU arm" % args.batch,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": config,
-                "cpu_baseline": {"value": v, "unit": "pairs/s", "cores": threads, "kind": kind, "sample": sample},
+                "config": config, "cpu_baseline": cpu, "native_so_loaded": repo_libs_loaded(),
                 "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
         print(json.dumps(line))
         return 0
+
+    import of_dis_b200 as dis   # raises if libdisb200.so is missing: there is no fallback
+    p = dis.operating_point(op, w0, mode, ch).copy(verbosity=0)
+    if args.workload in C4_LINES:
+        p = p.copy(**C4_LINES[args.workload])
+    if args.sor == "redblack":
+        p = p.copy(sor_mode=dis.SOR_REDBLACK)
 
     # ------------------------------------------------------------------ our arm (GPU)
     import torch
@@ -456,8 +576,7 @@ def main():
     cpu = parity = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
-        v, kind, sample = cpu_reference_throughput(p, A, B, args.cpu_seconds / 4, threads)
-        cpu = {"value": v, "unit": "pairs/s", "cores": threads, "kind": kind, "sample": sample}
+        cpu = CpuArm(q_orc, A, B).measure(args.cpu_seconds, threads)
         parity = parity_report(p, A, B, G, hd)
 
     if rank == 0:

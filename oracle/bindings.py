@@ -117,10 +117,20 @@ class Port:
         return out
 
     def pyramid(self, img_u8, sc_f, sc_l, pad, gradmag=False):
-        """-> ({level: img}, {level: dx}, {level: dy})"""
+        """-> ({level: img}, {level: dx}, {level: dy}); one cascade per frame"""
+        h0, w0 = img_u8.shape[:2]
+        Cn = 1 if img_u8.ndim == 2 else img_u8.shape[2]
+        W, H, _, _ = self.pad_dims(w0, h0, sc_f)
         I, X, Y = {}, {}, {}
         for l in range(sc_l, sc_f + 1):
-            I[l], X[l], Y[l] = self.pyramid_level(img_u8, sc_f, l, pad, gradmag)
+            shp = ((H >> l) + 2 * pad, (W >> l) + 2 * pad, Cn)
+            I[l], X[l], Y[l] = (np.empty(shp, np.float32) for _ in range(3))
+        img_u8 = np.ascontiguousarray(img_u8)
+        self.lib.orc_set_pyramid_gradmag(int(bool(gradmag)))
+        try:
+            self.lib.orc_pyramid_all(_p(img_u8, u8p), w0, h0, Cn, sc_f, sc_l, pad, pyr_ptrs(I, sc_f), pyr_ptrs(X, sc_f), pyr_ptrs(Y, sc_f))
+        finally:
+            self.lib.orc_set_pyramid_gradmag(0)
         return I, X, Y
 
     def halve(self, src):

@@ -179,6 +179,17 @@ void upsample_crop(const float* flow, int w_l, int h_l, int nop, int sc_l, int p
   }
   const double inv = 1.0 / k;
   const float sc = (float)k;
+  // per-column source coordinates do not depend on the row: computed once (same expressions, same bits)
+  std::vector<int> sx0(w0), sx1v(w0);
+  std::vector<float> fxv(w0);
+  for (int x = 0; x < w0; ++x) {
+    float fx = (float)((x + padl + 0.5) * inv - 0.5);
+    int sx = (int)std::floor(fx);
+    fx -= sx;
+    if (sx < 0) { sx = 0; fx = 0.f; }
+    if (sx >= w_l - 1) { sx = w_l - 1; fx = 0.f; }
+    sx0[x] = sx; sx1v[x] = std::min(sx + 1, w_l - 1); fxv[x] = fx;
+  }
   for (int y = 0; y < h0; ++y) {
     float fy = (float)((y + padt + 0.5) * inv - 0.5);
     int sy = (int)std::floor(fy);
@@ -186,18 +197,17 @@ void upsample_crop(const float* flow, int w_l, int h_l, int nop, int sc_l, int p
     if (sy < 0) { sy = 0; fy = 0.f; }
     if (sy >= h_l - 1) { sy = h_l - 1; fy = 0.f; }
     int sy1 = std::min(sy + 1, h_l - 1);
+    const float* row0 = flow + (size_t)sy * w_l * nop;
+    const float* row1 = flow + (size_t)sy1 * w_l * nop;
+    float* o = out + (size_t)y * w0 * nop;
     for (int x = 0; x < w0; ++x) {
-      float fx = (float)((x + padl + 0.5) * inv - 0.5);
-      int sx = (int)std::floor(fx);
-      fx -= sx;
-      if (sx < 0) { sx = 0; fx = 0.f; }
-      if (sx >= w_l - 1) { sx = w_l - 1; fx = 0.f; }
-      int sx1 = std::min(sx + 1, w_l - 1);
+      const float fx = fxv[x];
+      const int a = sx0[x] * nop, b = sx1v[x] * nop;
       for (int c = 0; c < nop; ++c) {
         // horizontal pass on rows sy, sy1, then vertical pass
-        float r0 = (flow[((size_t)sy * w_l + sx) * nop + c] * sc) * (1.f - fx) + (flow[((size_t)sy * w_l + sx1) * nop + c] * sc) * fx;
-        float r1 = (flow[((size_t)sy1 * w_l + sx) * nop + c] * sc) * (1.f - fx) + (flow[((size_t)sy1 * w_l + sx1) * nop + c] * sc) * fx;
-        out[((size_t)y * w0 + x) * nop + c] = r0 * (1.f - fy) + r1 * fy;
+        float r0 = (row0[a + c] * sc) * (1.f - fx) + (row0[b + c] * sc) * fx;
+        float r1 = (row1[a + c] * sc) * (1.f - fx) + (row1[b + c] * sc) * fx;
+        o[x * nop + c] = r0 * (1.f - fy) + r1 * fy;
       }
     }
   }
@@ -1118,6 +1128,18 @@ void orc_pyramid_level(const uint8_t* im, int w0, int h0, int C, int sc_f, int l
   std::memcpy(img, P.img[level].data(), P.img[level].size() * sizeof(float));
   std::memcpy(dx, P.dx[level].data(), P.dx[level].size() * sizeof(float));
   std::memcpy(dy, P.dy[level].data(), P.dy[level].size() * sizeof(float));
+}
+
+// All padded levels sc_l..sc_f of one frame from ONE cascade (img[l], dx[l], dy[l] caller-allocated for those levels).
+void orc_pyramid_all(const uint8_t* im, int w0, int h0, int C, int sc_f, int sc_l, int pad, float* const* img, float* const* dx,
+                     float* const* dy) {
+  Pyramid P;
+  build_pyramid(im, w0, h0, C, sc_f, sc_l, pad, P, g_pyr_gradmag);
+  for (int l = sc_l; l <= sc_f; ++l) {
+    std::memcpy(img[l], P.img[l].data(), P.img[l].size() * sizeof(float));
+    std::memcpy(dx[l], P.dx[l].data(), P.dx[l].size() * sizeof(float));
+    std::memcpy(dy[l], P.dy[l].data(), P.dy[l].size() * sizeof(float));
+  }
 }
 
 // Float-source variants of the OpenCV steps (for the cv2 golden vectors).

@@ -406,7 +406,7 @@ def test_bench_reference_arm_prints_the_contract_line():
     import json
     import subprocess
     import sys
-    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "2", "--warmup", "1"],
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "2", "--warmup", "1", "--ref-seconds", "12"],
                        capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stderr[-2000:]
     lines = [l for l in r.stdout.splitlines() if l.startswith("{")]
@@ -418,3 +418,34 @@ def test_bench_reference_arm_prints_the_contract_line():
     assert d["cpu_baseline"]["kind"] in ("reference", "port") and d["cpu_baseline"]["cores"] >= 1
     assert d["cpu_baseline"]["value"] == d["value"] == d["e2e"]["value"]
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
+    # core (the OFClass constructor) and pre/post (the OpenCV steps) separately, one thread and all cores
+    cb = d["cpu_baseline"]
+    assert cb["kind_prepost"] in ("cv2", "port") and cb["core_ms_1t"] > 0 and cb["prepost_ms_1t"] > 0
+    assert cb["core_pairs_per_s"] >= cb["core_plus_prepost_pairs_per_s"] == cb["value"]
+    # the reference arm never loads the product library
+    assert d["native_so_loaded"] and not any("libdisb200" in x for x in d["native_so_loaded"]), d["native_so_loaded"]
+
+
+@pytest.mark.parametrize("mode,noc,w0,h0", [(1, 1, 333, 217), (1, 3, 256, 150), (2, 1, 320, 200)])
+def test_cv2_prepost_of_the_cpu_baseline_is_the_oracles(port, mode, noc, w0, h0):
+    """bench.py times python-cv2 for the reference's OpenCV steps (oracle/cv2_prepost.py); what it computes must be what
+    the parity oracle computes: pyramids bit for bit on u8 frames, the final resize within 1e-5 px."""
+    from oracle import cv2_prepost as cp
+    if not cp.HAVE_CV2:
+        pytest.skip("python-cv2 not importable")
+    from of_dis_b200.synth import make_pair
+    A, _, _ = make_pair(h0, w0, channels=noc, mode="OF" if mode == 1 else "DE", seed=5)
+    sc_f, sc_l, pad = 3, 1, 8
+    PA = port.pyramid(A, sc_f, sc_l, pad)
+    Ap, padl, padt = cp.pad_frame(A, sc_f)
+    CA = cp.pyramid(Ap, sc_f, pad)
+    W, H, pl, pt = port.pad_dims(w0, h0, sc_f)
+    assert (padl, padt) == (pl, pt) and Ap.shape[:2] == (H, W)
+    for k in range(3):
+        for l in range(sc_l, sc_f + 1):
+            assert np.array_equal(PA[k][l].reshape(CA[k][l].shape), CA[k][l]), (k, l)
+    nop = 2 if mode == 1 else 1
+    low = np.random.default_rng(0).standard_normal((H >> sc_l, W >> sc_l, nop)).astype(np.float32) * 5
+    a = port.upsample_crop(low, sc_l, pl, pt, w0, h0)
+    b = cp.upsample_crop(low, sc_l, padl, padt, w0, h0)
+    assert a.shape == b.shape and np.abs(a - b).max() <= 1e-5
