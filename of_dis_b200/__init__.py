@@ -12,7 +12,8 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libdisb200.so")
+# DISB200_LIB selects another build of the same C-ABI (the tolerance build libdisb200_tol.so, see build.py)
+LIB_PATH = os.environ.get("DISB200_LIB") or os.path.join(HERE, "libdisb200.so")
 
 MODE_OF, MODE_DE = 1, 2
 SOR_LEXICOGRAPHIC, SOR_REDBLACK = 0, 1

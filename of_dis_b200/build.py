@@ -41,9 +41,17 @@ def _stale(target: str, deps) -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
+# "tolerance" variant (libdisb200_tol.so): FMA contraction and approximate division / square root allowed.  NOT the
+# parity build: reported next to it with its own EPE against the CPU reference ("what bit-exactness costs").
+TOL_LIB = os.path.join(HERE, "libdisb200_tol.so")
+TOL_FLAGS = ["-prec-div=false", "-prec-sqrt=false"]
+
+
+def build(force: bool = False, verbose: bool = False, variant: str = "parity") -> str:
     nvcc = _nvcc()
-    objdir = os.path.join(HERE, "build")
+    tol = variant == "tol"
+    LIB = TOL_LIB if tol else globals()["LIB"]
+    objdir = os.path.join(HERE, "build_tol" if tol else "build")
     os.makedirs(objdir, exist_ok=True)
     headers = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".h", ".cuh"))]
     headers.append(os.path.join(HERE, "..", "include", "disb200.h"))
@@ -53,7 +61,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         s = os.path.join(CSRC, src)
         o = os.path.join(objdir, src.replace(".cu", ".o"))
         if force or _stale(o, [s] + headers):
-            flags = [f for f in NVCC_FLAGS if not (src in FMA_OK and f == "-fmad=false")] + os.environ.get("DISB200_NVCC_EXTRA", "").split()
+            flags = [f for f in NVCC_FLAGS if not ((tol or src in FMA_OK) and f == "-fmad=false")] + (TOL_FLAGS if tol else []) + os.environ.get("DISB200_NVCC_EXTRA", "").split()
             r = subprocess.run([nvcc] + flags + ["-c", s, "-o", o], capture_output=True, text=True)
             logs[src] = r.stderr
             if r.returncode != 0:
@@ -67,6 +75,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
                            capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("link failed:\n" + r.stderr)
+    if tol:
+        return LIB
     # the four CLIs of the reference (CMakeLists.txt:35-61), thin mains over the library
     cli_src = os.path.join(CSRC, "run_dense.cpp")
     if os.path.exists(cli_src):
@@ -99,4 +109,4 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, variant="tol" if "--tol" in sys.argv else "parity"))

@@ -40,6 +40,8 @@ struct LaunchStats {
   // optional stage marks for the CUDA-event stopwatch (begin = 1 / end = 0)
   void (*mark)(void* ctx, int stage, int begin);
   void* ctx;
+  // optional: called after every fixed-point iteration of the refinement has been enqueued (sub-batch staggering)
+  void (*phase)(void* ctx) = nullptr;
 };
 
 // ---- stage 1: pyramid -------------------------------------------------------------------

@@ -137,6 +137,7 @@ struct Engine {
     if (W % (1 << p.sc_f) || H % (1 << p.sc_f)) return fail(DISB200_EINVAL, "W and H must be divisible by 2^sc_f (oflow.h:102)");
     CU(cudaSetDevice(device));
     CU(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&stagger_ev, cudaEventDisableTiming));
     geom.resize(p.sc_f + 1);
     for (int f = 0; f < 2; ++f)
       for (int a = 0; a < 3; ++a) pyr[f][a].assign(p.sc_f + 1, nullptr);
@@ -211,6 +212,8 @@ struct Engine {
     for (cudaEvent_t e : ev_pool) cudaEventDestroy(e);
     ev_pool.clear();
     if (stream) cudaStreamDestroy(stream);
+    if (stagger_ev) cudaEventDestroy(stagger_ev);
+    stagger_ev = nullptr;
     stream = nullptr;
   }
 
@@ -252,6 +255,9 @@ struct Engine {
     else e->marks.push_back({stage, e->open_mark[stage], ev});
   }
   void begin_run() {
+    phase_ctr = 0;
+    stagger_done = false;
+    stats.phase = &Engine::phase_cb;
     stats.launches = 0;
     stats.mark = stage_timing ? &Engine::mark_cb : nullptr;
     stats.ctx = this;
@@ -267,6 +273,18 @@ struct Engine {
       cudaEventElapsedTime(&ms, m.a, m.b);
       stage_ms[m.stage] += ms;
     }
+  }
+
+  // Staggered sub-batches: the engine records `stagger_ev` when its pipeline passes phase number `stagger_point`
+  // (1 = pyramids done, then one per level: search, densify, each fixed-point iteration); the next sub-batch's
+  // stream waits for it before it starts, so that the sub-batches run DIFFERENT kernels side by side (the one-warp
+  // SOR of one next to the system assembly / inverse search of another) instead of marching in lock-step.
+  cudaEvent_t stagger_ev = nullptr;
+  int stagger_point = 0, phase_ctr = 0;
+  bool stagger_done = false;
+  static void phase_cb(void* ctx) { static_cast<Engine*>(ctx)->phase(); }
+  void phase() {
+    if (++phase_ctr == stagger_point && stagger_ev && !stagger_done) { cudaEventRecord(stagger_ev, stream); stagger_done = true; }
   }
 
   // Sequence mode (video): pair i = frames (i, i+1); the n + 1 frame pyramids live in the role-A arrays and the
@@ -293,6 +311,7 @@ struct Engine {
       for (int f = 0; f < 2; ++f) { lv[nlev].img[f] = pyr[f][0][l]; lv[nlev].dx[f] = pyr[f][1][l]; lv[nlev].dy[f] = pyr[f][2][l]; }
     }
     launch_sobel_pad_levels(lv, gl, nlev, nA, nB, C, stream, &stats);
+    phase();
   }
 
   // The scale loop, oflow.cpp:182-330.  Result: flow[0][sc_l].
@@ -320,6 +339,7 @@ struct Engine {
             return fail(DISB200_EUNSUPPORTED, "no inverse-search kernel for this patch size / channel count");
         }
       }
+      phase();
       {
         StageScope sc(this, 2);
         for (int d = 0; d < ndir; ++d) {                               // oflow.cpp:259-267
@@ -334,6 +354,7 @@ struct Engine {
           launch_densify(a, g, o, n, stream, &stats);
         }
       }
+      phase();
       if (p.usetvref) {                                                // oflow.cpp:281-290
         StageScope sc(this, 3);
         launch_varref_level(P(0, 0, sl), P(1, 0, sl), flow[0][sl], g, p, 0, vb, n, stream, &stats);
@@ -358,6 +379,7 @@ struct DisHandle {
   Engine e;                       // sub-batch engine 0; owns the handle's main stream
   std::vector<Engine*> extra;     // sub-batch engines 1.. (own stream each), created on demand
   int nsub = 1;                   // sub-batches run concurrently on separate streams
+  int stagger = 0;                // phase of sub-batch i - 1 that sub-batch i waits for before it starts (0: none)
   int cap = 0;                    // pairs per sub-batch engine
   int max_batch = 0;              // pairs per call
   int last_per = 0;               // sub-batch size of the most recent run (for disb200_fetch)
@@ -446,10 +468,15 @@ struct DisHandle {
       if (i > 0 && !serial) {
         E.begin_run();
         CU(cudaStreamWaitEvent(E.stream, ev_fork, 0));
+        if (stagger > 0) CU(cudaStreamWaitEvent(E.stream, sub(i - 1).stagger_ev, 0));
       }
       E.stats.launches = 0;
+      E.phase_ctr = 0;
+      E.stagger_done = false;
+      E.stagger_point = (stagger > 0 && !serial && i + 1 < S) ? stagger : 0;
       int rc = enqueue_one(E, a + (size_t)lo * in_bytes, b ? b + (size_t)lo * in_bytes : nullptr, m, out + (size_t)lo * out_elems);
       if (rc) return rc;
+      if (E.stagger_point && !E.stagger_done) { CU(cudaEventRecord(E.stagger_ev, E.stream)); E.stagger_done = true; }
       launches += E.stats.launches;     // kernels of this enqueue() call (all sub-batches)
       if (i > 0 && !serial) {
         CU(cudaEventRecord(ev_join[i - 1], E.stream));
@@ -543,6 +570,7 @@ int disb200_create(const DisParams* params, int w0, int h0, int max_batch, int d
     h->nsub = std::max(1, std::min(std::min(want, 16), max_batch));
   }
   h->cap = (max_batch + h->nsub - 1) / h->nsub;
+  { const char* ev = getenv("DISB200_STAGGER"); h->stagger = ev ? std::max(0, atoi(ev)) : 0; }
   if (!rc) rc = h->e.init(*params, W, H, h->cap, device);
   if (!rc) {
     h->w0 = w0; h->h0 = h0;
