@@ -149,6 +149,15 @@ int disb200_ofclass(const DisParams* params, const float* const* im_ao, const fl
 int disb200_varref_level(const DisParams* params, const float* im_a, const float* im_b, int w_l, int h_l,
                          int level, int camlr, float* flow);
 
+/* PatGridClass::AggregateFlowDense-level entry (patchgrid.cpp:213-397, called at oflow.cpp:259-267): densify the patch
+ * results of one w_l x h_l level.  p_iter [npatch][nop], pweight [npatch][novals] of the grid itself; cg_* = p_iter,
+ * pt_iter [npatch][2] (end positions) and pweight of the complementary grid for forward-backward merging, or all NULL.
+ * flow: h_l*w_l*nop f32 out.  npatch as PatGridClass computes it (patchgrid.cpp:43-46); returned through *npatch_out
+ * when not NULL so that callers can size the arrays (call with all data pointers NULL to query). */
+int disb200_aggregate_dense(const DisParams* params, int w_l, int h_l, const float* p_iter, const float* pweight,
+                            const float* cg_p_iter, const float* cg_pt_iter, const float* cg_pweight, float* flow,
+                            int* npatch_out);
+
 /* File writers with the reference's framing (run_dense.cpp:17-82). */
 int disb200_save_flo(const char* path, const float* flow, int w, int h, int nc);
 int disb200_save_pfm(const char* path, const float* disp, int w, int h);

@@ -271,6 +271,21 @@ def ofclass(params: DisParams, A, B, W: int, H: int, initflow=None) -> np.ndarra
     return out
 
 
+def aggregate_dense(params: DisParams, w_l: int, h_l: int, p_iter, pweight, cg=None) -> np.ndarray:
+    """AggregateFlowDense cut (patchgrid.cpp:213-397); cg = (p_iter, pt_iter, pweight) of the complementary grid."""
+    out = np.empty((h_l, w_l, params.nop), np.float32)
+    arrs = [np.ascontiguousarray(x, np.float32) for x in (p_iter, pweight) + (tuple(cg) if cg else ())]
+    ptrs = [_ptr(x) for x in arrs] + ([None] * 3 if not cg else [])
+    _check(lib().disb200_aggregate_dense(C.byref(params), w_l, h_l, *ptrs, _ptr(out), None))
+    return out
+
+
+def patch_count(params: DisParams, w_l: int, h_l: int) -> int:
+    n = C.c_int()
+    _check(lib().disb200_aggregate_dense(C.byref(params), w_l, h_l, None, None, None, None, None, None, C.byref(n)))
+    return n.value
+
+
 def varref_level(params: DisParams, im_a, im_b, w_l: int, h_l: int, level: int, camlr: int, flow) -> np.ndarray:
     flow = np.ascontiguousarray(flow, np.float32).copy()
     _check(lib().disb200_varref_level(C.byref(params), _ptr(im_a), _ptr(im_b), w_l, h_l, level, camlr, _ptr(flow)))

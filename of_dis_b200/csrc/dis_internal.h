@@ -40,8 +40,6 @@ struct LaunchStats {
   // optional stage marks for the CUDA-event stopwatch (begin = 1 / end = 0)
   void (*mark)(void* ctx, int stage, int begin);
   void* ctx;
-  // optional: called after every fixed-point iteration of the refinement has been enqueued (sub-batch staggering)
-  void (*phase)(void* ctx) = nullptr;
 };
 
 // ---- stage 1: pyramid -------------------------------------------------------------------
@@ -92,11 +90,11 @@ struct DensifyArgs {
   const float* cg_pt_iter;
   const float* cg_pweight;
   float* flow;             // [n][h][w][nop]
-  // scratch for the backward merge (cell lists), may be null when cg is null
+  // scratch for the backward merge (CSR cell lists), may be null when cg is null
   int* cell_count;         // [n][ncell]
-  int* cell_list;          // [n][ncell][cell_cap]
-  int cell_cap;
-  int* overflow;         // single int, set to the largest cell population that exceeded cell_cap
+  int* cell_start;         // [n][ncell]  exclusive scan of cell_count
+  int* cell_end;           // [n][ncell]  fill cursor, = start + count once filled
+  int* cell_list;          // [n][npatch] patch indices grouped by cell, ascending inside a cell
 };
 void launch_densify(const DensifyArgs& a, const LevelGeom& g, const OptConst& o, int n, cudaStream_t s,
                     LaunchStats* st);

@@ -78,8 +78,7 @@ static int validate(const DisParams& p) {
   if (p.gradmag && p.channels != 1) return fail(DISB200_EINVAL, "gradmag (SELECTCHANNEL 2) is a single-band mode: channels must be 1");
   if (p.sc_l < 0 || p.sc_f < p.sc_l || p.sc_f > 8) return fail(DISB200_EINVAL, "need 0 <= sc_l <= sc_f <= 8");
   if (p.patove < 0.f || p.patove >= 1.f) return fail(DISB200_EINVAL, "patove must be in [0,1)");
-  if (p.patchsz != 4 && p.patchsz != 8 && p.patchsz != 12 && p.patchsz != 16)
-    return fail(DISB200_EUNSUPPORTED, "patch size must be one of 4, 8, 12, 16");
+  if (p.patchsz < 2 || p.patchsz > 16) return fail(DISB200_EUNSUPPORTED, "patch size must be in 2..16");
   if (p.costfct != 0 && p.costfct != 1 && p.costfct != 2 && p.costfct != 10)
     return fail(DISB200_EUNSUPPORTED, "costfct must be 0 (L2), 1 (L1), 2 (pseudo-Huber) or 10 (NCC)");
   if (p.max_iter < 0 || p.min_iter < 0) return fail(DISB200_EINVAL, "iteration counts must be >= 0");
@@ -103,10 +102,10 @@ struct Engine {
   bool has_initflow = false;
   float* vpool = nullptr;
   VarRefBuffers vb;
-  int* cell_count = nullptr;
+  int* cell_count = nullptr;      // fwd/bwd merge: CSR binning of the complementary grid's end positions
+  int* cell_start = nullptr;
+  int* cell_end = nullptr;
   int* cell_list = nullptr;
-  int cell_cap = 0;
-  int* overflow = nullptr;
   unsigned* sorb_ctl = nullptr;     // banded SOR: device {ticket counter, error flag}
   unsigned sorb_host[2] = {0, 0};   //             host {launch epoch, tickets issued}
   size_t ncell_max = 0;
@@ -137,7 +136,6 @@ struct Engine {
     if (W % (1 << p.sc_f) || H % (1 << p.sc_f)) return fail(DISB200_EINVAL, "W and H must be divisible by 2^sc_f (oflow.h:102)");
     CU(cudaSetDevice(device));
     CU(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
-    CU(cudaEventCreateWithFlags(&stagger_ev, cudaEventDisableTiming));
     geom.resize(p.sc_f + 1);
     for (int f = 0; f < 2; ++f)
       for (int a = 0; a < 3; ++a) pyr[f][a].assign(p.sc_f + 1, nullptr);
@@ -168,12 +166,10 @@ struct Engine {
       if (rc) return rc;
     }
     if (p.usefbcon) {
-      const int per_axis = (o.psz + o.steps - 1) / o.steps + 1;
-      cell_cap = std::max(16, 4 * per_axis * per_axis);
       int rc = dalloc(&cell_count, ncell_max * max_batch);
-      if (!rc) rc = dalloc(&overflow, 1);
-      if (!rc) CU(cudaMemset(overflow, 0, sizeof(int)));
-      if (!rc) rc = dalloc(&cell_list, ncell_max * cell_cap * max_batch);
+      if (!rc) rc = dalloc(&cell_start, ncell_max * max_batch);
+      if (!rc) rc = dalloc(&cell_end, ncell_max * max_batch);
+      if (!rc) rc = dalloc(&cell_list, max_patch * max_batch);
       if (rc) return rc;
     }
     {
@@ -212,8 +208,6 @@ struct Engine {
     for (cudaEvent_t e : ev_pool) cudaEventDestroy(e);
     ev_pool.clear();
     if (stream) cudaStreamDestroy(stream);
-    if (stagger_ev) cudaEventDestroy(stagger_ev);
-    stagger_ev = nullptr;
     stream = nullptr;
   }
 
@@ -255,9 +249,6 @@ struct Engine {
     else e->marks.push_back({stage, e->open_mark[stage], ev});
   }
   void begin_run() {
-    phase_ctr = 0;
-    stagger_done = false;
-    stats.phase = &Engine::phase_cb;
     stats.launches = 0;
     stats.mark = stage_timing ? &Engine::mark_cb : nullptr;
     stats.ctx = this;
@@ -273,18 +264,6 @@ struct Engine {
       cudaEventElapsedTime(&ms, m.a, m.b);
       stage_ms[m.stage] += ms;
     }
-  }
-
-  // Staggered sub-batches: the engine records `stagger_ev` when its pipeline passes phase number `stagger_point`
-  // (1 = pyramids done, then one per level: search, densify, each fixed-point iteration); the next sub-batch's
-  // stream waits for it before it starts, so that the sub-batches run DIFFERENT kernels side by side (the one-warp
-  // SOR of one next to the system assembly / inverse search of another) instead of marching in lock-step.
-  cudaEvent_t stagger_ev = nullptr;
-  int stagger_point = 0, phase_ctr = 0;
-  bool stagger_done = false;
-  static void phase_cb(void* ctx) { static_cast<Engine*>(ctx)->phase(); }
-  void phase() {
-    if (++phase_ctr == stagger_point && stagger_ev && !stagger_done) { cudaEventRecord(stagger_ev, stream); stagger_done = true; }
   }
 
   // Sequence mode (video): pair i = frames (i, i+1); the n + 1 frame pyramids live in the role-A arrays and the
@@ -311,7 +290,6 @@ struct Engine {
       for (int f = 0; f < 2; ++f) { lv[nlev].img[f] = pyr[f][0][l]; lv[nlev].dx[f] = pyr[f][1][l]; lv[nlev].dy[f] = pyr[f][2][l]; }
     }
     launch_sobel_pad_levels(lv, gl, nlev, nA, nB, C, stream, &stats);
-    phase();
   }
 
   // The scale loop, oflow.cpp:182-330.  Result: flow[0][sc_l].
@@ -339,7 +317,6 @@ struct Engine {
             return fail(DISB200_EUNSUPPORTED, "no inverse-search kernel for this patch size / channel count");
         }
       }
-      phase();
       {
         StageScope sc(this, 2);
         for (int d = 0; d < ndir; ++d) {                               // oflow.cpp:259-267
@@ -350,11 +327,10 @@ struct Engine {
           a.cg_pt_iter = p.usefbcon ? pt_iter[1 - d] : nullptr;
           a.cg_pweight = p.usefbcon ? pweight[1 - d] : nullptr;
           a.flow = flow[d][sl];
-          a.cell_count = cell_count; a.cell_list = cell_list; a.cell_cap = cell_cap; a.overflow = overflow;
+          a.cell_count = cell_count; a.cell_start = cell_start; a.cell_end = cell_end; a.cell_list = cell_list;
           launch_densify(a, g, o, n, stream, &stats);
         }
       }
-      phase();
       if (p.usetvref) {                                                // oflow.cpp:281-290
         StageScope sc(this, 3);
         launch_varref_level(P(0, 0, sl), P(1, 0, sl), flow[0][sl], g, p, 0, vb, n, stream, &stats);
@@ -379,7 +355,6 @@ struct DisHandle {
   Engine e;                       // sub-batch engine 0; owns the handle's main stream
   std::vector<Engine*> extra;     // sub-batch engines 1.. (own stream each), created on demand
   int nsub = 1;                   // sub-batches run concurrently on separate streams
-  int stagger = 0;                // phase of sub-batch i - 1 that sub-batch i waits for before it starts (0: none)
   int cap = 0;                    // pairs per sub-batch engine
   int max_batch = 0;              // pairs per call
   int last_per = 0;               // sub-batch size of the most recent run (for disb200_fetch)
@@ -468,15 +443,10 @@ struct DisHandle {
       if (i > 0 && !serial) {
         E.begin_run();
         CU(cudaStreamWaitEvent(E.stream, ev_fork, 0));
-        if (stagger > 0) CU(cudaStreamWaitEvent(E.stream, sub(i - 1).stagger_ev, 0));
       }
       E.stats.launches = 0;
-      E.phase_ctr = 0;
-      E.stagger_done = false;
-      E.stagger_point = (stagger > 0 && !serial && i + 1 < S) ? stagger : 0;
       int rc = enqueue_one(E, a + (size_t)lo * in_bytes, b ? b + (size_t)lo * in_bytes : nullptr, m, out + (size_t)lo * out_elems);
       if (rc) return rc;
-      if (E.stagger_point && !E.stagger_done) { CU(cudaEventRecord(E.stagger_ev, E.stream)); E.stagger_done = true; }
       launches += E.stats.launches;     // kernels of this enqueue() call (all sub-batches)
       if (i > 0 && !serial) {
         CU(cudaEventRecord(ev_join[i - 1], E.stream));
@@ -492,14 +462,6 @@ struct DisHandle {
   int check_overflow() {
     for (int i = 0; i <= (int)extra.size(); ++i) {
       Engine& E = sub(i);
-      if (E.overflow) {
-        int v = 0;
-        CU(cudaMemcpy(&v, E.overflow, sizeof(int), cudaMemcpyDeviceToHost));
-        if (v > 0) {
-          cudaMemset(E.overflow, 0, sizeof(int));
-          return fail(DISB200_EUNSUPPORTED, "forward-backward merge: " + std::to_string(v) + " patches ended in one cell, capacity " + std::to_string(E.cell_cap));
-        }
-      }
       int rc = E.check_sorb();
       if (rc) return rc;
     }
@@ -570,7 +532,6 @@ int disb200_create(const DisParams* params, int w0, int h0, int max_batch, int d
     h->nsub = std::max(1, std::min(std::min(want, 16), max_batch));
   }
   h->cap = (max_batch + h->nsub - 1) / h->nsub;
-  { const char* ev = getenv("DISB200_STAGGER"); h->stagger = ev ? std::max(0, atoi(ev)) : 0; }
   if (!rc) rc = h->e.init(*params, W, H, h->cap, device);
   if (!rc) {
     h->w0 = w0; h->h0 = h0;
@@ -862,12 +823,53 @@ int disb200_ofclass(const DisParams* params, const float* const* im_ao, const fl
     if (ce == cudaSuccess) ce = cudaStreamSynchronize(e.stream);
     if (ce != cudaSuccess) rc = fail(DISB200_ECUDA, std::string("ofclass: ") + cudaGetErrorString(ce));
   }
-  if (!rc && e.overflow) {
-    int v = 0;
-    cudaMemcpy(&v, e.overflow, sizeof(int), cudaMemcpyDeviceToHost);
-    if (v > 0) rc = fail(DISB200_EUNSUPPORTED, "forward-backward merge cell overflow");
-  }
   if (!rc) rc = e.check_sorb();
+  e.destroy();
+  return rc;
+}
+
+int disb200_aggregate_dense(const DisParams* params, int w_l, int h_l, const float* p_iter_h, const float* pweight_h,
+                            const float* cg_p_iter, const float* cg_pt_iter, const float* cg_pweight, float* flow,
+                            int* npatch_out) {
+  if (!params) return fail(DISB200_EINVAL, "null argument");
+  int rc = validate(*params);
+  if (rc) return rc;
+  if (w_l < 1 || h_l < 1) return fail(DISB200_EINVAL, "bad level size");
+  DisParams q = *params;
+  q.sc_f = q.sc_l = 0;
+  q.usetvref = 0;
+  const bool fb = cg_p_iter || cg_pt_iter || cg_pweight;
+  q.usefbcon = fb ? 1 : 0;
+  const LevelGeom g0 = make_levelgeom(q, w_l, h_l, 0);
+  if (npatch_out) *npatch_out = g0.npatch;
+  if (!p_iter_h && !pweight_h && !flow && !fb) return DISB200_OK;   // size query
+  if (!p_iter_h || !pweight_h || !flow || (fb && !(cg_p_iter && cg_pt_iter && cg_pweight)))
+    return fail(DISB200_EINVAL, "null argument");
+  if (disb200_device_count() < 1) return fail(DISB200_ECUDA, "no CUDA device (this library has no CPU path)");
+  Engine e;
+  rc = e.init(q, w_l, h_l, 1, 0);
+  if (!rc) {
+    const LevelGeom& g = e.geom[0];
+    const size_t np = g.npatch, nv = e.o.novals;
+    cudaError_t ce = cudaMemcpyAsync(e.p_iter[0], p_iter_h, np * e.nop * sizeof(float), cudaMemcpyHostToDevice, e.stream);
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(e.pweight[0], pweight_h, np * nv * sizeof(float), cudaMemcpyHostToDevice, e.stream);
+    if (fb && ce == cudaSuccess) ce = cudaMemcpyAsync(e.p_iter[1], cg_p_iter, np * e.nop * sizeof(float), cudaMemcpyHostToDevice, e.stream);
+    if (fb && ce == cudaSuccess) ce = cudaMemcpyAsync(e.pt_iter[1], cg_pt_iter, np * 2 * sizeof(float), cudaMemcpyHostToDevice, e.stream);
+    if (fb && ce == cudaSuccess) ce = cudaMemcpyAsync(e.pweight[1], cg_pweight, np * nv * sizeof(float), cudaMemcpyHostToDevice, e.stream);
+    if (ce == cudaSuccess) {
+      e.begin_run();
+      DensifyArgs a;
+      a.p_iter = e.p_iter[0]; a.pweight = e.pweight[0];
+      a.cg_p_iter = fb ? e.p_iter[1] : nullptr; a.cg_pt_iter = fb ? e.pt_iter[1] : nullptr; a.cg_pweight = fb ? e.pweight[1] : nullptr;
+      a.flow = e.flow[0][0];
+      a.cell_count = e.cell_count; a.cell_start = e.cell_start; a.cell_end = e.cell_end; a.cell_list = e.cell_list;
+      launch_densify(a, g, e.o, 1, e.stream, &e.stats);
+      ce = cudaGetLastError();
+    }
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(flow, e.flow[0][0], (size_t)w_l * h_l * e.nop * sizeof(float), cudaMemcpyDeviceToHost, e.stream);
+    if (ce == cudaSuccess) ce = cudaStreamSynchronize(e.stream);
+    if (ce != cudaSuccess) rc = fail(DISB200_ECUDA, std::string("aggregate_dense: ") + cudaGetErrorString(ce));
+  }
   e.destroy();
   return rc;
 }

@@ -377,6 +377,242 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Any patch size (run-time psz, 2..16) and channel count: one warp per patch, value n of the patch vector in lane
+// n % 32, slot n / 32.  This is the reference's arithmetic INCLUDING what it does for odd patch sizes
+// (patch.cpp:316-317,377-378: lb = -psz/2, ub = psz/2 - 1 sample PS = 2 (psz/2) rows and columns, while every vector
+// has novals = psz^2 C entries, oflow.cpp:91):
+//   * entries n >= NE = PS^2 C are never sampled: template and gradients stay 0 there (zero-initialised vectors,
+//     SURVEY.md 8c) and the query vector keeps what the PREVIOUS evaluation left in them;
+//   * the mean subtraction (patch.cpp:342,412) shifts all novals entries and divides by novals;
+//   * LossComputeErrorImage (patch.cpp:226-272) touches the first 4 (novals / 4) entries only: the last novals % 4
+//     entries of pdiff stay "query minus mean" and their weights stay 0.
+// Used for every (psz, channels) without a specialised instantiation; compared with a tolerance like the other
+// kernels whose reduction order differs from Eigen's packets.
+template <bool OF, int VPL>
+__global__ void __launch_bounds__(128)
+patch_search_generic_kernel(PatchArgs a, LevelGeom g, OptConst o) {
+  constexpr int NOP = OF ? 2 : 1, G = 32;
+  const int C = o.noc, psz = o.psz, NV = o.novals;
+  const int lbi = -(psz / 2), PS = 2 * (psz / 2), rowlen = PS * C, NE = PS * rowlen, NB4 = (NV / 4) * 4;
+  const int lane = threadIdx.x % G;
+  const int ip_raw = blockIdx.x * (blockDim.x / G) + threadIdx.x / G;
+  const bool active = ip_raw < g.npatch;
+  const int ip = active ? ip_raw : g.npatch - 1;
+  const int pair = blockIdx.y;
+  const int rowstride = g.tw * C;
+  const float fnv = (float)NV;
+
+  const float* timg = a.tmpl_img + (size_t)pair * g.img_elems;
+  const float* tdxp = a.tmpl_dx + (size_t)pair * g.img_elems;
+  const float* tdyp = a.tmpl_dy + (size_t)pair * g.img_elems;
+  const float* qimg = a.tgt_img + (size_t)pair * g.img_elems;
+  const int gx = ip / g.noph, gy = ip - gx * g.noph;
+  const float ptrx = (float)(gx * g.steps + g.offw), ptry = (float)(gy * g.steps + g.offh);
+
+  int off[VPL];
+  bool smp[VPL], val[VPL];   // sampled (n < NE), exists (n < NV)
+#pragma unroll
+  for (int k = 0; k < VPL; ++k) {
+    const int n = k * G + lane;
+    val[k] = n < NV;
+    smp[k] = n < NE;
+    const int nn = smp[k] ? n : 0, row = nn / rowlen;
+    off[k] = row * rowstride + (nn - row * rowlen);
+  }
+  float t[VPL], dx[VPL], dy[VPL], pd[VPL];
+  {
+    const int base = (((int)ptry + g.pad + lbi) * g.tw + ((int)ptrx + g.pad + lbi)) * C;
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) {
+      t[k] = smp[k] ? __ldg(timg + base + off[k]) : 0.f;
+      dx[k] = smp[k] ? __ldg(tdxp + base + off[k]) : 0.f;
+      dy[k] = (OF && smp[k]) ? __ldg(tdyp + base + off[k]) : 0.f;
+      pd[k] = 0.f;
+      s += t[k];
+    }
+    if (o.patnorm > 0 || o.costfct == 10) {
+      const float m = gsum<G>(s) / fnv;
+#pragma unroll
+      for (int k = 0; k < VPL; ++k) t[k] = val[k] ? t[k] - m : 0.f;
+    }
+  }
+  float tnorm = 0.f;
+  if (o.costfct == 10) {
+    float s2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) s2 += t[k] * t[k];
+    tnorm = sqrtf(gsum<G>(s2));
+  }
+  float H00 = 0.f, H01 = 0.f, H11 = 0.f;
+#pragma unroll
+  for (int k = 0; k < VPL; ++k) {
+    H00 += dx[k] * dx[k];
+    if (OF) { H01 += dx[k] * dy[k]; H11 += dy[k] * dy[k]; }
+  }
+  H00 = gsum<G>(H00);
+  if (OF) { H01 = gsum<G>(H01); H11 = gsum<G>(H11); }
+  float l00, l10 = 0.f, l11 = 1.f;
+  if (OF) {
+    if (H00 * H11 - H01 * H01 == 0.f) { H00 = (float)((double)H00 + 1e-10); H11 = (float)((double)H11 + 1e-10); }
+    l00 = H00; l10 = H01; l11 = H11;
+    if (l00 > 0.f) {
+      l00 = sqrtf(l00);
+      l10 = l10 / l00;
+      const float x = l11 - l10 * l10;
+      if (x > 0.f) l11 = sqrtf(x);
+    }
+  } else {
+    if (H00 == 0.f) H00 = (float)((double)H00 + 1e-10);
+    l00 = H00;
+    if (l00 > 0.f) l00 = sqrtf(l00);
+  }
+
+  float p_in0 = 0.f, p_in1 = 0.f;
+  if (a.flow_prev) {
+    const int x = (int)floorf(ptrx / 2), y = (int)floorf(ptry / 2);
+    const float* fp = a.flow_prev + (size_t)pair * a.flow_prev_stride + (size_t)(y * (g.w / 2) + x) * NOP;
+    p_in0 = fp[0] * 2;
+    if (OF) p_in1 = fp[1] * 2;
+  }
+  float p0 = p_in0, p1 = p_in1;
+  float ptx = ptrx + p0, pty = OF ? ptry + p1 : ptry;
+  const float stx = ptx, sty = pty;
+  float dp0 = 0.f, dp1 = 0.f, dpsq_init = 1e-10f, mares = 1e5f;
+  int cnt = 0;
+  const bool start_ok = !(ptx < g.lb || pty < g.lb || ptx > g.ubw || pty > g.ubh);
+  bool conv = !start_ok;
+  float s0 = 0.f, s1 = 0.f;
+  const size_t pi = (size_t)pair * g.npatch + ip;
+  float* wout = a.pweight + pi * NV;
+  if (active && !start_ok) {
+#pragma unroll
+    for (int k = 0; k < VPL; ++k)
+      if (val[k]) wout[k * G + lane] = 0.f;
+  }
+  const float bsq = o.normoutlier * o.normoutlier, bsq2 = bsq * 2.0f;
+
+  bool first = true;
+  while (true) {
+    const bool upd = first ? start_ok : !conv;
+    float np0 = p0, np1 = p1, nptx = ptx, npty = pty, ndp0 = dp0, ndp1 = dp1;
+    bool nconv = conv;
+    int ncnt = cnt;
+    if (!first) {
+      ncnt = cnt + 1;
+      if (OF) {
+        const float y0 = s0 / l00;
+        const float y1 = (s1 - l10 * y0) / l11;
+        const float x1 = y1 / l11;
+        const float x0 = (y0 - l10 * x1) / l00;
+        ndp0 = x0; ndp1 = x1;
+        np0 = p0 - ndp0; np1 = p1 - ndp1;
+      } else {
+        ndp0 = (s0 / l00) / l00;
+        np0 = p0 - ndp0;
+        np0 = (a.camlr == 0) ? fminf(np0, 0.f) : fmaxf(np0, 0.f);
+      }
+      nptx = ptrx + np0;
+      if (OF) npty = ptry + np1;
+      const float ddx = stx - nptx, ddy = sty - npty;
+      if (sqrtf(ddx * ddx + ddy * ddy) > o.outlierthresh || nptx < g.lb || npty < g.lb || nptx > g.ubw || npty > g.ubh) {
+        np0 = p_in0; np1 = p_in1;
+        nptx = ptrx + np0;
+        if (OF) npty = ptry + np1;
+        nconv = true;
+      }
+    }
+    const float ex = upd ? nptx : ptrx, ey = upd ? npty : ptry;
+    const int ix1 = (int)ceilf(ex + .00001f), iy1 = (int)ceilf(ey + .00001f);
+    const float rx = ex - floorf(ex), ry = ey - floorf(ey);
+    const float w0 = rx * ry, w1 = (1.f - rx) * ry, w2 = rx * (1.f - ry), w3 = (1.f - rx) * (1.f - ry);
+    const float* qb = qimg + ((iy1 + g.pad + lbi) * g.tw + (ix1 + g.pad + lbi)) * C;
+    float q[VPL];
+    float qs = 0.f;
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) {
+      const float* p = qb + off[k];
+      if (smp[k]) {
+        const float va = __ldg(p), vb = __ldg(p - C), vc = __ldg(p - rowstride), vd = __ldg(p - rowstride - C);
+        q[k] = w0 * va + w1 * vb + w2 * vc + w3 * vd;
+      } else {
+        q[k] = pd[k];          // never sampled: what the previous evaluation left there (0 before the first, and 0 beyond novals)
+      }
+      qs += q[k];
+    }
+    if (o.patnorm > 0 || o.costfct == 10) {
+      const float m = gsum<G>(qs) / fnv;
+#pragma unroll
+      for (int k = 0; k < VPL; ++k) q[k] = val[k] ? q[k] - m : 0.f;
+    }
+    float qscale = 1.0f;
+    if (o.costfct == 10) {
+      float s2 = 0.f;
+#pragma unroll
+      for (int k = 0; k < VPL; ++k) s2 += q[k] * q[k];
+      const float qn = sqrtf(gsum<G>(s2));
+      qscale = qn > 0.f ? tnorm / qn : 0.f;
+    }
+    float npd[VPL], npw[VPL];
+    float as0 = 0.f, as1 = 0.f, aws = 0.f;
+#pragma unroll
+    for (int k = 0; k < VPL; ++k) {
+      const int n = k * G + lane;
+      float vpd = q[k], vpw = 0.f;            // tail beyond 4 (novals / 4): pdiff keeps the shifted query, the weight is never written
+      if (n < NB4) {
+        const float d = (o.costfct == 10 ? q[k] * qscale : q[k]) - t[k];
+        if (o.costfct == 0 || o.costfct == 10) loss<0>(d, bsq, bsq2, vpd, vpw);
+        else if (o.costfct == 1) loss<1>(d, bsq, bsq2, vpd, vpw);
+        else loss<2>(d, bsq, bsq2, vpd, vpw);
+      }
+      if (!val[k]) { vpd = 0.f; vpw = 0.f; }
+      npd[k] = vpd; npw[k] = vpw;
+      as0 += dx[k] * vpd;
+      if (OF) as1 += dy[k] * vpd;
+      aws += fabsf(vpw);
+    }
+    const float ns0 = gsum<G>(as0);
+    const float ns1 = OF ? gsum<G>(as1) : 0.f;
+    const float wsum = gsum<G>(aws);
+    if (upd) {
+      const float dpsq = OF ? ndp0 * ndp0 + ndp1 * ndp1 : ndp0 * ndp0;
+      if (ncnt == 1) dpsq_init = dpsq;
+      const float mares_old = mares;
+      const float nmares = wsum / fnv;
+      bool go_on = (ncnt < o.max_iter) & (nmares > o.res_thresh);
+      if (go_on && ncnt >= o.min_iter)
+        go_on = (dpsq / dpsq_init >= o.dp_thresh_sq) & (nmares / mares_old <= o.dr_thresh);
+      if (!go_on) nconv = true;
+      mares = nmares;
+      p0 = np0; p1 = np1; ptx = nptx; pty = npty; dp0 = ndp0; dp1 = ndp1; cnt = ncnt; conv = nconv;
+      s0 = ns0; s1 = ns1;
+#pragma unroll
+      for (int k = 0; k < VPL; ++k) pd[k] = npd[k];
+      if (nconv && active) {
+#pragma unroll
+        for (int k = 0; k < VPL; ++k)
+          if (val[k]) wout[k * G + lane] = npw[k];
+      }
+    }
+    first = false;
+    if (!__any_sync(0xffffffffu, !conv)) break;
+  }
+  if (active && lane == 0) {
+    a.p_iter[pi * NOP] = p0;
+    if (OF) a.p_iter[pi * NOP + 1] = p1;
+    if (a.pt_iter) { a.pt_iter[pi * 2] = ptx; a.pt_iter[pi * 2 + 1] = pty; }
+  }
+}
+
+template <int VPL>
+static void launch_generic(const PatchArgs& a, const LevelGeom& g, const OptConst& o, int n, cudaStream_t s) {
+  const int threads = 128, per_block = threads / 32;
+  dim3 grd((g.npatch + per_block - 1) / per_block, n);
+  if (o.mode == DISB200_MODE_OF) patch_search_generic_kernel<true, VPL><<<grd, threads, 0, s>>>(a, g, o);
+  else patch_search_generic_kernel<false, VPL><<<grd, threads, 0, s>>>(a, g, o);
+}
+
 template <int PSZ, int C, int G, int LPR = 0, bool FM = false>
 static void launch_one(const PatchArgs& a, const LevelGeom& g, const OptConst& o, int n, cudaStream_t s) {
   const int threads = 128, per_block = threads / G;
@@ -413,7 +649,15 @@ bool launch_patch_search(const PatchArgs& a, const LevelGeom& g, const OptConst&
       else launch_one<12, 3, 32>(a, g, o, n, s);
       break;
     case 163: launch_one<16, 3, 32>(a, g, o, n, s); break;
-    default: return false;
+    default: {
+      // every other patch size the reference accepts (oflow.cpp:90-91 take any p_samp_s): the run-time-size kernel
+      if (o.psz < 2 || o.psz > 16 || (o.noc != 1 && o.noc != 3)) return false;
+      const int slots = (o.novals + 31) / 32;
+      if (slots <= 4) launch_generic<4>(a, g, o, n, s);
+      else if (slots <= 8) launch_generic<8>(a, g, o, n, s);
+      else if (slots <= 16) launch_generic<16>(a, g, o, n, s);
+      else launch_generic<24>(a, g, o, n, s);
+    }
   }
   st->launches++;
   return true;

@@ -861,7 +861,6 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
     else sor_wavefront_kernel<OF><<<n, threads, 0, st>>>(vb.du, cA, cB, d, p.tv_solverit, p.tv_sor, pipelined ? 1 : 0);
     if (ls->mark) ls->mark(ls->ctx, 5, 0);
     ls->launches += 3;
-    if (ls->phase) ls->phase(ls->ctx);
   }
   finish_kernel<OF><<<grd, blk, 0, st>>>(flow, vb.du, d, camlr);
   ls->launches++;

@@ -167,6 +167,15 @@ class Port:
     def patchgrid_level(self, p: OrcParams, A, B, w_l, h_l, level, prev_fw=None, prev_bw=None):
         return _patchgrid(self.lib.orc_patchgrid_level, True, p, A, B, w_l, h_l, level, prev_fw, prev_bw)
 
+    def aggregate_dense(self, p: OrcParams, w_l, h_l, p_iter, pweight, cg=None):
+        """AggregateFlowDense cut; cg = (p_iter, pt_iter, pweight) of the complementary grid or None."""
+        nop = 2 if p.mode == 1 else 1
+        out = np.zeros((h_l, w_l, nop), np.float32)
+        arrs = [np.ascontiguousarray(x, np.float32) for x in (p_iter, pweight) + (tuple(cg) if cg else ())]
+        ptrs = [_p(x) for x in arrs] + ([None] * 3 if not cg else [])
+        self.lib.orc_aggregate_dense(C.byref(p), w_l, h_l, *ptrs, _p(out))
+        return out
+
     def varref_level(self, p: OrcParams, a, b, w_l, h_l, level, camlr, flow):
         flow = np.ascontiguousarray(flow, np.float32).copy()
         self.lib.orc_varref_level(C.byref(p), _p(a), _p(b), w_l, h_l, level, camlr, _p(flow))

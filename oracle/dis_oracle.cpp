@@ -328,7 +328,9 @@ void patch_bilinear(const float* img, const Level& L, const Opt& o, float mx, fl
     const float* c = img + ((size_t)(y - 1) * L.tmp_w + (pos0 + lb)) * C; // (x1, y0)
     const float* b = a - C;                                                // (x0, y1)
     const float* d = c - C;                                                // (x0, y0)
-    for (int k = 0; k < o.psz * C; ++k) *t++ = we0 * a[k] + we1 * b[k] + we2 * c[k] + we3 * d[k];
+    // columns lb..ub like the rows (patch.cpp:388): an odd patch size samples (psz - 1)^2 positions and the last
+    // novals - (psz - 1)^2 C entries of the vector keep what they held (patch.cpp:411 still shifts all novals of them)
+    for (int k = 0; k < (ub - lb + 1) * C; ++k) *t++ = we0 * a[k] + we1 * b[k] + we2 * c[k] + we3 * d[k];
   }
   if (o.patnorm > 0 || o.costfct == 10) {                                  // patch.cpp:411-412 (NCC: always)
     float m = packet_redux(o.novals, [out](size_t i) { return out[i]; }) / o.novals;
@@ -381,7 +383,9 @@ struct PatchWork {
 void optimize_patch(Grid& g, int ip, const Level& L, const Opt& o, const float* a, const float* adx,
                     const float* ady, const float* b, PatchWork& wk) {
   const int C = o.noc, nv = o.novals, lb = -o.psz / 2, ub = o.psz / 2 - 1;
-  wk.tmpl.resize(nv); wk.dx.resize(nv); wk.dy.resize(nv); wk.pdiff.resize(nv);
+  // every PatClass owns its vectors (patch.cpp:31-41); entries no loop writes (odd patch sizes) start as zero, as in
+  // oracle/_ref where the Eigen shim zero-initialises on resize (heap garbage upstream)
+  wk.tmpl.assign(nv, 0.f); wk.dx.assign(nv, 0.f); wk.dy.assign(nv, 0.f); wk.pdiff.assign(nv, 0.f);
   float *tmpl = wk.tmpl.data(), *tdx = wk.dx.data(), *tdy = wk.dy.data(), *pdiff = wk.pdiff.data();
   float* pweight = &g.pweight[(size_t)ip * nv];
   const float ptrx = g.ptx[ip], ptry = g.pty[ip];
@@ -1193,6 +1197,26 @@ int orc_patchgrid_level(const OrcParams* p, const float* a, const float* adx, co
   if (dense_fw) aggregate_dense(gf, p->usefbcon ? &gb : nullptr, Ll, o, dense_fw);
   if (p->usefbcon && dense_bw) aggregate_dense(gb, &gf, Lr, o, dense_bw);
   return gf.n;
+}
+
+// The AggregateFlowDense cut (patchgrid.cpp:213-397): patch results of one level in, dense flow out.  cg_* = results of
+// the complementary grid (forward-backward merging) or null.  Arrays are [npatch][nop], [npatch][2], [npatch][novals].
+int orc_aggregate_dense(const OrcParams* p, int w_l, int h_l, const float* p_iter, const float* pweight,
+                        const float* cg_p_iter, const float* cg_pt_iter, const float* cg_pweight, float* flowout) {
+  const Opt o = make_opt(*p);
+  const Level L = make_level(w_l, h_l, 0, p->psz, p->psz, 0);
+  Grid g, cg;
+  g.build(L, o);
+  g.p_iter.assign(p_iter, p_iter + (size_t)g.n * o.nop);
+  g.pweight.assign(pweight, pweight + (size_t)g.n * o.novals);
+  if (cg_p_iter) {
+    cg.build(L, o);
+    cg.p_iter.assign(cg_p_iter, cg_p_iter + (size_t)cg.n * o.nop);
+    cg.pt_iter.assign(cg_pt_iter, cg_pt_iter + (size_t)cg.n * 2);
+    cg.pweight.assign(cg_pweight, cg_pweight + (size_t)cg.n * o.novals);
+  }
+  aggregate_dense(g, cg_p_iter ? &cg : nullptr, L, o, flowout);
+  return g.n;
 }
 
 void orc_varref_level(const OrcParams* p, const float* a, const float* b, int w_l, int h_l, int level, int camlr, float* flow) {

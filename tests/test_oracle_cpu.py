@@ -107,6 +107,25 @@ def test_port_matches_reference_live(port, mode, noc):
                               ref.varref_level(p, a[0], b[0], wl, hl, p.sc_l, 0, fl)), kw
 
 
+@pytest.mark.parametrize("mode,noc,psz,ov", [(1, 1, 5, .4), (1, 1, 9, .5), (1, 3, 5, .4), (1, 1, 6, .4), (2, 1, 7, .4), (1, 1, 2, 0.), (1, 1, 3, 0.),
+                                             (1, 3, 7, .6), (2, 3, 15, .7), (1, 1, 10, .6)])
+def test_port_matches_reference_on_every_patch_size(port, mode, noc, psz, ov):
+    """The 20-parameter interface takes any patch size (oflow.cpp:90-91).  Odd sizes sample (psz - 1)^2 positions into
+    vectors of psz^2 entries whose tail LossComputeErrorImage partly skips (patch.cpp:226-232,316-317,377-378); the
+    restatement must follow the reference through all of that, bit for bit (oracle/_ref zero-initialises the vectors)."""
+    if not ob.have_ref(mode, noc):
+        pytest.skip("oracle/_ref not built on this machine")
+    from of_dis_b200.synth import make_pair
+    ref = ob.Ref(mode, noc)
+    A, B, _ = make_pair(96, 160, channels=noc, mode="OF" if mode == 1 else "DE", seed=1)
+    for kw in (dict(), dict(usefbcon=1, costfct=1)):
+        p = base_orc(mode, noc, psz=psz, patove=ov, sc_f=2, sc_l=0, **kw)
+        W, H, _, _ = port.pad_dims(160, 96, p.sc_f)
+        PA = port.pyramid(A, p.sc_f, p.sc_l, p.psz)
+        PB = port.pyramid(B, p.sc_f, p.sc_l, p.psz)
+        assert np.array_equal(port.ofclass(p, PA, PB, W, H), ref.ofclass(p, PA, PB, W, H)), kw
+
+
 # ---------------------------------------------------------------- SELECTCHANNEL == 2 (gradient-magnitude input)
 def test_gradmag_pyramid_steps_match_cv2(port, gradmag_golden):
     """run_dense.cpp:139-148 on arbitrary floats: level 0 and the .5 cascade (OpenCV's own summation order, including

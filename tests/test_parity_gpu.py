@@ -235,6 +235,16 @@ CONFIGS = [
     ("of_int_nonorm", 1, 1, 2, 1024, 436, dict(patnorm=0), MAX_TOL_FINE),
     ("of_int_psz16", 1, 1, 2, 640, 272, dict(patchsz=16, patove=0.5, sc_f=3, sc_l=1), 0.05),
     ("of_int_psz4", 1, 1, 2, 320, 136, dict(patchsz=4, patove=0.5, sc_f=3, sc_l=2), 0.05),
+    # every patch size the reference accepts (oflow.cpp:90-91): even sizes without a specialised kernel, and ODD sizes,
+    # where the reference samples (psz - 1)^2 positions into vectors of psz^2 entries and LossComputeErrorImage skips
+    # the last novals % 4 of them (patch.cpp:226-232,316-317) - oracle pinned against oracle/_ref on the same cases
+    ("of_int_psz6", 1, 1, 2, 640, 272, dict(patchsz=6, patove=0.5, sc_f=3, sc_l=1), 0.05),
+    ("of_int_psz9", 1, 1, 2, 640, 272, dict(patchsz=9, patove=0.5, sc_f=3, sc_l=1), 0.05),
+    ("of_rgb_psz5", 1, 3, 2, 320, 136, dict(patchsz=5, patove=0.4, sc_f=3, sc_l=1), 0.05),
+    ("de_int_psz7_huber", 2, 1, 2, 640, 360, dict(patchsz=7, patove=0.4, sc_f=3, sc_l=1, costfct=2), 0.05),
+    ("of_int_psz10_fb", 1, 1, 2, 640, 272, dict(patchsz=10, patove=0.6, sc_f=3, sc_l=1, usefbcon=1), 0.05),
+    ("of_rgb_psz15_fb", 1, 3, 2, 320, 136, dict(patchsz=15, patove=0.7, sc_f=2, sc_l=0, usefbcon=1), 0.05),
+    ("of_int_psz2", 1, 1, 2, 160, 96, dict(patchsz=2, patove=0.0, sc_f=2, sc_l=0), 0.05),
 ]
 
 
@@ -259,7 +269,36 @@ def test_run_dense_parity(gpu, port, cfg):
     assert epe(out[1], want_swapped)[0] <= MEAN_TOL
 
 
-def test_c2_rgb_op4_full_size(gpu, port):
+@pytest.mark.parametrize("mode,noc,psz,ov", [(1, 1, 8, .4), (1, 3, 8, .4), (2, 1, 12, .75), (1, 1, 5, .4), (2, 3, 9, .5)])
+@pytest.mark.parametrize("spread", ["regular", "collapsed"])
+def test_aggregate_dense_cut(gpu, port, mode, noc, psz, ov, spread):
+    """AggregateFlowDense (patchgrid.cpp:213-397) on hand-made patch results, with forward-backward merging.
+    "collapsed": every patch of the complementary grid ends inside one patch-sized cell (a contracting / occluded
+    region) - hundreds of entries per cell, which the CSR binning must take like any other distribution."""
+    w_l, h_l = 150, 90
+    q = base_orc(mode, noc, psz=psz, patove=ov)
+    p = to_dis(gpu, q)
+    n = gpu.patch_count(p, w_l, h_l)
+    nop, nv = p.nop, noc * psz * psz
+    rng = np.random.default_rng(7)
+    p_iter = rng.standard_normal((n, nop)).astype(np.float32) * 3
+    pweight = (rng.random((n, nv)) * 9).astype(np.float32)
+    cg_p = rng.standard_normal((n, nop)).astype(np.float32) * 3
+    cg_w = (rng.random((n, nv)) * 9).astype(np.float32)
+    if spread == "regular":
+        cg_pt = np.stack([rng.random(n) * (w_l + 20) - 10, rng.random(n) * (h_l + 20) - 10], -1).astype(np.float32)
+    else:
+        cg_pt = np.stack([60 + rng.random(n) * 5, 40 + rng.random(n) * 5], -1).astype(np.float32)
+    for cg in (None, (cg_p, cg_pt, cg_w)):
+        want = port.aggregate_dense(q, w_l, h_l, p_iter, pweight, cg)
+        got = gpu.aggregate_dense(p, w_l, h_l, p_iter, pweight, cg)
+        if cg is None:
+            assert np.array_equal(got, want)      # the gather adds the covering patches in the reference's order
+        else:
+            assert np.allclose(got, want, rtol=2e-4, atol=2e-4), float(np.abs(got - want).max())
+
+
+def test_c2_rgb_op4_full_size(gpu, port):def test_c2_rgb_op4_full_size(gpu, port):
     """BASELINE.json configs[1]: run_OF_RGB operating point 4 (128 iterations, psz 12, overlap .75, scales 5..0)."""
     A, B, gt = make_pair(436, 1024, channels=3, seed=0)
     p = gpu.operating_point(4, 1024, 1, 3).copy(verbosity=0)
