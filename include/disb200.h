@@ -119,6 +119,15 @@ int disb200_run_sequence_device(DisHandle* h, const uint8_t* dFrames, int nframe
 int disb200_run_sequence_host(DisHandle* h, const uint8_t* frames, int nframes, float* out);
 int disb200_run_sequence_host_lowres(DisHandle* h, const uint8_t* frames, int nframes, float* out_low);
 
+/* Video with the temporal warm start of oflow.cpp:213-217 (the `initflow` argument; its only caller ships commented out,
+ * run_dense.cpp:354-379): pair i starts its coarsest level from pair i-1's result instead of zero - the level-sc_l flow of
+ * pair i-1, box-averaged (INTER_AREA, run_dense.cpp:372) down to the (H >> (sc_f+1)) x (W >> (sc_f+1)) grid OFClass expects
+ * and rescaled to that grid's units; pair 0 starts cold.  Pyramids are shared like in run_sequence_*; the pairs run one
+ * after another (each depends on the one before), so this is the latency path.  Results differ from run_sequence_* (a
+ * different starting point); they equal OFClass called pair by pair with that initflow. */
+int disb200_run_sequence_warm_device(DisHandle* h, const uint8_t* dFrames, int nframes, float* dOut);
+int disb200_run_sequence_warm_host(DisHandle* h, const uint8_t* frames, int nframes, float* out);
+
 /* CUDA-event stopwatch on the handle's stream (the stream every kernel is launched on). */
 int disb200_timer_begin(DisHandle* h);
 int disb200_timer_end(DisHandle* h, float* elapsed_ms);
@@ -130,6 +139,11 @@ int disb200_last_launch_count(const DisHandle* h);
  * disb200_set_stage_timing(h, 1) is on (it serialises the stream with events). */
 int disb200_set_stage_timing(DisHandle* h, int on);
 int disb200_stage_ms(const DisHandle* h, int stage, float* ms);
+
+/* The per-scale split the reference prints at verbosity 2 (oflow.cpp:292-298): device time of the inverse search (the
+ * reference's pconst + pinit + poptim: one kernel here), the densification (cflow) and the refinement (tvopt) of pyramid
+ * level `level` in the most recent run with stage timing on, and the level's patch count (#p). */
+int disb200_scale_ms(const DisHandle* h, int level, float* search_ms, float* densify_ms, float* refine_ms, int* npatches);
 
 /* Intermediate results of the most recent run (parity tests): copies to host
  *   kind 0/1/2 : padded pyramid image / dx / dy of frame `which` (0 = A, 1 = B) at `level`

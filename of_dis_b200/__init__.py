@@ -147,6 +147,15 @@ class Handle:
         _check(lib().disb200_run_sequence_host(self.h, _ptr(frames, C.c_uint8), nf, _ptr(out)))
         return out
 
+    def run_sequence_warm(self, frames: np.ndarray, out: np.ndarray | None = None) -> np.ndarray:
+        """frames (n+1, h0, w0[, C]) u8 -> (n, h0, w0, nop) f32; pair i warm-started from pair i-1 (oflow.cpp:213-217)."""
+        frames = np.ascontiguousarray(frames, np.uint8)
+        n = frames.shape[0] - 1
+        if out is None:
+            out = np.empty((n, self.h0, self.w0, self.p.nop), np.float32)
+        _check(lib().disb200_run_sequence_warm_host(self.h, _ptr(frames, C.c_uint8), n + 1, _ptr(out)))
+        return out
+
     def lowres_dims(self):
         """(h_l, w_l, nop) of the level-sc_l flow that the *_lowres entry points return (OFClass's outflow, oflow.h:105)."""
         w, h, nop = C.c_int(), C.c_int(), C.c_int()
@@ -225,6 +234,12 @@ class Handle:
         return out
 
     # -- intermediates ---------------------------------------------------------------------
+    def scale_ms(self, level: int):
+        """(search_ms, densify_ms, refine_ms, npatches) of one pyramid level in the last stage-timed run (oflow.cpp:297)."""
+        a, b, c, n = C.c_float(), C.c_float(), C.c_float(), C.c_int()
+        _check(lib().disb200_scale_ms(self.h, level, C.byref(a), C.byref(b), C.byref(c), C.byref(n)))
+        return a.value, b.value, c.value, n.value
+
     def level_shape(self, level):
         return self.H >> level, self.W >> level
 

@@ -123,6 +123,10 @@ size_t varref_plane_count(int C, int nop);  // number of float planes VarRefBuff
 void launch_upsample_crop(const float* flow, const LevelGeom& g, int nop, int sc_l, int padl, int padt, int w0,
                           int h0, float* out, int n, cudaStream_t s, LaunchStats* st);
 
+// level-sc_l flow of one pair -> initflow of the next (box mean over k x k, times scale)
+void launch_warm_init(const float* flow, int wl, int nop, int k, float scale, int wi, int hi, float* init, cudaStream_t s,
+                      LaunchStats* st);
+
 }  // namespace disb200
 
 #endif

@@ -83,7 +83,7 @@ static int validate(const DisParams& p) {
     return fail(DISB200_EUNSUPPORTED, "costfct must be 0 (L2), 1 (L1), 2 (pseudo-Huber) or 10 (NCC)");
   if (p.max_iter < 0 || p.min_iter < 0) return fail(DISB200_EINVAL, "iteration counts must be >= 0");
   if (p.sor_mode != DISB200_SOR_LEXICOGRAPHIC && p.sor_mode != DISB200_SOR_REDBLACK) return fail(DISB200_EINVAL, "sor_mode must be 0 (lexicographic) or 1 (red-black)");
-  if (p.usetvref && (p.tv_innerit < 0 || p.tv_solverit < 1)) return fail(DISB200_EINVAL, "tv_innerit >= 0 and tv_solverit >= 1 required");
+  if (p.usetvref && (p.tv_innerit < 0 || p.tv_solverit < 0)) return fail(DISB200_EINVAL, "tv_innerit >= 0 and tv_solverit >= 0 required");
   return DISB200_OK;
 }
 
@@ -116,7 +116,8 @@ struct Engine {
   bool stage_timing = false;
   float stage_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   std::vector<cudaEvent_t> ev_pool;
-  struct Mark { int stage; cudaEvent_t a, b; };
+  struct Mark { int stage; cudaEvent_t a, b; int level; };
+  float scale_ms[17][3] = {};     // [level][inverse search | densification | refinement] of the last timed run (oflow.cpp:297)
   std::vector<Mark> marks;
   size_t ev_used = 0;
 
@@ -145,7 +146,10 @@ struct Engine {
     for (int l = p.sc_l; l <= p.sc_f; ++l) {
       geom[l] = make_levelgeom(p, W, H, l);
       const LevelGeom& g = geom[l];
-      if (g.w < 2 || g.h < 2) return fail(DISB200_EUNSUPPORTED, "coarsest level smaller than 2x2 pixels");
+      if (g.w < 1 || g.h < 1) return fail(DISB200_EINVAL, "coarsest level is empty: W and H must be at least 2^sc_f");
+      // (one-pixel-wide levels run: sor_coupled's fallback, solver.c:86-89.  A level ONE ROW high with the refinement on
+      //  crashes the reference itself - segmentation fault in its 5-tap column filter - so there is nothing to match)
+      if (p.usetvref && g.h < 2) return fail(DISB200_EUNSUPPORTED, "a pyramid level one row high cannot be refined (the reference crashes on it)");
       for (int f = 0; f < 2; ++f)
         for (int a = 0; a < 3; ++a) {
           int rc = dalloc(&pyr[f][a][l], g.img_elems * (max_batch + (f == 0 ? 1 : 0)));
@@ -232,12 +236,12 @@ struct Engine {
     return ev_pool[ev_used++];
   }
   struct StageScope {
-    Engine* e; int stage; cudaEvent_t a;
-    StageScope(Engine* e_, int s) : e(e_), stage(s), a(nullptr) {
+    Engine* e; int stage, level; cudaEvent_t a;
+    StageScope(Engine* e_, int s, int lvl = -1) : e(e_), stage(s), level(lvl), a(nullptr) {
       if (e->stage_timing) { a = e->next_event(); cudaEventRecord(a, e->stream); }
     }
     ~StageScope() {
-      if (e->stage_timing) { cudaEvent_t b = e->next_event(); cudaEventRecord(b, e->stream); e->marks.push_back({stage, a, b}); }
+      if (e->stage_timing) { cudaEvent_t b = e->next_event(); cudaEventRecord(b, e->stream); e->marks.push_back({stage, a, b, level}); }
     }
   };
   cudaEvent_t open_mark[8] = {nullptr};
@@ -246,7 +250,7 @@ struct Engine {
     cudaEvent_t ev = e->next_event();
     cudaEventRecord(ev, e->stream);
     if (begin) e->open_mark[stage] = ev;
-    else e->marks.push_back({stage, e->open_mark[stage], ev});
+    else e->marks.push_back({stage, e->open_mark[stage], ev, -1});
   }
   void begin_run() {
     stats.launches = 0;
@@ -259,17 +263,20 @@ struct Engine {
     if (!stage_timing) return;
     cudaStreamSynchronize(stream);
     for (float& v : stage_ms) v = 0.f;
+    for (auto& row : scale_ms) row[0] = row[1] = row[2] = 0.f;
     for (const Mark& m : marks) {
       float ms = 0.f;
       cudaEventElapsedTime(&ms, m.a, m.b);
       stage_ms[m.stage] += ms;
+      if (m.level >= 0 && m.level < 17 && m.stage >= 1 && m.stage <= 3) scale_ms[m.level][m.stage - 1] += ms;
     }
   }
 
   // Sequence mode (video): pair i = frames (i, i+1); the n + 1 frame pyramids live in the role-A arrays and the
   // second frame of pair i is simply the first frame of pair i + 1.
   bool seq = false;
-  float* P(int f, int a, int l) const { return seq ? pyr[0][a][l] + (f ? geom[l].img_elems : 0) : pyr[f][a][l]; }
+  int pair0 = 0;   // sequence mode: first pair of the current run_levels call (warm-started sequences run pair by pair)
+  float* P(int f, int a, int l) const { return seq ? pyr[0][a][l] + (size_t)(f + pair0) * geom[l].img_elems : pyr[f][a][l]; }
 
   // a1 + a2: u8 frames (device) -> padded pyramids of both frames (dB == nullptr: dA holds n + 1 consecutive frames)
   void build_pyramids(const uint8_t* dA, const uint8_t* dB, int n, int w0, int h0, int padl, int padt) {
@@ -298,7 +305,7 @@ struct Engine {
       const LevelGeom& g = geom[sl];
       const int ndir = p.usefbcon ? 2 : 1;
       {
-        StageScope sc(this, 1);
+        StageScope sc(this, 1, sl);
         for (int d = 0; d < ndir; ++d) {                               // oflow.cpp:191-232
           PatchArgs a;
           a.tmpl_img = P(d, 0, sl); a.tmpl_dx = P(d, 1, sl); a.tmpl_dy = P(d, 2, sl);
@@ -318,7 +325,7 @@ struct Engine {
         }
       }
       {
-        StageScope sc(this, 2);
+        StageScope sc(this, 2, sl);
         for (int d = 0; d < ndir; ++d) {                               // oflow.cpp:259-267
           if (d == 1 && sl == p.sc_l) break;
           DensifyArgs a;
@@ -332,7 +339,7 @@ struct Engine {
         }
       }
       if (p.usetvref) {                                                // oflow.cpp:281-290
-        StageScope sc(this, 3);
+        StageScope sc(this, 3, sl);
         launch_varref_level(P(0, 0, sl), P(1, 0, sl), flow[0][sl], g, p, 0, vb, n, stream, &stats);
         if (p.usefbcon && sl > p.sc_l)
           launch_varref_level(P(1, 0, sl), P(0, 0, sl), flow[1][sl], g, p, 1, vb, n, stream, &stats);
@@ -457,6 +464,41 @@ struct DisHandle {
     if (ce != cudaSuccess) return fail(DISB200_ECUDA, std::string("kernel launch: ") + cudaGetErrorString(ce));
     return DISB200_OK;
   }
+
+  // Sequence with temporal warm start (oflow.cpp:213-217; the caller the reference ships disabled, run_dense.cpp:354-379):
+  // every frame's pyramid is built once, then the pairs run ONE AFTER ANOTHER on the handle's stream - pair i starts its
+  // coarsest level from pair i-1's result (its level-sc_l flow, box-averaged down to half the coarsest resolution and
+  // rescaled to that grid's units), pair 0 from zero like a cold start.
+  int enqueue_warm(const uint8_t* frames, int n, float* out) {
+    Engine& E = e;
+    if (n > cap) return fail(DISB200_EINVAL, "warm-started sequence chunk exceeds the engine capacity");
+    E.stats.launches = 0;
+    E.build_pyramids(frames, nullptr, n, w0, h0, padl, padt);
+    const LevelGeom& gl = E.geom[E.p.sc_l];
+    const LevelGeom& gc = E.geom[E.p.sc_f];
+    const int k = 1 << (E.p.sc_f + 1 - E.p.sc_l);
+    const size_t out_elems = (lowres ? low_bytes : out_bytes) / sizeof(float);
+    int rc = DISB200_OK;
+    for (int i = 0; i < n && !rc; ++i) {
+      E.pair0 = i;
+      E.has_initflow = warm_valid;
+      rc = E.run_levels(1);
+      if (rc) break;
+      launch_warm_init(E.flow[0][E.p.sc_l], gl.w, E.nop, k, 1.0f / (float)k, gc.w / 2, gc.h / 2, E.initflow, E.stream, &E.stats);
+      warm_valid = true;
+      if (lowres) {
+        CU(cudaMemcpyAsync(out + i * out_elems, E.flow[0][E.p.sc_l], low_bytes, cudaMemcpyDeviceToDevice, E.stream));
+      } else {
+        Engine::StageScope sc(&E, 4);
+        launch_upsample_crop(E.flow[0][E.p.sc_l], gl, E.nop, E.p.sc_l, padl, padt, w0, h0, out + i * out_elems, 1, E.stream, &E.stats);
+      }
+    }
+    E.pair0 = 0;
+    E.has_initflow = false;
+    launches = E.stats.launches;
+    return rc;
+  }
+  bool warm_valid = false;   // E.initflow holds the previous pair's result (within one warm-started sequence)
 
   // device-side error flags, read after the work has been synchronised
   int check_overflow() {
@@ -702,6 +744,40 @@ int disb200_run_sequence_host_lowres(DisHandle* h, const uint8_t* frames, int nf
   return run_sequence_host_impl(h, frames, nframes, out_low, true);
 }
 
+int disb200_run_sequence_warm_device(DisHandle* h, const uint8_t* dFrames, int nframes, float* dOut) {
+  if (!h || !dFrames || !dOut) return fail(DISB200_EINVAL, "null argument");
+  if (nframes < 2 || nframes - 1 > h->cap) return fail(DISB200_EINVAL, "nframes - 1 must be in 1..max_batch (one sub-batch)");
+  CU(cudaSetDevice(h->e.device));
+  h->e.begin_run();
+  h->warm_valid = false;
+  return h->enqueue_warm(dFrames, nframes - 1, dOut);
+}
+
+int disb200_run_sequence_warm_host(DisHandle* h, const uint8_t* frames, int nframes, float* out) {
+  if (!h || !frames || !out) return fail(DISB200_EINVAL, "null argument");
+  if (nframes < 2) return fail(DISB200_EINVAL, "a sequence needs at least two frames");
+  CU(cudaSetDevice(h->e.device));
+  int rc = h->ensure_staging();
+  if (rc) return rc;
+  h->e.begin_run();
+  h->warm_valid = false;
+  const int n = nframes - 1, mb = h->cap;
+  int total_launches = 0;
+  // the pairs are serial by construction (pair i needs pair i-1's result): chunks only bound the device staging
+  for (int i0 = 0; i0 < n; i0 += mb) {
+    const int m = std::min(mb, n - i0);
+    CU(cudaMemcpyAsync(h->dA[0], frames + (size_t)i0 * h->in_bytes, h->in_bytes * (m + 1), cudaMemcpyHostToDevice, h->e.stream));
+    rc = h->enqueue_warm(h->dA[0], m, h->dOut[0]);
+    if (rc) return rc;
+    total_launches += h->launches;
+    CU(cudaMemcpyAsync(out + (size_t)i0 * (h->out_bytes / sizeof(float)), h->dOut[0], h->out_bytes * m, cudaMemcpyDeviceToHost, h->e.stream));
+    CU(cudaStreamSynchronize(h->e.stream));
+  }
+  h->launches = total_launches;
+  h->e.collect_stage_times();
+  return h->check_overflow();
+}
+
 int disb200_run_batch(DisHandle* h, const uint8_t* const* imgA, const uint8_t* const* imgB, int n, float* const* out) {
   if (!h || !imgA || !imgB || !out) return fail(DISB200_EINVAL, "null argument");
   if (n < 1) return fail(DISB200_EINVAL, "n must be >= 1");
@@ -752,6 +828,16 @@ int disb200_set_stage_timing(DisHandle* h, int on) {
 int disb200_stage_ms(const DisHandle* h, int stage, float* ms) {
   if (!h || !ms || stage < 0 || stage > 7) return fail(DISB200_EINVAL, "bad argument");
   *ms = h->e.stage_ms[stage];
+  return DISB200_OK;
+}
+
+int disb200_scale_ms(const DisHandle* h, int level, float* search_ms, float* densify_ms, float* refine_ms, int* npatches) {
+  if (!h) return fail(DISB200_EINVAL, "null handle");
+  if (level < h->e.p.sc_l || level > h->e.p.sc_f) return fail(DISB200_EINVAL, "level outside sc_l..sc_f");
+  if (search_ms) *search_ms = h->e.scale_ms[level][0];
+  if (densify_ms) *densify_ms = h->e.scale_ms[level][1];
+  if (refine_ms) *refine_ms = h->e.scale_ms[level][2];
+  if (npatches) *npatches = h->e.geom[level].npatch;
   return DISB200_OK;
 }
 
@@ -880,7 +966,7 @@ int disb200_varref_level(const DisParams* params, const float* im_a, const float
   int rc = validate(*params);
   if (rc) return rc;
   if (disb200_device_count() < 1) return fail(DISB200_ECUDA, "no CUDA device (this library has no CPU path)");
-  if (w_l < 2 || h_l < 2) return fail(DISB200_EUNSUPPORTED, "level smaller than 2x2 pixels");
+  if (w_l < 1 || h_l < 2) return fail(DISB200_EUNSUPPORTED, "level must be at least 1 x 2 pixels (the reference crashes on one-row levels)");
   // an engine whose only level is `level`-like: reuse the allocator with sc_f = sc_l = 0 on a w_l x h_l frame
   DisParams q = *params;
   q.sc_f = q.sc_l = 0;

@@ -106,6 +106,15 @@ int main(int argc, char** argv) {
     static const char* names[5] = {"Pyramide+Gradients", "Inverse search    ", "Densification     ",
                                    "Variational refin.", "Upsample+crop     "};
     std::printf("TIME (Device setup       ) (ms): %3g\n", ms_create);
+    // the reference's per-scale line (oflow.cpp:297); template extraction, start values and the search are ONE kernel
+    // here, so its time is reported as poptim and pconst / pinit are 0
+    for (int sl = p.sc_f; sl >= p.sc_l; --sl) {
+      float se = 0.f, de = 0.f, tv = 0.f;
+      int np = 0;
+      disb200_scale_ms(h, sl, &se, &de, &tv, &np);
+      std::printf("TIME (Sc: %i, #p:%6i, pconst, pinit, poptim, cflow, tvopt, total): %8.2f %8.2f %8.2f %8.2f %8.2f -> %8.2f ms.\n", sl, np,
+                  0.0, 0.0, se, de, tv, se + de + tv);
+    }
     for (int s = 0; s < 5; ++s) {
       float ms = 0.f;
       disb200_stage_ms(h, s, &ms);

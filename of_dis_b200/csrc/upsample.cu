@@ -93,7 +93,36 @@ __global__ void crop_kernel(const float* __restrict__ flow, int wl, int hl, int 
   for (int c = 0; c < NOP; ++c) d[c] = __ldg(s + c);
 }
 
+// Temporal warm start: the level-sc_l flow of the previous pair -> the `initflow` array OFClass takes
+// (oflow.h:106, oflow.cpp:213-217: (h_c / 2) x (w_c / 2) x nop at half the coarsest resolution, in units of that grid),
+// by the rule of the reference's disabled caller (run_dense.cpp:370-373: flow *= scale; cv::resize(INTER_AREA) = box mean).
+template <int NOP>
+__global__ void warm_init_kernel(const float* __restrict__ flow, int wl, int k, float scale, int wi, int hi,
+                                 float* __restrict__ init) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y;
+  if (x >= wi || y >= hi) return;
+  float acc[NOP];
+#pragma unroll
+  for (int c = 0; c < NOP; ++c) acc[c] = 0.f;
+  for (int r = 0; r < k; ++r)
+    for (int q = 0; q < k; ++q)
+#pragma unroll
+      for (int c = 0; c < NOP; ++c) acc[c] += flow[((size_t)(y * k + r) * wl + (x * k + q)) * NOP + c];
+  const float m = scale / (float)(k * k);
+#pragma unroll
+  for (int c = 0; c < NOP; ++c) init[((size_t)y * wi + x) * NOP + c] = acc[c] * m;
+}
+
 }  // namespace
+
+void launch_warm_init(const float* flow, int wl, int nop, int k, float scale, int wi, int hi, float* init, cudaStream_t s,
+                      LaunchStats* st) {
+  if (wi < 1 || hi < 1) return;
+  dim3 blk(64), grd((wi + 63) / 64, hi);
+  if (nop == 2) warm_init_kernel<2><<<grd, blk, 0, s>>>(flow, wl, k, scale, wi, hi, init);
+  else warm_init_kernel<1><<<grd, blk, 0, s>>>(flow, wl, k, scale, wi, hi, init);
+  st->launches++;
+}
 
 void launch_upsample_crop(const float* flow, const LevelGeom& g, int nop, int sc_l, int padl, int padt, int w0,
                           int h0, float* out, int n, cudaStream_t s, LaunchStats* st) {

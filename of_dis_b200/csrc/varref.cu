@@ -340,7 +340,9 @@ __device__ __forceinline__ void data_term_de(const Deriv8 (&dv)[C], float m, flo
 //   OF: cA = {h, v, vt, i12}   cB = {i11, i22, b1, b2}
 //   DE: cA = {h, v, vt, a11 + sum(psi)}   cB = {b1, 0, 0, 0}
 // (hl of pixel i is h of pixel i-1, which the solver already holds.)
-template <int C, bool OF>
+// RAW (OF only; the one-pixel-wide levels that sor_coupled hands to sor_coupled_slow_but_readable, solver.c:86-89): the
+// data term as compute_data leaves it, cA = {h, v, vt, a12}, cB = {a11, a22, b1, b2}.
+template <int C, bool OF, bool RAW = false>
 __device__ __forceinline__ void system_pixel(const DerivPtrs& D, const float* __restrict__ mask, const float* sp,
                                              const float* __restrict__ fl, const float* q, int i, int j, int w,
                                              int h, size_t cstride, size_t o, float hd3, float hg3, float4& cA,
@@ -388,7 +390,10 @@ __device__ __forceinline__ void system_pixel(const DerivPtrs& D, const float* __
     bb += vv * (wb[k] - wc[k]);
     b[k] = bb;
   }
-  if (OF) {
+  if (OF && RAW) {
+    cA = make_float4(hh, vv, vt, A12);
+    cB = make_float4(A11, A22, b[0], b[NOP - 1]);
+  } else if (OF) {
     // solver.c:122-128,184,244
     const float dfirst = hl + (hh + vv), dmid = (hl + hh) + (vt + vv), dlast = hl + (hh + vt);
     const float dpsis = !hast ? dfirst : (hasb ? dmid : dlast);
@@ -762,6 +767,71 @@ tv_fused_kernel(DerivPtrs D, const float* __restrict__ mask_all, float* __restri
   }
 }
 
+// Levels one pixel wide (w < 2, any h >= 2; h < 2 crashes the reference itself and is refused at create): sor_coupled
+// falls back to sor_coupled_slow_but_readable (solver.c:34-78,86-89), a point-wise update - du from the OLD dv, then dv
+// from the NEW du - instead of the 2x2 block solve.  A handful of pixels per pair: one thread per pair runs the whole
+// level sequentially (diffusivity, data term + laplacian, the sweeps), in the reference's order.
+template <int C, bool OF>
+__global__ void tv_narrow_kernel(DerivPtrs D, const float* __restrict__ mask_all, float* __restrict__ flow_all,
+                                 float* __restrict__ du_all, float* __restrict__ s_all, Dims d, int camlr,
+                                 float quarter_alpha, float hd3, float hg3, int n_inner, int iters, float omega,
+                                 float4* __restrict__ cA_all, float4* __restrict__ cB_all, int n) {
+  constexpr int NOP = OF ? 2 : 1;
+  const int pair = blockIdx.x * blockDim.x + threadIdx.x;
+  if (pair >= n) return;
+  const int w = d.w, h = d.h, npix = w * h;
+  float* fl = flow_all + (size_t)pair * npix * NOP;
+  float* du = du_all + (size_t)pair * d.plane * NOP;
+  float* sp = s_all + (size_t)pair * d.plane;
+  const float* mask = mask_all + (size_t)pair * d.plane;
+  float4* cA = cA_all + (size_t)pair * d.plane;
+  float4* cB = cB_all + (size_t)pair * d.plane;
+  const size_t o = (size_t)pair * C * d.plane;
+  for (int k = 0; k < npix * NOP; ++k) du[k] = 0.f;
+  for (int it = 0; it < n_inner; ++it) {
+    for (int pix = 0; pix < npix; ++pix) sp[pix] = smooth_pixel<OF>(fl, du, pix % w, pix / w, w, h, camlr, quarter_alpha, it == 0);
+    for (int pix = 0; pix < npix; ++pix) {
+      float4 a, b;
+      system_pixel<C, OF, true>(D, mask, sp, fl, du, pix % w, pix / w, w, h, d.plane, o, hd3, hg3, a, b);
+      cA[pix] = a;
+      cB[pix] = b;
+    }
+    for (int sw = 0; sw < iters; ++sw)
+      for (int j = 0; j < h; ++j)
+        for (int i = 0; i < w; ++i) {
+          const int pix = j * w + i;
+          const float4 a = cA[pix], b = cB[pix];
+          const float hl = i > 0 ? cA[pix - 1].x : 0.f;
+          if (OF) {
+            float2* q = reinterpret_cast<float2*>(du);
+            float su = 0.f, sv = 0.f, sum = 0.f;                     // solver.c:42-63
+            if (j > 0) { su -= a.z * q[pix - w].x; sv -= a.z * q[pix - w].y; sum += a.z; }
+            if (i > 0) { su -= hl * q[pix - 1].x; sv -= hl * q[pix - 1].y; sum += hl; }
+            if (j < h - 1) { su -= a.y * q[pix + w].x; sv -= a.y * q[pix + w].y; sum += a.y; }
+            if (i < w - 1) { su -= a.x * q[pix + 1].x; sv -= a.x * q[pix + 1].y; sum += a.x; }
+            const float A11 = b.x + sum, A12 = a.w, A22 = b.y + sum;
+            const float B1 = b.z - su, B2 = b.w - sv;
+            float2 c = q[pix];
+            c.x = (1.0f - omega) * c.x + omega / A11 * (B1 - A12 * c.y);   // solver.c:73-74
+            c.y = (1.0f - omega) * c.y + omega / A22 * (B2 - A12 * c.x);
+            q[pix] = c;
+          } else {
+            const float2 z = make_float2(0.f, 0.f);
+            const float2 left = i > 0 ? make_float2(du[pix - 1], 0.f) : z, r = i < w - 1 ? make_float2(du[pix + 1], 0.f) : z;
+            const float2 t = j > 0 ? make_float2(du[pix - w], 0.f) : z, bt = j < h - 1 ? make_float2(du[pix + w], 0.f) : z;
+            const int rowtype = j == 0 ? 0 : (j < h - 1 ? 1 : 2);
+            du[pix] = sor_update<false>(a, b, hl, i > 0, rowtype, omega, left, make_float2(du[pix], 0.f), r, t, bt).x;
+          }
+        }
+  }
+  for (int pix = 0; pix < npix; ++pix) {
+    float u, v;
+    load_uv<OF>(fl, du, pix, camlr, u, v);
+    fl[pix * NOP] = u;
+    if (OF) fl[pix * NOP + 1] = v;
+  }
+}
+
 template <int C, bool OF>
 void varref_level_impl(const float* im_a, const float* im_b, float* flow, const LevelGeom& g, const DisParams& p,
                        int camlr, const VarRefBuffers& vb, int n, cudaStream_t st, LaunchStats* ls) {
@@ -779,6 +849,20 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
   DerivPtrs D{vb.Ix, vb.Iy, vb.Iz, vb.Ixx, vb.Ixy, vb.Iyy, vb.Ixz, vb.Iyz};
   float4* cA = reinterpret_cast<float4*>(vb.coef);
   float4* cB = reinterpret_cast<float4*>(vb.inv);
+  if (g.w < 2) {   // one-pixel-wide level: the reference's point-wise fallback (solver.c:86-89)
+    tv_narrow_kernel<C, OF><<<(n + 31) / 32, 32, 0, st>>>(D, vb.mask, flow, vb.du, vb.smooth, d, camlr, qa, hd3, hg3, n_inner,
+                                                          p.tv_solverit, p.tv_sor, cA, cB, n);
+    ls->launches++;
+    return;
+  }
+  if (p.tv_solverit < 1) {
+    // sor_coupled / sor_coupled_slow_but_readable_DE with zero sweeps leave the increment at 0: the level's result is
+    // uu = wx + 0, which for depth still applies the sign clamp (refine_variational.cpp:301-323)
+    cudaMemsetAsync(vb.du, 0, sizeof(float) * vb.plane_cap * NOP * n, st);
+    finish_kernel<OF><<<grd, blk, 0, st>>>(flow, vb.du, d, camlr);
+    ls->launches++;
+    return;
+  }
   const bool pipelined = g.h * p.tv_solverit <= 512;
   const size_t fused_smem = (size_t)g.w * g.h * (NOP + 1) * sizeof(float);
   const char* tv_path = getenv("DISB200_TV_PATH");   // experiment / test switch, see below

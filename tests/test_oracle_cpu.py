@@ -11,7 +11,7 @@ import numpy as np
 import pytest
 
 from oracle import bindings as ob
-from tests.helpers import base_orc, epe
+from tests.helpers import TINY_CASES, base_orc, epe
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
@@ -124,6 +124,24 @@ def test_port_matches_reference_on_every_patch_size(port, mode, noc, psz, ov):
         PA = port.pyramid(A, p.sc_f, p.sc_l, p.psz)
         PB = port.pyramid(B, p.sc_f, p.sc_l, p.psz)
         assert np.array_equal(port.ofclass(p, PA, PB, W, H), ref.ofclass(p, PA, PB, W, H)), kw
+
+
+@pytest.mark.parametrize("case", TINY_CASES)
+def test_port_matches_reference_on_tiny_levels(port, case):
+    """Pyramid levels down to one pixel: the restatement against oracle/_ref.  (A level one ROW high with the refinement
+    on is outside the domain: the reference itself dies with a segmentation fault there.)"""
+    mode, noc, w0, h0, sc_f, sc_l, kw = case
+    if not ob.have_ref(mode, noc):
+        pytest.skip("oracle/_ref not built on this machine")
+    from of_dis_b200.synth import make_pair
+    A, B, _ = make_pair(h0, w0, channels=noc, mode="OF" if mode == 1 else "DE", seed=1)
+    p = base_orc(mode, noc, sc_f=sc_f, sc_l=sc_l, **kw)
+    W, H, _, _ = port.pad_dims(w0, h0, p.sc_f)
+    PA = port.pyramid(A, p.sc_f, p.sc_l, p.psz)
+    PB = port.pyramid(B, p.sc_f, p.sc_l, p.psz)
+    want = ob.Ref(mode, noc).ofclass(p, PA, PB, W, H)
+    assert np.isfinite(want).all()
+    assert np.array_equal(port.ofclass(p, PA, PB, W, H), want)
 
 
 # ---------------------------------------------------------------- SELECTCHANNEL == 2 (gradient-magnitude input)
@@ -256,7 +274,7 @@ def test_clis_fail_loudly_without_gpu(dis, tmp_path):
 
 def test_invalid_parameters_are_rejected(dis):
     p = dis.operating_point(2, 256)
-    for kw in (dict(mode=3), dict(channels=2), dict(sc_l=4, sc_f=3), dict(patove=1.0), dict(patchsz=7), dict(costfct=3), dict(sor_mode=2), dict(gradmag=2),
+    for kw in (dict(mode=3), dict(channels=2), dict(sc_l=4, sc_f=3), dict(patove=1.0), dict(patchsz=1), dict(patchsz=17), dict(costfct=3), dict(tv_solverit=-1), dict(sor_mode=2), dict(gradmag=2),
                dict(gradmag=1, channels=3)):
         with pytest.raises(dis.DisError) as e:
             dis.Handle(p.copy(**kw), 256, 128, 1)

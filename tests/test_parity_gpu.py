@@ -13,7 +13,7 @@ import pytest
 
 from oracle import bindings as ob
 from of_dis_b200.synth import make_pair
-from tests.helpers import base_orc, epe, to_dis, to_orc
+from tests.helpers import TINY_CASES, base_orc, epe, to_dis, to_orc
 
 pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -269,6 +269,29 @@ def test_run_dense_parity(gpu, port, cfg):
     assert epe(out[1], want_swapped)[0] <= MEAN_TOL
 
 
+@pytest.mark.parametrize("case", TINY_CASES)
+def test_tiny_levels_and_zero_sweeps(gpu, port, case):
+    """Levels down to one pixel wide (sor_coupled's point-wise fallback, solver.c:86-89), 1 x 1 levels without
+    refinement, tv_solverit = 0: same cases on which the oracle is pinned against oracle/_ref in the CPU suite."""
+    mode, noc, w0, h0, sc_f, sc_l, kw = case
+    A, B, _ = make_pair(h0, w0, channels=noc, mode="OF" if mode == 1 else "DE", seed=1)
+    q = base_orc(mode, noc, sc_f=sc_f, sc_l=sc_l, **kw)
+    want = port.run_dense(q, A, B)
+    with gpu.Handle(to_dis(gpu, q), w0, h0, max_batch=2) as hd:
+        out = hd.run_host(np.stack([A, A]), np.stack([B, B]))
+    assert np.isfinite(out).all()
+    m, mx = epe(out[0], want)
+    assert m <= MEAN_TOL and mx <= 0.05, "EPE(GPU,CPU) mean %g max %g" % (m, mx)
+    assert np.array_equal(out[0], out[1])
+
+
+def test_one_row_level_with_refinement_is_refused(gpu):
+    """The reference segfaults on a level one row high when the refinement is on (probe in DESIGN.md): refused, not guessed."""
+    q = base_orc(1, 1, sc_f=4, sc_l=0)
+    with pytest.raises(gpu.DisError):
+        gpu.Handle(to_dis(gpu, q), 64, 16, max_batch=1)
+
+
 @pytest.mark.parametrize("mode,noc,psz,ov", [(1, 1, 8, .4), (1, 3, 8, .4), (2, 1, 12, .75), (1, 1, 5, .4), (2, 3, 9, .5)])
 @pytest.mark.parametrize("spread", ["regular", "collapsed"])
 def test_aggregate_dense_cut(gpu, port, mode, noc, psz, ov, spread):
@@ -298,7 +321,33 @@ def test_aggregate_dense_cut(gpu, port, mode, noc, psz, ov, spread):
             assert np.allclose(got, want, rtol=2e-4, atol=2e-4), float(np.abs(got - want).max())
 
 
-def test_c2_rgb_op4_full_size(gpu, port):def test_c2_rgb_op4_full_size(gpu, port):
+@pytest.mark.parametrize("mode,ch,op,w0,h0", [(1, 1, 2, 1024, 436), (1, 3, 2, 640, 272), (2, 1, 2, 1280, 720), (1, 1, 3, 512, 218)])
+def test_against_the_compiled_reference_directly(gpu, port, mode, ch, op, w0, h0):
+    """No indirection: the CUDA path against oracle/_ref (the reference's own sources, compiled unmodified by
+    oracle/Makefile; the .so travels to the GPU box) on the same pyramids - OFClass cut and whole driver path."""
+    if not ob.have_ref(mode, ch):
+        pytest.skip("oracle/_ref did not travel with this snapshot")
+    ref = ob.Ref(mode, ch)
+    A, B, _ = make_pair(h0, w0, channels=ch, mode="OF" if mode == 1 else "DE", seed=4)
+    p = gpu.operating_point(op, w0, mode, ch).copy(verbosity=0)
+    q = to_orc(p)
+    W, H, padl, padt = port.pad_dims(w0, h0, p.sc_f)
+    PA = port.pyramid(A, p.sc_f, p.sc_l, p.patchsz)
+    PB = port.pyramid(B, p.sc_f, p.sc_l, p.patchsz)
+    want_low = ref.ofclass(q, PA, PB, W, H)
+    got_low = gpu.ofclass(p, PA, PB, W, H)
+    with gpu.Handle(p, w0, h0, max_batch=1) as hd:
+        got = hd.run_host(A[None], B[None])[0]
+    want = port.upsample_crop(want_low, p.sc_l, padl, padt, w0, h0)
+    tol = MAX_TOL_FINE if op == 2 else MAX_TOL_DENSE
+    for g, w in ((got_low, want_low), (got, want)):
+        m, mx = epe(g, w)
+        assert m <= MEAN_TOL and mx <= tol, "EPE(GPU, compiled reference) mean %g max %g" % (m, mx)
+    if op == 2 and ch == 1:
+        assert np.array_equal(got_low, want_low) and np.array_equal(got, want)   # grey op2: bit-identical to the reference
+
+
+def test_c2_rgb_op4_full_size(gpu, port):
     """BASELINE.json configs[1]: run_OF_RGB operating point 4 (128 iterations, psz 12, overlap .75, scales 5..0)."""
     A, B, gt = make_pair(436, 1024, channels=3, seed=0)
     p = gpu.operating_point(4, 1024, 1, 3).copy(verbosity=0)
@@ -367,6 +416,9 @@ def test_cli_matches_library(gpu, tmp_path):
         assert r.returncode == 0, r.stderr
         assert "O.Flow Run-Time" in r.stdout
         p = gpu.operating_point(2, 200, mode, 1).copy(gradmag=int(exe.endswith("GRAD")))
+        # operating points print at verbosity 2 (run_dense.cpp:234): one "TIME (Sc: l, #p: n, ...)" line per scale (oflow.cpp:297)
+        sc_lines = [l for l in r.stdout.splitlines() if l.startswith("TIME (Sc: ")]
+        assert [int(l.split(",")[0].split(":")[1]) for l in sc_lines] == list(range(p.sc_f, p.sc_l - 1, -1)), r.stdout
         with gpu.Handle(p, 200, 120, 1) as hd:
             want = hd.run_host(A[None], B[None])[0]
         raw = open(out, "rb").read()
@@ -491,6 +543,41 @@ def test_video_sequence_reuses_pyramids_and_matches_explicit_pairs(gpu):
             assert hd.launch_count() > 0 and l_pairs > 0
         assert np.array_equal(got, want)
         assert np.array_equal(got3, want[:3])
+
+
+@pytest.mark.parametrize("mode,ch", [(1, 1), (2, 1), (1, 3)])
+def test_video_sequence_temporal_warm_start(gpu, port, mode, ch):
+    """disb200_run_sequence_warm_*: pair i starts from pair i-1's result through OFClass's `initflow` (oflow.cpp:213-217).
+    Checked against the CPU oracle called pair by pair with the same initflow (box mean of its own previous level-sc_l
+    flow, the INTER_AREA rule of the reference's disabled caller, run_dense.cpp:370-373)."""
+    from of_dis_b200.synth import make_sequence
+    h0, w0 = 136, 240
+    fr = make_sequence(h0, w0, 5, seed=1)
+    frames = np.stack(fr) if ch == 1 else np.stack([np.stack([f, np.roll(f, 3, 0), np.roll(f, 5, 1)], -1) for f in fr])
+    q = base_orc(mode, ch, sc_f=3, sc_l=1)
+    p = to_dis(gpu, q)
+    W, H, padl, padt = port.pad_dims(w0, h0, q.sc_f)
+    k = 1 << (q.sc_f + 1 - q.sc_l)
+    hi, wi = (H >> q.sc_f) // 2, (W >> q.sc_f) // 2
+    nop = p.nop
+    want, prev = [], None
+    for i in range(len(frames) - 1):
+        PA = port.pyramid(frames[i], q.sc_f, q.sc_l, q.psz)
+        PB = port.pyramid(frames[i + 1], q.sc_f, q.sc_l, q.psz)
+        init = None
+        if prev is not None:
+            init = (prev[:hi * k, :wi * k].reshape(hi, k, wi, k, nop).astype(np.float64).sum(axis=(1, 3)) / (k * k) / k).astype(np.float32)
+        prev = port.ofclass(q, PA, PB, W, H, initflow=init)
+        want.append(port.upsample_crop(prev, q.sc_l, padl, padt, w0, h0))
+    want = np.stack(want)
+    with gpu.Handle(p, w0, h0, max_batch=3) as hd:        # 4 pairs, capacity 3: two chunks, the warm state carries over
+        got = hd.run_sequence_warm(frames)
+        cold = hd.run_sequence(frames)
+        assert hd.launch_count() > 0
+    assert np.array_equal(got[0], cold[0])                # pair 0 starts cold
+    assert not np.array_equal(got[1:], cold[1:])          # the others start somewhere else
+    m, mx = epe(got, want)
+    assert m <= MEAN_TOL and mx <= 0.05, "EPE(GPU,CPU) mean %g max %g" % (m, mx)
 
 
 @pytest.mark.parametrize("mode,ch,op,w0,h0", [(1, 1, 2, 1024, 436), (2, 1, 2, 640, 360), (1, 3, 2, 320, 136), (1, 1, 4, 150, 90)])
