@@ -322,6 +322,8 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="CPU baseline sample budget (seconds of measuring windows)")
     ap.add_argument("--ref-seconds", type=float, default=150.0, help="--impl reference: total budget of the measuring windows")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--streams", type=int, default=0, help="DisTuning.streams (0 = automatic); 1 for a serialised ncu launch list")
+    ap.add_argument("--tv-schedule", type=int, default=0, help="DisTuning.tv_schedule (0 auto, 1 fused, 2 split, 3 general wavefront)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--sor", default="lexicographic", choices=["lexicographic", "redblack"],
                     help="redblack: the throughput variant (a different iterate: ~0.04 px mean from the parity result, never the headline)")
@@ -397,6 +399,8 @@ def main():
     dA, dB = hA.cuda(non_blocking=False), hB.cuda(non_blocking=False)
     dOut = torch.empty((nb, h0, w0, nop), dtype=torch.float32, device="cuda")
     torch.cuda.synchronize()
+    if args.streams or args.tv_schedule:
+        dis.set_tuning(streams=args.streams, tv_schedule=args.tv_schedule)
     hd = dis.Handle(p, w0, h0, max_batch=nb, device=local_rank)
 
     def barrier():

@@ -70,6 +70,19 @@ typedef struct DisParams {
 
 typedef struct DisHandle DisHandle;
 
+/* Schedule selection (every choice computes the same result; the automatic one is what the benchmarks run).  Read when a
+ * handle is created (and by the one-shot stage entry points); 0 in a field = automatic.  Used by the tests to force each
+ * SOR schedule against the oracle and by the A/B measurements in DESIGN.md. */
+typedef struct DisTuning {
+  int streams;       /* sub-batches of one run_batch call on their own streams (auto: 2 from 1184 pairs up) */
+  int host_chunk;    /* pairs per pipelined chunk of the host-pointer entry points (auto: n / 8, at least 16) */
+  int tv_schedule;   /* refinement of a level: 1 fused (one CTA per pair), 2 split (one-warp / banded SOR), 3 split with the
+                        general CTA wavefront SOR */
+  int sorb_max;      /* largest n * bands the banded SOR takes (auto and upper bound: the number of co-resident CTAs) */
+  int patch_map;     /* 1: value-interleaved lane mapping of the inverse search where the block mapping is the default */
+} DisTuning;
+int disb200_set_tuning(const DisTuning* t);   /* NULL restores the automatic choices */
+
 /* Operating points 1..4 of run_dense.cpp:226-268 (anything else selects 2), including
  * AutoFirstScaleSelect (run_dense.cpp:181-184) on the unpadded image width. */
 int disb200_operating_point(int op, int width, int mode, int channels, DisParams* out);
@@ -157,6 +170,13 @@ int disb200_fetch(DisHandle* h, int kind, int which, int level, int pair, void* 
 int disb200_ofclass(const DisParams* params, const float* const* im_ao, const float* const* im_ao_dx,
                     const float* const* im_ao_dy, const float* const* im_bo, const float* const* im_bo_dx,
                     const float* const* im_bo_dy, int W, int H, float* outflow, const float* initflow);
+
+/* The same on an existing handle (no allocation per call: what a maintainer who replaces the OFClass constructor inside a
+ * loop over frames wants).  W, H are the handle's padded dimensions (disb200_padded_dims of its w0, h0);
+ * uses pair slot 0 of the handle's workspace and returns when outflow is complete. */
+int disb200_ofclass_handle(DisHandle* h, const float* const* im_ao, const float* const* im_ao_dx, const float* const* im_ao_dy,
+                           const float* const* im_bo, const float* const* im_bo_dx, const float* const* im_bo_dy,
+                           float* outflow, const float* initflow);
 
 /* VarRefClass-level entry (refine_variational.h:35-37): refine `flow` (h_l*w_l*nop, in place)
  * on one level given the padded level images of both frames. */

@@ -156,6 +156,12 @@ class Handle:
         _check(lib().disb200_run_sequence_warm_host(self.h, _ptr(frames, C.c_uint8), n + 1, _ptr(out)))
         return out
 
+    def ofclass(self, A, B, initflow=None) -> np.ndarray:
+        """disb200_ofclass_handle: the OFClass cut on this handle's workspace (A, B as for ofclass())."""
+        out = np.zeros((self.H >> self.p.sc_l, self.W >> self.p.sc_l, self.p.nop), np.float32)
+        _check(lib().disb200_ofclass_handle(self.h, *_pyr_ptrs(self.p, A, B), _ptr(out), _ptr(initflow)))
+        return out
+
     def lowres_dims(self):
         """(h_l, w_l, nop) of the level-sc_l flow that the *_lowres entry points return (OFClass's outflow, oflow.h:105)."""
         w, h, nop = C.c_int(), C.c_int(), C.c_int()
@@ -269,6 +275,35 @@ class Handle:
         for kind, key in ((4, "p_iter"), (5, "pt_iter"), (6, "pweight")):
             _check(lib().disb200_fetch(self.h, kind, which, self.p.sc_l, pair, _ptr(r[key]), C.c_size_t(r[key].nbytes)))
         return r
+
+
+class DisTuning(C.Structure):
+    """Mirror of struct DisTuning (schedule selection; 0 = automatic)."""
+    _fields_ = [("streams", C.c_int), ("host_chunk", C.c_int), ("tv_schedule", C.c_int), ("sorb_max", C.c_int), ("patch_map", C.c_int)]
+
+
+TV_AUTO, TV_FUSED, TV_SPLIT, TV_GENERAL = 0, 1, 2, 3
+
+
+def set_tuning(**kw):
+    """disb200_set_tuning; no arguments restores the automatic choices.  Read by handles created afterwards."""
+    if not kw:
+        _check(lib().disb200_set_tuning(None))
+        return
+    t = DisTuning(**kw)
+    _check(lib().disb200_set_tuning(C.byref(t)))
+
+
+def _pyr_ptrs(params, A, B):
+    fp = C.POINTER(C.c_float)
+    ptrs = []
+    for d in (*A, *B):
+        arr = (fp * (params.sc_f + 1))()
+        for l, a in d.items():
+            assert a.dtype == np.float32 and a.flags.c_contiguous
+            arr[l] = a.ctypes.data_as(fp)
+        ptrs.append(arr)
+    return ptrs
 
 
 def ofclass(params: DisParams, A, B, W: int, H: int, initflow=None) -> np.ndarray:

@@ -29,6 +29,7 @@ struct OptConst {
   int max_iter, min_iter, patnorm, costfct, mode;
   float dp_thresh_sq, dr_thresh, res_thresh, outlierthresh;
   float minerrval, normoutlier;
+  int patch_map = 0;   // DisTuning::patch_map
 };
 
 OptConst make_optconst(const DisParams& p);
@@ -114,7 +115,11 @@ struct VarRefBuffers {
   unsigned* sorb_ctl = nullptr;   // device: {ticket counter, error flag} of the banded SOR; null = banded SOR off
   unsigned* sorb_host = nullptr;  // host:   {launch epoch, tickets issued so far}
   size_t plane_cap;  // elements per pair per plane (>= w*h of the largest level)
+  int tv_schedule = 0;   // DisTuning::tv_schedule
+  int sorb_max = 0;      // banded SOR: largest n * bands (<= co-resident CTAs of sor_band_kernel on this device; 0 = off)
 };
+// co-resident CTAs of the banded SOR kernel on the current device (occupancy API x SM count), for `solverit` sweeps
+int sor_band_resident_ctas(bool of, int solverit);
 void launch_varref_level(const float* im_a, const float* im_b, float* flow, const LevelGeom& g, const DisParams& p,
                          int camlr, const VarRefBuffers& vb, int n, cudaStream_t s, LaunchStats* st);
 size_t varref_plane_count(int C, int nop);  // number of float planes VarRefBuffers needs

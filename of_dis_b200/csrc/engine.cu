@@ -15,10 +15,13 @@
 namespace disb200 {
 
 static thread_local std::string g_err;
+static DisTuning g_tuning = {0, 0, 0, 0, 0};   // disb200_set_tuning; copied into every handle / engine at create
 static int fail(int code, const std::string& msg) {
   g_err = msg;
   return code;
 }
+// internal: the banded SOR lost co-residency; the caller reruns the call once (bands are off from then on)
+static const int DISB200_RETRY_NO_BANDS = -77;
 #define CU(call)                                                                          \
   do {                                                                                    \
     cudaError_t e__ = (call);                                                             \
@@ -133,6 +136,7 @@ struct Engine {
   int init(const DisParams& prm, int W_, int H_, int max_batch_, int device_) {
     p = prm;
     o = make_optconst(p);
+    o.patch_map = g_tuning.patch_map;
     W = W_; H = H_; C = p.channels; nop = o.nop; max_batch = max_batch_; device = device_;
     if (W % (1 << p.sc_f) || H % (1 << p.sc_f)) return fail(DISB200_EINVAL, "W and H must be divisible by 2^sc_f (oflow.h:102)");
     CU(cudaSetDevice(device));
@@ -201,6 +205,12 @@ struct Engine {
       CU(cudaMemset(sorb_ctl, 0, 2 * sizeof(unsigned)));
       sorb_host[0] = sorb_host[1] = 0;
       vb.sorb_ctl = sorb_ctl; vb.sorb_host = sorb_host;
+      vb.tv_schedule = g_tuning.tv_schedule;
+      // Bands wait for their neighbours: all bands of a launch must be co-resident.  The bound is what THIS device holds
+      // of THIS kernel (occupancy API), not a constant; a handle that shares the GPU with other work can still fall short
+      // of it, which the bounded poll turns into a flag and the entry points into a rerun without bands (band_off).
+      const int resident = sor_band_resident_ctas(p.mode == DISB200_MODE_OF, std::min(std::max(p.tv_solverit, 1), 3));
+      vb.sorb_max = g_tuning.sorb_max > 0 ? std::min(g_tuning.sorb_max, resident) : resident;
     }
     return DISB200_OK;
   }
@@ -222,7 +232,8 @@ struct Engine {
     CU(cudaMemcpy(&v, sorb_ctl + 1, sizeof(unsigned), cudaMemcpyDeviceToHost));
     if (v) {
       cudaMemset(sorb_ctl + 1, 0, sizeof(unsigned));
-      return fail(DISB200_ECUDA, "banded SOR: a band timed out waiting for its neighbour (result invalid)");
+      vb.sorb_max = 0;   // this engine stops using bands: its GPU does not keep them co-resident (shared device)
+      return fail(DISB200_RETRY_NO_BANDS, "banded SOR: a band timed out waiting for its neighbour (result invalid)");
     }
     return DISB200_OK;
   }
@@ -362,6 +373,7 @@ struct DisHandle {
   Engine e;                       // sub-batch engine 0; owns the handle's main stream
   std::vector<Engine*> extra;     // sub-batch engines 1.. (own stream each), created on demand
   int nsub = 1;                   // sub-batches run concurrently on separate streams
+  int host_chunk = 0;             // DisTuning::host_chunk
   int cap = 0;                    // pairs per sub-batch engine
   int max_batch = 0;              // pairs per call
   int last_per = 0;               // sub-batch size of the most recent run (for disb200_fetch)
@@ -498,10 +510,12 @@ struct DisHandle {
     launches = E.stats.launches;
     return rc;
   }
+  // the most recent device-pointer call, kept so that disb200_sync can rerun it without bands (DISB200_RETRY_NO_BANDS)
+  struct { int kind = 0; const uint8_t* a = nullptr; const uint8_t* b = nullptr; int n = 0; float* out = nullptr; } last_dev;
   bool warm_valid = false;   // E.initflow holds the previous pair's result (within one warm-started sequence)
 
   // device-side error flags, read after the work has been synchronised
-  int check_overflow() {
+  int check_device_flags() {
     for (int i = 0; i <= (int)extra.size(); ++i) {
       Engine& E = sub(i);
       int rc = E.check_sorb();
@@ -511,10 +525,74 @@ struct DisHandle {
   }
 };
 
+// clears DisHandle::lowres when the entry point returns, whatever the path
+struct LowresScope {
+  DisHandle* h;
+  LowresScope(DisHandle* h_, bool on) : h(h_) { if (h) h->lowres = on; }
+  ~LowresScope() { if (h) h->lowres = false; }
+};
+
+// The host-pointer pipeline shared by every host entry point.  Chunks are pipelined over three streams (upload, compute,
+// download) with two staging buffers, so the PCIe transfers of neighbouring chunks hide the compute and each other.
+// About eight chunks per call keep the un-overlapped head (first upload + first compute) small; chunks below 16 pairs
+// would starve the one-CTA-per-pair kernels.  `upload(i0, m, b, stream)` enqueues the host->device copies of pairs
+// i0 .. i0+m-1 into staging buffer b, `download` the device->host copies of their results; seq: dA[b] holds m + 1 frames.
+template <class Up, class Down>
+static int run_pipelined(DisHandle* h, int n, bool lowres, bool seq, Up upload, Down download) {
+  LowresScope ls(h, lowres);
+  CU(cudaSetDevice(h->e.device));
+  int rc = h->ensure_staging();
+  if (rc) return rc;
+  h->e.begin_run();
+  const int want = h->host_chunk > 0 ? h->host_chunk : std::max(16, (n + 7) / 8);
+  const int mb = std::max(1, std::min(h->max_batch, want));
+  int k = 0, total_launches = 0;
+  for (int i0 = 0; i0 < n; i0 += mb, ++k) {
+    const int m = std::min(mb, n - i0), b = k & 1;
+    // input buffer b is free once the compute of chunk k-2 is done
+    if (k >= 2) CU(cudaStreamWaitEvent(h->s_h2d, h->ev_comp[b], 0));
+    rc = upload(i0, m, b, h->s_h2d);
+    if (rc) return rc;
+    CU(cudaEventRecord(h->ev_h2d[b], h->s_h2d));
+    CU(cudaStreamWaitEvent(h->e.stream, h->ev_h2d[b], 0));
+    // output buffer b is free once the download of chunk k-2 is done
+    if (k >= 2) CU(cudaStreamWaitEvent(h->e.stream, h->ev_d2h[b], 0));
+    rc = h->enqueue(h->dA[b], seq ? nullptr : h->dB[b], m, h->dOut[b]);
+    if (rc) return rc;
+    total_launches += h->launches;
+    CU(cudaEventRecord(h->ev_comp[b], h->e.stream));
+    CU(cudaStreamWaitEvent(h->s_d2h, h->ev_comp[b], 0));
+    rc = download(i0, m, b, h->s_d2h);
+    if (rc) return rc;
+    CU(cudaEventRecord(h->ev_d2h[b], h->s_d2h));
+  }
+  CU(cudaStreamSynchronize(h->s_d2h));
+  CU(cudaStreamSynchronize(h->e.stream));
+  h->launches = total_launches;
+  h->e.collect_stage_times();
+  return h->check_device_flags();
+}
+
+// a host entry point whose banded SOR lost co-residency runs once more (the engine has switched bands off by then)
+template <class F>
+static int with_band_retry(F call) {
+  int rc = call();
+  if (rc == DISB200_RETRY_NO_BANDS) rc = call();
+  return rc == DISB200_RETRY_NO_BANDS ? fail(DISB200_ECUDA, "banded SOR timed out twice") : rc;
+}
+
 extern "C" {
 
 const char* disb200_last_error(void) { return g_err.c_str(); }
 const char* disb200_version(void) { return "disb200 0.1 (sm_100a)"; }
+
+int disb200_set_tuning(const DisTuning* t) {
+  if (!t) { g_tuning = DisTuning{0, 0, 0, 0, 0}; return DISB200_OK; }
+  if (t->streams < 0 || t->host_chunk < 0 || t->tv_schedule < 0 || t->tv_schedule > 3 || t->sorb_max < 0 || t->patch_map < 0 || t->patch_map > 1)
+    return fail(DISB200_EINVAL, "bad tuning value");
+  g_tuning = *t;
+  return DISB200_OK;
+}
 
 int disb200_device_count(void) {
   int n = 0;
@@ -567,11 +645,12 @@ int disb200_create(const DisParams* params, int w0, int h0, int max_batch, int d
   rc = disb200_padded_dims(w0, h0, params->sc_f, &W, &H, &h->padl, &h->padt);
   h->max_batch = max_batch;
   {
-    const char* ev = getenv("DISB200_STREAMS");
     // two sub-batches on two streams overlap the tail of each kernel with the head of the next one of the other
-    // half: +3 % at 1480 pairs (234.7 k -> 242.5 k pairs/s); more streams or smaller batches do not pay
-    int want = ev ? atoi(ev) : (max_batch >= 1184 ? 2 : 1);
+    // half: +3 % at 1480 pairs (234.7 k -> 242.5 k pairs/s); more streams or smaller batches do not pay, and
+    // staggering the sub-batches so that they run DIFFERENT kernels side by side loses 3-14 % (profiles/r02a_stagger_sweep.txt)
+    const int want = g_tuning.streams > 0 ? g_tuning.streams : (max_batch >= 1184 ? 2 : 1);
     h->nsub = std::max(1, std::min(std::min(want, 16), max_batch));
+    h->host_chunk = g_tuning.host_chunk;
   }
   h->cap = (max_batch + h->nsub - 1) / h->nsub;
   if (!rc) rc = h->e.init(*params, W, H, h->cap, device);
@@ -609,6 +688,7 @@ int disb200_run_batch_device(DisHandle* h, const uint8_t* dA, const uint8_t* dB,
   if (n < 1 || n > h->max_batch) return fail(DISB200_EINVAL, "n must be in 1..max_batch");
   CU(cudaSetDevice(h->e.device));
   h->e.begin_run();
+  h->last_dev.kind = 1; h->last_dev.a = dA; h->last_dev.b = dB; h->last_dev.n = n; h->last_dev.out = dOut;
   return h->enqueue(dA, dB, n, dOut);
 }
 
@@ -617,67 +697,41 @@ int disb200_sync(DisHandle* h) {
   CU(cudaSetDevice(h->e.device));
   CU(cudaStreamSynchronize(h->e.stream));
   h->e.collect_stage_times();
-  return h->check_overflow();
+  int rc = h->check_device_flags();
+  if (rc == DISB200_RETRY_NO_BANDS && h->last_dev.kind) {   // bands are off now: the same call again, general wavefront SOR
+    h->e.begin_run();
+    h->warm_valid = false;
+    rc = h->last_dev.kind == 1 ? h->enqueue(h->last_dev.a, h->last_dev.b, h->last_dev.n, h->last_dev.out)
+                               : h->enqueue_warm(h->last_dev.a, h->last_dev.n, h->last_dev.out);
+    if (rc) return rc;
+    CU(cudaStreamSynchronize(h->e.stream));
+    h->e.collect_stage_times();
+    rc = h->check_device_flags();
+  }
+  return rc == DISB200_RETRY_NO_BANDS ? fail(DISB200_ECUDA, "banded SOR timed out twice") : rc;
 }
-
-// clears DisHandle::lowres when the entry point returns, whatever the path
-struct LowresScope {
-  DisHandle* h;
-  LowresScope(DisHandle* h_, bool on) : h(h_) { if (h) h->lowres = on; }
-  ~LowresScope() { if (h) h->lowres = false; }
-};
 
 static int run_batch_host_impl(DisHandle* h, const uint8_t* A, const uint8_t* B, int n, float* out, bool lowres) {
   if (!h || !A || !B || !out) return fail(DISB200_EINVAL, "null argument");
   if (n < 1) return fail(DISB200_EINVAL, "n must be >= 1");
-  LowresScope ls(h, lowres);
   const size_t obytes = lowres ? h->low_bytes : h->out_bytes;
-  CU(cudaSetDevice(h->e.device));
-  int rc = h->ensure_staging();
-  if (rc) return rc;
-  h->e.begin_run();
-  // Chunks are pipelined over three streams (upload, compute, download) with two staging
-  // buffers, so the PCIe transfers of neighbouring chunks hide the compute and each other.
-  // About eight chunks per call keep the un-overlapped head (first upload + first compute)
-  // small; chunks below 16 pairs would starve the one-CTA-per-pair kernels.
-  int mb = h->max_batch;
-  {
-    static const char* ev = getenv("DISB200_HOST_CHUNK");
-    const int want = ev ? atoi(ev) : std::max(16, (n + 7) / 8);
-    mb = std::max(1, std::min(mb, want));
-  }
-  int k = 0;
-  int total_launches = 0;
-  for (int i0 = 0; i0 < n; i0 += mb, ++k) {
-    const int m = std::min(mb, n - i0), b = k & 1;
-    // input buffer b is free once the compute of chunk k-2 is done
-    if (k >= 2) CU(cudaStreamWaitEvent(h->s_h2d, h->ev_comp[b], 0));
-    CU(cudaMemcpyAsync(h->dA[b], A + (size_t)i0 * h->in_bytes, h->in_bytes * m, cudaMemcpyHostToDevice, h->s_h2d));
-    CU(cudaMemcpyAsync(h->dB[b], B + (size_t)i0 * h->in_bytes, h->in_bytes * m, cudaMemcpyHostToDevice, h->s_h2d));
-    CU(cudaEventRecord(h->ev_h2d[b], h->s_h2d));
-    CU(cudaStreamWaitEvent(h->e.stream, h->ev_h2d[b], 0));
-    // output buffer b is free once the download of chunk k-2 is done
-    if (k >= 2) CU(cudaStreamWaitEvent(h->e.stream, h->ev_d2h[b], 0));
-    rc = h->enqueue(h->dA[b], h->dB[b], m, h->dOut[b]);
-    if (rc) return rc;
-    total_launches += h->launches;
-    CU(cudaEventRecord(h->ev_comp[b], h->e.stream));
-    CU(cudaStreamWaitEvent(h->s_d2h, h->ev_comp[b], 0));
-    CU(cudaMemcpyAsync(out + (size_t)i0 * (obytes / sizeof(float)), h->dOut[b], obytes * m, cudaMemcpyDeviceToHost, h->s_d2h));
-    CU(cudaEventRecord(h->ev_d2h[b], h->s_d2h));
-  }
-  CU(cudaStreamSynchronize(h->s_d2h));
-  CU(cudaStreamSynchronize(h->e.stream));
-  h->launches = total_launches;
-  h->e.collect_stage_times();
-  return h->check_overflow();
+  return run_pipelined(h, n, lowres, false,
+    [&](int i0, int m, int b, cudaStream_t st) -> int {
+      CU(cudaMemcpyAsync(h->dA[b], A + (size_t)i0 * h->in_bytes, h->in_bytes * m, cudaMemcpyHostToDevice, st));
+      CU(cudaMemcpyAsync(h->dB[b], B + (size_t)i0 * h->in_bytes, h->in_bytes * m, cudaMemcpyHostToDevice, st));
+      return DISB200_OK;
+    },
+    [&](int i0, int m, int b, cudaStream_t st) -> int {
+      CU(cudaMemcpyAsync(out + (size_t)i0 * (obytes / sizeof(float)), h->dOut[b], obytes * m, cudaMemcpyDeviceToHost, st));
+      return DISB200_OK;
+    });
 }
 
 int disb200_run_batch_host(DisHandle* h, const uint8_t* A, const uint8_t* B, int n, float* out) {
-  return run_batch_host_impl(h, A, B, n, out, false);
+  return with_band_retry([&] { return run_batch_host_impl(h, A, B, n, out, false); });
 }
 int disb200_run_batch_host_lowres(DisHandle* h, const uint8_t* A, const uint8_t* B, int n, float* out_low) {
-  return run_batch_host_impl(h, A, B, n, out_low, true);
+  return with_band_retry([&] { return run_batch_host_impl(h, A, B, n, out_low, true); });
 }
 
 int disb200_lowres_dims(const DisHandle* h, int* w_l, int* h_l, int* nop) {
@@ -694,54 +748,31 @@ int disb200_run_sequence_device(DisHandle* h, const uint8_t* dFrames, int nframe
   if (nframes < 2 || nframes - 1 > h->max_batch) return fail(DISB200_EINVAL, "nframes - 1 must be in 1..max_batch");
   CU(cudaSetDevice(h->e.device));
   h->e.begin_run();
+  h->last_dev.kind = 1; h->last_dev.a = dFrames; h->last_dev.b = nullptr; h->last_dev.n = nframes - 1; h->last_dev.out = dOut;
   return h->enqueue(dFrames, nullptr, nframes - 1, dOut);
 }
 
 static int run_sequence_host_impl(DisHandle* h, const uint8_t* frames, int nframes, float* out, bool lowres) {
   if (!h || !frames || !out) return fail(DISB200_EINVAL, "null argument");
   if (nframes < 2) return fail(DISB200_EINVAL, "a sequence needs at least two frames");
-  LowresScope ls(h, lowres);
   const size_t obytes = lowres ? h->low_bytes : h->out_bytes;
-  CU(cudaSetDevice(h->e.device));
-  int rc = h->ensure_staging();
-  if (rc) return rc;
-  h->e.begin_run();
-  const int n = nframes - 1;
-  int mb = h->max_batch;
-  {
-    static const char* ev = getenv("DISB200_HOST_CHUNK");
-    const int want = ev ? atoi(ev) : std::max(16, (n + 7) / 8);
-    mb = std::max(1, std::min(mb, want));
-  }
-  int k = 0, total_launches = 0;
-  for (int i0 = 0; i0 < n; i0 += mb, ++k) {
-    const int m = std::min(mb, n - i0), b = k & 1;
-    if (k >= 2) CU(cudaStreamWaitEvent(h->s_h2d, h->ev_comp[b], 0));
-    // pairs i0 .. i0+m-1 need frames i0 .. i0+m (the last one is uploaded again with the next chunk)
-    CU(cudaMemcpyAsync(h->dA[b], frames + (size_t)i0 * h->in_bytes, h->in_bytes * (m + 1), cudaMemcpyHostToDevice, h->s_h2d));
-    CU(cudaEventRecord(h->ev_h2d[b], h->s_h2d));
-    CU(cudaStreamWaitEvent(h->e.stream, h->ev_h2d[b], 0));
-    if (k >= 2) CU(cudaStreamWaitEvent(h->e.stream, h->ev_d2h[b], 0));
-    rc = h->enqueue(h->dA[b], nullptr, m, h->dOut[b]);
-    if (rc) return rc;
-    total_launches += h->launches;
-    CU(cudaEventRecord(h->ev_comp[b], h->e.stream));
-    CU(cudaStreamWaitEvent(h->s_d2h, h->ev_comp[b], 0));
-    CU(cudaMemcpyAsync(out + (size_t)i0 * (obytes / sizeof(float)), h->dOut[b], obytes * m, cudaMemcpyDeviceToHost, h->s_d2h));
-    CU(cudaEventRecord(h->ev_d2h[b], h->s_d2h));
-  }
-  CU(cudaStreamSynchronize(h->s_d2h));
-  CU(cudaStreamSynchronize(h->e.stream));
-  h->launches = total_launches;
-  h->e.collect_stage_times();
-  return h->check_overflow();
+  return run_pipelined(h, nframes - 1, lowres, true,
+    [&](int i0, int m, int b, cudaStream_t st) -> int {
+      // pairs i0 .. i0+m-1 need frames i0 .. i0+m (the last one is uploaded again with the next chunk)
+      CU(cudaMemcpyAsync(h->dA[b], frames + (size_t)i0 * h->in_bytes, h->in_bytes * (m + 1), cudaMemcpyHostToDevice, st));
+      return DISB200_OK;
+    },
+    [&](int i0, int m, int b, cudaStream_t st) -> int {
+      CU(cudaMemcpyAsync(out + (size_t)i0 * (obytes / sizeof(float)), h->dOut[b], obytes * m, cudaMemcpyDeviceToHost, st));
+      return DISB200_OK;
+    });
 }
 
 int disb200_run_sequence_host(DisHandle* h, const uint8_t* frames, int nframes, float* out) {
-  return run_sequence_host_impl(h, frames, nframes, out, false);
+  return with_band_retry([&] { return run_sequence_host_impl(h, frames, nframes, out, false); });
 }
 int disb200_run_sequence_host_lowres(DisHandle* h, const uint8_t* frames, int nframes, float* out_low) {
-  return run_sequence_host_impl(h, frames, nframes, out_low, true);
+  return with_band_retry([&] { return run_sequence_host_impl(h, frames, nframes, out_low, true); });
 }
 
 int disb200_run_sequence_warm_device(DisHandle* h, const uint8_t* dFrames, int nframes, float* dOut) {
@@ -750,10 +781,11 @@ int disb200_run_sequence_warm_device(DisHandle* h, const uint8_t* dFrames, int n
   CU(cudaSetDevice(h->e.device));
   h->e.begin_run();
   h->warm_valid = false;
+  h->last_dev.kind = 2; h->last_dev.a = dFrames; h->last_dev.b = nullptr; h->last_dev.n = nframes - 1; h->last_dev.out = dOut;
   return h->enqueue_warm(dFrames, nframes - 1, dOut);
 }
 
-int disb200_run_sequence_warm_host(DisHandle* h, const uint8_t* frames, int nframes, float* out) {
+static int run_sequence_warm_host_impl(DisHandle* h, const uint8_t* frames, int nframes, float* out) {
   if (!h || !frames || !out) return fail(DISB200_EINVAL, "null argument");
   if (nframes < 2) return fail(DISB200_EINVAL, "a sequence needs at least two frames");
   CU(cudaSetDevice(h->e.device));
@@ -775,34 +807,34 @@ int disb200_run_sequence_warm_host(DisHandle* h, const uint8_t* frames, int nfra
   }
   h->launches = total_launches;
   h->e.collect_stage_times();
-  return h->check_overflow();
+  return h->check_device_flags();
 }
 
+int disb200_run_sequence_warm_host(DisHandle* h, const uint8_t* frames, int nframes, float* out) {
+  return with_band_retry([&] { return run_sequence_warm_host_impl(h, frames, nframes, out); });
+}
+
+// Pointer lists (the entry the four run_* CLIs and INTEGRATION.md use): same three-stream pipeline, one copy per image.
 int disb200_run_batch(DisHandle* h, const uint8_t* const* imgA, const uint8_t* const* imgB, int n, float* const* out) {
   if (!h || !imgA || !imgB || !out) return fail(DISB200_EINVAL, "null argument");
   if (n < 1) return fail(DISB200_EINVAL, "n must be >= 1");
-  CU(cudaSetDevice(h->e.device));
-  int rc = h->ensure_staging();
-  if (rc) return rc;
-  h->e.begin_run();
-  const int mb = h->max_batch;
-  int total_launches = 0;
-  for (int i0 = 0; i0 < n; i0 += mb) {
-    const int m = std::min(mb, n - i0);
-    for (int i = 0; i < m; ++i) {
-      CU(cudaMemcpyAsync(h->dA[0] + (size_t)i * h->in_bytes, imgA[i0 + i], h->in_bytes, cudaMemcpyHostToDevice, h->e.stream));
-      CU(cudaMemcpyAsync(h->dB[0] + (size_t)i * h->in_bytes, imgB[i0 + i], h->in_bytes, cudaMemcpyHostToDevice, h->e.stream));
-    }
-    rc = h->enqueue(h->dA[0], h->dB[0], m, h->dOut[0]);
-    if (rc) return rc;
-    for (int i = 0; i < m; ++i)
-      CU(cudaMemcpyAsync(out[i0 + i], h->dOut[0] + (size_t)i * (h->out_bytes / sizeof(float)), h->out_bytes, cudaMemcpyDeviceToHost, h->e.stream));
-    CU(cudaStreamSynchronize(h->e.stream));
-    total_launches += h->launches;
-  }
-  h->launches = total_launches;
-  h->e.collect_stage_times();
-  return h->check_overflow();
+  for (int i = 0; i < n; ++i)
+    if (!imgA[i] || !imgB[i] || !out[i]) return fail(DISB200_EINVAL, "null image / output pointer in the list");
+  return with_band_retry([&] {
+    return run_pipelined(h, n, false, false,
+      [&](int i0, int m, int b, cudaStream_t st) -> int {
+        for (int i = 0; i < m; ++i) {
+          CU(cudaMemcpyAsync(h->dA[b] + (size_t)i * h->in_bytes, imgA[i0 + i], h->in_bytes, cudaMemcpyHostToDevice, st));
+          CU(cudaMemcpyAsync(h->dB[b] + (size_t)i * h->in_bytes, imgB[i0 + i], h->in_bytes, cudaMemcpyHostToDevice, st));
+        }
+        return DISB200_OK;
+      },
+      [&](int i0, int m, int b, cudaStream_t st) -> int {
+        for (int i = 0; i < m; ++i)
+          CU(cudaMemcpyAsync(out[i0 + i], h->dOut[b] + (size_t)i * (h->out_bytes / sizeof(float)), h->out_bytes, cudaMemcpyDeviceToHost, st));
+        return DISB200_OK;
+      });
+  });
 }
 
 int disb200_timer_begin(DisHandle* h) {
@@ -878,6 +910,40 @@ int disb200_fetch(DisHandle* h, int kind, int which, int level, int pair, void* 
   return DISB200_OK;
 }
 
+// OFClass on an existing engine (pair slot 0): upload the padded pyramids, run the scale loop, download outflow
+static int ofclass_on_engine(Engine& e, const float* const* im_ao, const float* const* im_ao_dx, const float* const* im_ao_dy,
+                             const float* const* im_bo, const float* const* im_bo_dx, const float* const* im_bo_dy,
+                             float* outflow, const float* initflow) {
+  const DisParams& p = e.p;
+  const float* const* src[2][3] = {{im_ao, im_ao_dx, im_ao_dy}, {im_bo, im_bo_dx, im_bo_dy}};
+  for (int l = p.sc_l; l <= p.sc_f; ++l)
+    for (int f = 0; f < 2; ++f)
+      for (int a = 0; a < 3; ++a) {
+        if (!src[f][a][l]) return fail(DISB200_EINVAL, "pyramid level " + std::to_string(l) + " is null");
+        CU(cudaMemcpyAsync(e.pyr[f][a][l], src[f][a][l], e.geom[l].img_elems * sizeof(float), cudaMemcpyHostToDevice, e.stream));
+      }
+  if (initflow) {
+    const LevelGeom& gc = e.geom[p.sc_f];
+    CU(cudaMemcpyAsync(e.initflow, initflow, (size_t)(gc.w / 2) * (gc.h / 2) * e.nop * sizeof(float), cudaMemcpyHostToDevice, e.stream));
+  }
+  int rc = DISB200_OK;
+  for (int attempt = 0; attempt < 2; ++attempt) {   // second attempt only after a banded-SOR timeout (bands off by then)
+    e.seq = false;
+    e.pair0 = 0;
+    e.has_initflow = initflow != nullptr;
+    e.begin_run();
+    rc = e.run_levels(1);
+    e.has_initflow = false;
+    if (rc) return rc;
+    const LevelGeom& g = e.geom[p.sc_l];
+    CU(cudaMemcpyAsync(outflow, e.flow[0][p.sc_l], (size_t)g.w * g.h * e.nop * sizeof(float), cudaMemcpyDeviceToHost, e.stream));
+    CU(cudaStreamSynchronize(e.stream));
+    rc = e.check_sorb();
+    if (rc != DISB200_RETRY_NO_BANDS) break;
+  }
+  return rc == DISB200_RETRY_NO_BANDS ? fail(DISB200_ECUDA, "banded SOR timed out twice") : rc;
+}
+
 int disb200_ofclass(const DisParams* params, const float* const* im_ao, const float* const* im_ao_dx,
                     const float* const* im_ao_dy, const float* const* im_bo, const float* const* im_bo_dx,
                     const float* const* im_bo_dy, int W, int H, float* outflow, const float* initflow) {
@@ -888,30 +954,20 @@ int disb200_ofclass(const DisParams* params, const float* const* im_ao, const fl
   if (disb200_device_count() < 1) return fail(DISB200_ECUDA, "no CUDA device (this library has no CPU path)");
   Engine e;
   rc = e.init(*params, W, H, 1, 0);
-  const float* const* src[2][3] = {{im_ao, im_ao_dx, im_ao_dy}, {im_bo, im_bo_dx, im_bo_dy}};
-  for (int l = params->sc_l; !rc && l <= params->sc_f; ++l)
-    for (int f = 0; f < 2 && !rc; ++f)
-      for (int a = 0; a < 3 && !rc; ++a) {
-        if (!src[f][a][l]) { rc = fail(DISB200_EINVAL, "pyramid level " + std::to_string(l) + " is null"); break; }
-        if (cudaMemcpyAsync(e.pyr[f][a][l], src[f][a][l], e.geom[l].img_elems * sizeof(float), cudaMemcpyHostToDevice, e.stream) != cudaSuccess)
-          rc = fail(DISB200_ECUDA, "pyramid upload failed");
-      }
-  if (!rc && initflow) {
-    const LevelGeom& gc = e.geom[params->sc_f];
-    if (cudaMemcpyAsync(e.initflow, initflow, (size_t)(gc.w / 2) * (gc.h / 2) * e.nop * sizeof(float), cudaMemcpyHostToDevice, e.stream) != cudaSuccess)
-      rc = fail(DISB200_ECUDA, "initflow upload failed");
-    e.has_initflow = true;
-  }
-  if (!rc) { e.begin_run(); rc = e.run_levels(1); }
-  if (!rc) {
-    const LevelGeom& g = e.geom[params->sc_l];
-    cudaError_t ce = cudaMemcpyAsync(outflow, e.flow[0][params->sc_l], (size_t)g.w * g.h * e.nop * sizeof(float), cudaMemcpyDeviceToHost, e.stream);
-    if (ce == cudaSuccess) ce = cudaStreamSynchronize(e.stream);
-    if (ce != cudaSuccess) rc = fail(DISB200_ECUDA, std::string("ofclass: ") + cudaGetErrorString(ce));
-  }
-  if (!rc) rc = e.check_sorb();
+  if (!rc) rc = ofclass_on_engine(e, im_ao, im_ao_dx, im_ao_dy, im_bo, im_bo_dx, im_bo_dy, outflow, initflow);
   e.destroy();
   return rc;
+}
+
+int disb200_ofclass_handle(DisHandle* h, const float* const* im_ao, const float* const* im_ao_dx, const float* const* im_ao_dy,
+                           const float* const* im_bo, const float* const* im_bo_dx, const float* const* im_bo_dy,
+                           float* outflow, const float* initflow) {
+  if (!h || !im_ao || !im_ao_dx || !im_ao_dy || !im_bo || !im_bo_dx || !im_bo_dy || !outflow)
+    return fail(DISB200_EINVAL, "null argument");
+  CU(cudaSetDevice(h->e.device));
+  CU(cudaStreamSynchronize(h->e.stream));
+  h->last_dev.kind = 0;
+  return ofclass_on_engine(h->e, im_ao, im_ao_dx, im_ao_dy, im_bo, im_bo_dx, im_bo_dy, outflow, initflow);
 }
 
 int disb200_aggregate_dense(const DisParams* params, int w_l, int h_l, const float* p_iter_h, const float* pweight_h,
@@ -980,16 +1036,24 @@ int disb200_varref_level(const DisParams* params, const float* im_a, const float
     const size_t fb = (size_t)w_l * h_l * e.nop * sizeof(float);
     cudaError_t ce = cudaMemcpyAsync(e.pyr[0][0][0], im_a, g.img_elems * sizeof(float), cudaMemcpyHostToDevice, e.stream);
     if (ce == cudaSuccess) ce = cudaMemcpyAsync(e.pyr[1][0][0], im_b, g.img_elems * sizeof(float), cudaMemcpyHostToDevice, e.stream);
-    if (ce == cudaSuccess) ce = cudaMemcpyAsync(e.flow[0][0], flow, fb, cudaMemcpyHostToDevice, e.stream);
-    if (ce == cudaSuccess) {
+    float* d_in = nullptr;   // the flow is refined in place: keep the input for a rerun without bands
+    if (ce == cudaSuccess) ce = cudaMalloc(&d_in, fb);
+    if (ce == cudaSuccess) ce = cudaMemcpyAsync(d_in, flow, fb, cudaMemcpyHostToDevice, e.stream);
+    for (int attempt = 0; attempt < 2 && ce == cudaSuccess; ++attempt) {
+      ce = cudaMemcpyAsync(e.flow[0][0], d_in, fb, cudaMemcpyDeviceToDevice, e.stream);
+      if (ce != cudaSuccess) break;
       e.begin_run();
       launch_varref_level(e.pyr[0][0][0], e.pyr[1][0][0], e.flow[0][0], g, *params, camlr, e.vb, 1, e.stream, &e.stats);
       ce = cudaGetLastError();
+      if (ce == cudaSuccess) ce = cudaStreamSynchronize(e.stream);
+      if (ce != cudaSuccess) break;
+      rc = e.check_sorb();
+      if (rc != DISB200_RETRY_NO_BANDS) break;
     }
-    if (ce == cudaSuccess) ce = cudaMemcpyAsync(flow, e.flow[0][0], fb, cudaMemcpyDeviceToHost, e.stream);
-    if (ce == cudaSuccess) ce = cudaStreamSynchronize(e.stream);
+    if (ce == cudaSuccess && !rc) ce = cudaMemcpy(flow, e.flow[0][0], fb, cudaMemcpyDeviceToHost);
+    if (d_in) cudaFree(d_in);
     if (ce != cudaSuccess) rc = fail(DISB200_ECUDA, std::string("varref_level: ") + cudaGetErrorString(ce));
-    if (!rc) rc = e.check_sorb();
+    if (rc == DISB200_RETRY_NO_BANDS) rc = fail(DISB200_ECUDA, "banded SOR timed out twice");
   }
   e.destroy();
   return rc;

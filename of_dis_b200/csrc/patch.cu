@@ -626,11 +626,11 @@ static void launch_one(const PatchArgs& a, const LevelGeom& g, const OptConst& o
 bool launch_patch_search(const PatchArgs& a, const LevelGeom& g, const OptConst& o, int n, cudaStream_t s,
                          LaunchStats* st) {
   const int key = o.psz * 10 + o.noc;
-  // A/B switch: DISB200_PATCH_MAP=v selects the value-interleaved mapping (value n in lane n % G) wherever the block
-  // mapping is the default.  The 12 x 12 kernels (op3 / op4, compared with a tolerance anyway: different reduction
-  // order) also contract the interpolation and the two projections into FMAs: op4 588 -> 728 pairs/s.  8 x 8 BGR
-  // (op2 of run_*_RGB) keeps separate multiplies and adds: FMA gains 3 % of that kernel there.
-  static const bool blockmap = !(getenv("DISB200_PATCH_MAP") && getenv("DISB200_PATCH_MAP")[0] == 'v');
+  // A/B switch (DisTuning::patch_map = 1): the value-interleaved mapping (value n in lane n % G) wherever the block mapping
+  // is the default.  The 12 x 12 kernels (op3 / op4, compared with a tolerance anyway: different reduction order) also
+  // contract the interpolation and the two projections into FMAs: op4 588 -> 728 pairs/s.  8 x 8 BGR (op2 of run_*_RGB)
+  // keeps separate multiplies and adds: FMA gains 3 % of that kernel there.
+  const bool blockmap = o.patch_map != 1;
   switch (key) {
     case 41: launch_one<4, 1, 8>(a, g, o, n, s); break;
     case 81: launch_one<8, 1, 4>(a, g, o, n, s); break;

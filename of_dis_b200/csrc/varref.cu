@@ -17,8 +17,6 @@
 //   finish_kernel   flow += increment (with the DE sign clamp)         (refine_variational.cpp:208-227,301-323)
 // The planes read by the refinement are the unpadded interiors of the padded pyramid arrays,
 // addressed in place (the reference copies them out first, refine_variational.cpp:120-149).
-#include <cstdlib>
-
 #ifdef SORB_STATS
 #include <cstdio>
 #endif
@@ -865,11 +863,11 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
   }
   const bool pipelined = g.h * p.tv_solverit <= 512;
   const size_t fused_smem = (size_t)g.w * g.h * (NOP + 1) * sizeof(float);
-  const char* tv_path = getenv("DISB200_TV_PATH");   // experiment / test switch, see below
+  const int sched = vb.tv_schedule;   // 0 auto, 1 fused, 2 split, 3 split + general wavefront SOR (DisTuning)
   // "fused": one CTA per pair runs the whole level (best latency while every pair of the batch is resident,
   // i.e. up to two CTAs per SM); larger batches take the split path, whose one-warp-per-pair SOR keeps
-  // thousands of pairs resident.  DISB200_TV_PATH = fused | split | old (general wavefront SOR) overrides.
-  const bool want_split = p.sor_mode == DISB200_SOR_REDBLACK || (tv_path ? tv_path[0] != 'f' : n > 2 * 148);
+  // thousands of pairs resident.  DisTuning::tv_schedule overrides.
+  const bool want_split = p.sor_mode == DISB200_SOR_REDBLACK || (sched ? sched != 1 : n > 2 * 148);
   if (!want_split && pipelined && fused_smem <= 100 * 1024) {
     int threads = ((g.h * p.tv_solverit + 31) / 32) * 32;
     if (threads < 256) threads = 256;
@@ -884,7 +882,7 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
   cudaMemsetAsync(vb.du, 0, sizeof(float) * vb.plane_cap * NOP * n, st);
   // SOR launcher: one warp per pair (levels of up to 96 rows, up to 5 sweeps), else the general wavefront
   void (*sorw)(float*, const float4*, const float4*, Dims, float) = nullptr;
-  if (g.h <= 96 && !(tv_path && tv_path[0] == 'o')) {
+  if (g.h <= 96 && sched != 3) {
     const int nb = (g.h + 31) / 32;
     switch (p.tv_solverit) {
 #define DISB200_SORW_CASE(NS_) case NS_: sorw = nb == 3 ? sor_warp_kernel<OF, NS_, 3> : (nb == 2 ? sor_warp_kernel<OF, NS_, 2> : sor_warp_kernel<OF, NS_, 1>); break;
@@ -901,10 +899,10 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
   // (latency mode: measured 1.35-1.5x over the general wavefront while all bands of the batch are resident, 2 per
   //  SM — one 4K pair: 27.6 -> 19.8 ms of SOR; with more bands than that the general wavefront, one CTA per
   //  pair, has the better throughput: 64 4K pairs 33 vs 45 ms)
-  const char* sorb_max_env = getenv("DISB200_SORB_MAX");
-  const int sorb_max = sorb_max_env ? atoi(sorb_max_env) : 296;
-  if (!sorw && vb.sorb_ctl && g.h > 96 && g.w >= 8 && nbands <= 64 && p.tv_solverit <= 3 && n * nbands <= sorb_max &&
-      (size_t)nbands * g.w * sorb_rows * 4 <= vb.plane_cap * NOP && !(tv_path && tv_path[0] == 'o')) {
+  // vb.sorb_max = co-resident CTAs of the band kernel on this device (occupancy API, engine.cu) or less: bands spin on
+  // their neighbours, so every band of the launch must be resident - never more CTAs than that
+  if (!sorw && vb.sorb_ctl && g.h > 96 && g.w >= 8 && nbands <= 64 && p.tv_solverit <= 3 && n * nbands <= vb.sorb_max &&
+      (size_t)nbands * g.w * sorb_rows * 4 <= vb.plane_cap * NOP && sched != 3) {
     switch (p.tv_solverit) {
       case 1: sorb = sor_band_kernel<OF, 1>; sorb_smem = SorbCfg<1>::BYTES; break;
       case 2: sorb = sor_band_kernel<OF, 2>; sorb_smem = SorbCfg<2>::BYTES; break;
@@ -951,6 +949,22 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
 }
 
 }  // namespace
+
+int sor_band_resident_ctas(bool of, int solverit) {
+  int dev = 0, sms = 0, per_sm = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+  const void* fn = nullptr;
+  size_t smem = 0;
+  switch (solverit) {
+    case 1: fn = of ? (const void*)sor_band_kernel<true, 1> : (const void*)sor_band_kernel<false, 1>; smem = SorbCfg<1>::BYTES; break;
+    case 2: fn = of ? (const void*)sor_band_kernel<true, 2> : (const void*)sor_band_kernel<false, 2>; smem = SorbCfg<2>::BYTES; break;
+    case 3: fn = of ? (const void*)sor_band_kernel<true, 3> : (const void*)sor_band_kernel<false, 3>; smem = SorbCfg<3>::BYTES; break;
+    default: return 0;
+  }
+  if (cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) { cudaGetLastError(); return 0; }
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, 32, smem) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return per_sm * sms;
+}
 
 size_t varref_plane_count(int C, int nop) {
   // avg, Iz, Ix, Iy, Ixx, Ixy, Iyy, Ixz, Iyz (C each) + mask + s + du (nop) + coefficient pack (2 x float4) + spare (nop)

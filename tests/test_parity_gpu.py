@@ -155,10 +155,13 @@ def test_tv_paths_agree_bit_for_bit(gpu, port, monkeypatch, mode, ch, w0, h0, le
     if mode == 2:
         fl = -np.abs(fl)
     want = port.varref_level(q, a, b, wl, hl, level, 0, fl)
-    for path in ("fused", "split", "old"):
-        monkeypatch.setenv("DISB200_TV_PATH", path)
-        got = gpu.varref_level(to_dis(gpu, q), a, b, wl, hl, level, 0, fl)
-        assert np.array_equal(got, want), (path, float(np.abs(got - want).max()))
+    try:
+        for sched in (gpu.TV_FUSED, gpu.TV_SPLIT, gpu.TV_GENERAL):
+            gpu.set_tuning(tv_schedule=sched)
+            got = gpu.varref_level(to_dis(gpu, q), a, b, wl, hl, level, 0, fl)
+            assert np.array_equal(got, want), (sched, float(np.abs(got - want).max()))
+    finally:
+        gpu.set_tuning()
 
 
 @pytest.mark.parametrize("mode,ch", [(1, 1), (2, 1), (1, 3)])
@@ -208,6 +211,11 @@ def test_ofclass_initflow(gpu, port):
     want = port.ofclass(q, PA, PB, W, H, initflow=init)
     got = gpu.ofclass(to_dis(gpu, q), PA, PB, W, H, initflow=init)
     assert not np.array_equal(want, port.ofclass(q, PA, PB, W, H))
+    # the handle-based variant (no allocation per call) gives the same bits, with and without initflow, call after call
+    with gpu.Handle(to_dis(gpu, q), W, H, max_batch=1) as hd:
+        cold = hd.ofclass(PA, PB)
+        assert np.array_equal(hd.ofclass(PA, PB, initflow=init), got)
+        assert np.array_equal(hd.ofclass(PA, PB), cold) and np.array_equal(cold, gpu.ofclass(to_dis(gpu, q), PA, PB, W, H))
     m, mx = epe(got, want)
     assert m <= MEAN_TOL and mx <= 0.05
 
@@ -502,10 +510,12 @@ def test_band_sor_many_pairs_matches_general_wavefront(gpu, monkeypatch):
     pairs = [make_pair(h0, w0, seed=20 + s)[:2] for s in range(n)]
     A, B = np.stack([a for a, _ in pairs]), np.stack([b for _, b in pairs])
     p = gpu.operating_point(2, w0).copy(verbosity=0, sc_f=2, sc_l=0, usefbcon=1)
-    monkeypatch.setenv("DISB200_TV_PATH", "old")
-    with gpu.Handle(p, w0, h0, n) as hd:
-        want = hd.run_host(A, B)
-    monkeypatch.delenv("DISB200_TV_PATH")
+    try:
+        gpu.set_tuning(tv_schedule=gpu.TV_GENERAL)
+        with gpu.Handle(p, w0, h0, n) as hd:
+            want = hd.run_host(A, B)
+    finally:
+        gpu.set_tuning()
     with gpu.Handle(p, w0, h0, n) as hd:
         got1 = hd.run_host(A, B)
         got2 = hd.run_host(A[::-1].copy(), B[::-1].copy())[::-1]
