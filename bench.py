@@ -324,6 +324,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--streams", type=int, default=0, help="DisTuning.streams (0 = automatic); 1 for a serialised ncu launch list")
     ap.add_argument("--tv-schedule", type=int, default=0, help="DisTuning.tv_schedule (0 auto, 1 fused, 2 split, 3 general wavefront)")
+    ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--sor", default="lexicographic", choices=["lexicographic", "redblack"],
                     help="redblack: the throughput variant (a different iterate: ~0.04 px mean from the parity result, never the headline)")
@@ -578,10 +579,11 @@ def main():
                    "checksum": float(hLow[0].double().abs().mean())}
 
     cpu = parity = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        threads = os.cpu_count() or 1
-        cpu = CpuArm(q_orc, A, B).measure(args.cpu_seconds, threads)
-        parity = parity_report(p, A, B, G, hd)
+    if rank == 0 and world == 1:
+        if not args.no_cpu_baseline:
+            cpu = CpuArm(q_orc, A, B).measure(args.cpu_seconds, os.cpu_count() or 1)
+        if not args.no_parity:
+            parity = parity_report(p, A, B, G, hd)
 
     if rank == 0:
         line = {"metric": "frame_pairs_per_s", "value": value, "unit": "pairs/s", "mpix_per_s": value * w0 * h0 / 1e6,
