@@ -34,7 +34,7 @@ __device__ __forceinline__ int rgb_weight_offset(int r, int c, int ps, int c_lo,
 
 template <int C, int NOP>
 __global__ void densify_kernel(DensifyArgs a, LevelGeom g, OptConst o) {
-  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, pair = blockIdx.z;
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = a.y0 + blockIdx.y, pair = blockIdx.z;
   if (x >= g.w) return;
   // the patch window is lb..ub on both axes: ps = 2 (psz / 2) pixels, = psz for even sizes; the weight pointer runs
   // over exactly those ps x ps pixels (patchgrid.cpp:239-243), whatever novals is
@@ -234,7 +234,9 @@ void launch_densify(const DensifyArgs& a, const LevelGeom& g, const OptConst& o,
     bin_sort_kernel<<<dim3((ncell + 127) / 128, n), 128, 0, s>>>(a.cell_start, a.cell_end, a.cell_list, ncell, g.npatch);
     st->launches += 4;
   }
-  dim3 blk(128), grd((g.w + 127) / 128, g.h, n);
+  const int ny = a.ny < 0 ? g.h : a.ny;
+  if (ny <= 0) return;
+  dim3 blk(128), grd((g.w + 127) / 128, ny, n);
   if (o.noc == 1) {
     if (o.nop == 2) densify_kernel<1, 2><<<grd, blk, 0, s>>>(a, g, o);
     else densify_kernel<1, 1><<<grd, blk, 0, s>>>(a, g, o);

@@ -21,6 +21,12 @@ struct LevelGeom {
   int steps;
   float lb, ubw, ubh;
   size_t img_elems;  // tw*th*C
+  // Spatial tiling of one pair over several GPUs (tiled.cu): the part of the level this device works on.  Arrays are
+  // full-size and globally indexed on every device; a device computes patch rows gy0 .. gy0+ngy-1 (patches are owned by
+  // the row of their reference point) and pixel rows row0 .. row1-1 (plus the halo rows each stage needs, recomputed
+  // locally).  Untiled: the whole level.
+  int gy0, ngy;
+  int row0, row1;
 };
 
 // optparam (oflow.h:45-91, oflow.cpp:75-107)
@@ -96,6 +102,7 @@ struct DensifyArgs {
   int* cell_start;         // [n][ncell]  exclusive scan of cell_count
   int* cell_end;           // [n][ncell]  fill cursor, = start + count once filled
   int* cell_list;          // [n][npatch] patch indices grouped by cell, ascending inside a cell
+  int y0 = 0, ny = -1;     // pixel rows to produce (ny < 0: the whole level)
 };
 void launch_densify(const DensifyArgs& a, const LevelGeom& g, const OptConst& o, int n, cudaStream_t s,
                     LaunchStats* st);

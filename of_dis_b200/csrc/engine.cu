@@ -71,6 +71,8 @@ LevelGeom make_levelgeom(const DisParams& p, int W, int H, int level) {
   g.offh = (g.h - (g.noph - 1) * g.steps) / 2;
   g.npatch = g.nopw * g.noph;
   g.img_elems = (size_t)g.tw * g.th * p.channels;
+  g.gy0 = 0; g.ngy = g.noph;
+  g.row0 = 0; g.row1 = g.h;
   return g;
 }
 
@@ -283,6 +285,12 @@ struct Engine {
     }
   }
 
+  // `initflow` is indexed  floor(y / 2) * (w_c / 2) + floor(x / 2)  over the coarsest level's patch positions
+  // (patchgrid.cpp:199-201), which stays inside a (h_c / 2) x (w_c / 2) array only when w_c and h_c are even: the
+  // reference's (disabled) caller pads the frames to a multiple of 2^(sc_f + 1) for that reason (run_dense.cpp:301).
+  bool initflow_ok() const { return geom[p.sc_f].w % 2 == 0 && geom[p.sc_f].h % 2 == 0; }
+  static const char* initflow_why() { return "initflow / temporal warm start needs W and H divisible by 2^(sc_f + 1) (run_dense.cpp:301)"; }
+
   // Sequence mode (video): pair i = frames (i, i+1); the n + 1 frame pyramids live in the role-A arrays and the
   // second frame of pair i is simply the first frame of pair i + 1.
   bool seq = false;
@@ -483,6 +491,7 @@ struct DisHandle {
   // rescaled to that grid's units), pair 0 from zero like a cold start.
   int enqueue_warm(const uint8_t* frames, int n, float* out) {
     Engine& E = e;
+    if (!E.initflow_ok()) return fail(DISB200_EINVAL, E.initflow_why());
     if (n > cap) return fail(DISB200_EINVAL, "warm-started sequence chunk exceeds the engine capacity");
     E.stats.launches = 0;
     E.build_pyramids(frames, nullptr, n, w0, h0, padl, padt);
@@ -923,6 +932,7 @@ static int ofclass_on_engine(Engine& e, const float* const* im_ao, const float* 
         CU(cudaMemcpyAsync(e.pyr[f][a][l], src[f][a][l], e.geom[l].img_elems * sizeof(float), cudaMemcpyHostToDevice, e.stream));
       }
   if (initflow) {
+    if (!e.initflow_ok()) return fail(DISB200_EINVAL, Engine::initflow_why());
     const LevelGeom& gc = e.geom[p.sc_f];
     CU(cudaMemcpyAsync(e.initflow, initflow, (size_t)(gc.w / 2) * (gc.h / 2) * e.nop * sizeof(float), cudaMemcpyHostToDevice, e.stream));
   }

@@ -106,9 +106,13 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
 
   const int lane = threadIdx.x % G;
   const int blk_col = BLK ? (lane % LPR) * CW : 0, blk_row = BLK ? (lane / LPR) * RPL : 0;   // first float / row of the lane's block
+  // this device's patches: grid rows gy0 .. gy0+ngy-1 of every grid column (the whole grid unless the pair is tiled)
   const int ip_raw = blockIdx.x * (blockDim.x / G) + threadIdx.x / G;
-  const bool active = ip_raw < g.npatch;
-  const int ip = active ? ip_raw : g.npatch - 1;
+  const int nloc = g.nopw * g.ngy;
+  const bool active = ip_raw < nloc;
+  const int ipl = active ? ip_raw : nloc - 1;
+  const int gx = ipl / g.ngy, gy = g.gy0 + (ipl - gx * g.ngy);
+  const int ip = gx * g.noph + gy;   // patch index is column-major: ip = x * noph + y (patchgrid.cpp:64)
   const int pair = blockIdx.y;
   const int rowstride = g.tw * C;
 
@@ -117,8 +121,6 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
   const float* tdyp = a.tmpl_dy + (size_t)pair * g.img_elems;
   const float* qimg = a.tgt_img + (size_t)pair * g.img_elems;
 
-  // patch index is column-major: ip = x * noph + y (patchgrid.cpp:64)
-  const int gx = ip / g.noph, gy = ip - gx * g.noph;
   const float ptrx = (float)(gx * g.steps + g.offw);
   const float ptry = (float)(gy * g.steps + g.offh);
 
@@ -396,9 +398,13 @@ patch_search_generic_kernel(PatchArgs a, LevelGeom g, OptConst o) {
   const int C = o.noc, psz = o.psz, NV = o.novals;
   const int lbi = -(psz / 2), PS = 2 * (psz / 2), rowlen = PS * C, NE = PS * rowlen, NB4 = (NV / 4) * 4;
   const int lane = threadIdx.x % G;
+  // this device's patches: grid rows gy0 .. gy0+ngy-1 of every grid column (the whole grid unless the pair is tiled)
   const int ip_raw = blockIdx.x * (blockDim.x / G) + threadIdx.x / G;
-  const bool active = ip_raw < g.npatch;
-  const int ip = active ? ip_raw : g.npatch - 1;
+  const int nloc = g.nopw * g.ngy;
+  const bool active = ip_raw < nloc;
+  const int ipl = active ? ip_raw : nloc - 1;
+  const int gx = ipl / g.ngy, gy = g.gy0 + (ipl - gx * g.ngy);
+  const int ip = gx * g.noph + gy;   // patch index is column-major: ip = x * noph + y (patchgrid.cpp:64)
   const int pair = blockIdx.y;
   const int rowstride = g.tw * C;
   const float fnv = (float)NV;
@@ -407,7 +413,6 @@ patch_search_generic_kernel(PatchArgs a, LevelGeom g, OptConst o) {
   const float* tdxp = a.tmpl_dx + (size_t)pair * g.img_elems;
   const float* tdyp = a.tmpl_dy + (size_t)pair * g.img_elems;
   const float* qimg = a.tgt_img + (size_t)pair * g.img_elems;
-  const int gx = ip / g.noph, gy = ip - gx * g.noph;
   const float ptrx = (float)(gx * g.steps + g.offw), ptry = (float)(gy * g.steps + g.offh);
 
   int off[VPL];
@@ -608,7 +613,7 @@ patch_search_generic_kernel(PatchArgs a, LevelGeom g, OptConst o) {
 template <int VPL>
 static void launch_generic(const PatchArgs& a, const LevelGeom& g, const OptConst& o, int n, cudaStream_t s) {
   const int threads = 128, per_block = threads / 32;
-  dim3 grd((g.npatch + per_block - 1) / per_block, n);
+  dim3 grd((g.nopw * g.ngy + per_block - 1) / per_block, n);
   if (o.mode == DISB200_MODE_OF) patch_search_generic_kernel<true, VPL><<<grd, threads, 0, s>>>(a, g, o);
   else patch_search_generic_kernel<false, VPL><<<grd, threads, 0, s>>>(a, g, o);
 }
@@ -616,7 +621,7 @@ static void launch_generic(const PatchArgs& a, const LevelGeom& g, const OptCons
 template <int PSZ, int C, int G, int LPR = 0, bool FM = false>
 static void launch_one(const PatchArgs& a, const LevelGeom& g, const OptConst& o, int n, cudaStream_t s) {
   const int threads = 128, per_block = threads / G;
-  dim3 grd((g.npatch + per_block - 1) / per_block, n);
+  dim3 grd((g.nopw * g.ngy + per_block - 1) / per_block, n);
   if (o.mode == DISB200_MODE_OF)
     patch_search_kernel<PSZ, C, G, true, LPR, FM><<<grd, threads, 0, s>>>(a, g, o);
   else
@@ -625,6 +630,7 @@ static void launch_one(const PatchArgs& a, const LevelGeom& g, const OptConst& o
 
 bool launch_patch_search(const PatchArgs& a, const LevelGeom& g, const OptConst& o, int n, cudaStream_t s,
                          LaunchStats* st) {
+  if (g.ngy <= 0) return true;   // tiled pair: no patch row of this level belongs to this device
   const int key = o.psz * 10 + o.noc;
   // A/B switch (DisTuning::patch_map = 1): the value-interleaved mapping (value n in lane n % G) wherever the block mapping
   // is the default.  The 12 x 12 kernels (op3 / op4, compared with a tolerance anyway: different reduction order) also

@@ -68,13 +68,14 @@ __device__ __forceinline__ bool sorb_tag_ok(const float4 v, unsigned epoch) {
 }
 
 // xt: [pair][band][NS][w] entries written by the last row of a band; xb: [pair][band][NS-1 (min 1)][w] entries
-// written by its first row.  ctl[0]: ticket counter (monotonic, `ticket_base` = its value before this launch),
+// written by its first row.  xt_next_dev / xb_prev_dev: the same arrays on the device that runs band0+nb_local / band0-1
+// (spatial tiling of one pair, tiled.cu); equal to xt_all / xb_all when every band runs here.  ctl[0]: ticket counter (monotonic, `ticket_base` = its value before this launch),
 // ctl[1]: error flag.  nb = bands per pair = ceil(h / 32).
 template <bool OF, int NS>
 __global__ void __launch_bounds__(32)
 sor_band_kernel(float* __restrict__ du_all, const float4* __restrict__ cA_all, const float4* __restrict__ cB_all,
-                float4* xt_all, float4* xb_all, unsigned* ctl, unsigned ticket_base, unsigned epoch, Dims d, int nb,
-                float omega) {
+                float4* xt_all, float4* xb_all, float4* xt_next_dev, float4* xb_prev_dev, unsigned* ctl, unsigned ticket_base,
+                unsigned epoch, Dims d, int nb, int band0, int nb_local, float omega) {
   typedef SorbCfg<NS> Cfg;
   extern __shared__ float4 sorb_smem[];
   constexpr int NOP = OF ? 2 : 1, RPX = Cfg::RPX, DPX = Cfg::DPX, LEADPX = Cfg::LEADPX, SIG = Cfg::SIG, PF = Cfg::PF;
@@ -84,7 +85,8 @@ sor_band_kernel(float* __restrict__ du_all, const float4* __restrict__ cA_all, c
   unsigned tk = 0;
   if (lane == 0) tk = atomicAdd(ctl, 1u) - ticket_base;
   tk = __shfl_sync(0xffffffffu, tk, 0);
-  const int pair = (int)tk / nb, k = (int)tk - pair * nb;
+  // this launch runs bands band0 .. band0+nb_local-1 of every pair (all nb of them unless the pair is tiled over GPUs)
+  const int pair = (int)tk / nb_local, k = band0 + ((int)tk - pair * nb_local);
   const int w = d.w, h = d.h;
   const unsigned uw = (unsigned)w;
   float* du = du_all + (size_t)pair * d.plane * NOP;
@@ -95,8 +97,10 @@ sor_band_kernel(float* __restrict__ du_all, const float4* __restrict__ cA_all, c
   // exchange rows: read the previous band's last row / the next band's first row, write this band's own
   const float4* xt_in = xt_all + ((size_t)pair * nb + (has_prev ? k - 1 : 0)) * NS * w;
   const float4* xb_in = xb_all + ((size_t)pair * nb + (has_next ? k + 1 : k)) * NXB * w;
-  float4* xt_out = xt_all + ((size_t)pair * nb + k) * NS * w;
-  float4* xb_out = xb_all + ((size_t)pair * nb + k) * NXB * w;
+  // A band whose neighbour lives on another GPU publishes straight into THAT device's exchange array (same layout, peer
+  // memory over NVLink): plain 16-byte stores again, the tags make them self-validating, the consumer polls its own L2.
+  float4* xt_out = (k == band0 + nb_local - 1 ? xt_next_dev : xt_all) + ((size_t)pair * nb + k) * NS * w;
+  float4* xb_out = (k == band0 ? xb_prev_dev : xb_all) + ((size_t)pair * nb + k) * NXB * w;
   const float* du_next = du + (size_t)(has_next ? j0 + 32 : 0) * w * NOP;
   const float tagf = __uint_as_float(epoch);
 

@@ -43,15 +43,22 @@ struct Dims {
   int w, h, pad, tw;
   size_t img_elems;   // padded array elements per pair
   size_t plane;       // plane capacity per pair (elements)
+  int y0, y1;         // rows this launch produces (the whole level unless the pair is tiled over several GPUs)
 };
+__host__ __device__ inline Dims rows(Dims d, int y0, int y1) {   // the same level, rows [y0, y1) clamped to it
+  d.y0 = y0 < 0 ? 0 : y0;
+  d.y1 = y1 > d.h ? d.h : y1;
+  if (d.y1 < d.y0) d.y1 = d.y0;
+  return d;
+}
 
 // ---------------------------------------------------------------------------------------
 template <int C, bool OF>
 __global__ void warp_kernel(const float* __restrict__ im_a, const float* __restrict__ im_b,
                             const float* __restrict__ flow, Dims d, float* __restrict__ avg,
                             float* __restrict__ Iz, float* __restrict__ mask) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y, pair = blockIdx.z;
-  if (i >= d.w || j >= d.h) return;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = d.y0 + blockIdx.y * blockDim.y + threadIdx.y, pair = blockIdx.z;
+  if (i >= d.w || j >= d.y1) return;
   constexpr int NOP = OF ? 2 : 1;
   const size_t pix = (size_t)j * d.w + i;
   const float* fl = flow + ((size_t)pair * d.w * d.h + pix) * NOP;
@@ -90,8 +97,8 @@ __device__ __forceinline__ float conv5v(const float* p, int i, int j, int w, int
 __global__ void deriv1_kernel(const float* __restrict__ avg, const float* __restrict__ Iz, Dims d,
                               float* __restrict__ Ix, float* __restrict__ Iy, float* __restrict__ Ixz,
                               float* __restrict__ Iyz) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y;
-  if (i >= d.w || j >= d.h) return;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = d.y0 + blockIdx.y * blockDim.y + threadIdx.y;
+  if (i >= d.w || j >= d.y1) return;
   const size_t po = (size_t)blockIdx.z * d.plane, pix = (size_t)j * d.w + i;
   Ix[po + pix] = conv5h(avg + po, i, j, d.w);
   Iy[po + pix] = conv5v(avg + po, i, j, d.w, d.h);
@@ -100,8 +107,8 @@ __global__ void deriv1_kernel(const float* __restrict__ avg, const float* __rest
 }
 __global__ void deriv2_kernel(const float* __restrict__ Ix, const float* __restrict__ Iy, Dims d,
                               float* __restrict__ Ixx, float* __restrict__ Ixy, float* __restrict__ Iyy) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y;
-  if (i >= d.w || j >= d.h) return;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = d.y0 + blockIdx.y * blockDim.y + threadIdx.y;
+  if (i >= d.w || j >= d.y1) return;
   const size_t po = (size_t)blockIdx.z * d.plane, pix = (size_t)j * d.w + i;
   Ixx[po + pix] = conv5h(Ix + po, i, j, d.w);
   Ixy[po + pix] = conv5v(Ix + po, i, j, d.w, d.h);
@@ -411,8 +418,8 @@ template <int C, bool OF>
 __global__ void system_kernel(DerivPtrs D, const float* __restrict__ mask, const float* __restrict__ s,
                               const float* __restrict__ flow, const float* __restrict__ du, Dims d, float hd3,
                               float hg3, float4* __restrict__ cA, float4* __restrict__ cB) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y, pair = blockIdx.z;
-  if (i >= d.w || j >= d.h) return;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = d.y0 + blockIdx.y * blockDim.y + threadIdx.y, pair = blockIdx.z;
+  if (i >= d.w || j >= d.y1) return;
   constexpr int NOP = OF ? 2 : 1;
   const size_t po = (size_t)pair * d.plane;
   float4 a, b;
@@ -626,8 +633,8 @@ template <bool OF>
 __global__ void smooth_kernel4(const float* __restrict__ flow, const float* __restrict__ du, Dims d, int camlr,
                                float quarter_alpha, int first_iter, float* __restrict__ s) {
   constexpr int NOP = OF ? 2 : 1;
-  const int i0 = 4 * (blockIdx.x * blockDim.x + threadIdx.x), j = blockIdx.y * blockDim.y + threadIdx.y, pair = blockIdx.z;
-  if (i0 >= d.w || j >= d.h) return;
+  const int i0 = 4 * (blockIdx.x * blockDim.x + threadIdx.x), j = d.y0 + blockIdx.y * blockDim.y + threadIdx.y, pair = blockIdx.z;
+  if (i0 >= d.w || j >= d.y1) return;
   const float* fl = flow + (size_t)pair * d.w * d.h * NOP;
   const float* q = du + (size_t)pair * d.plane * NOP;
   const bool fi = first_iter != 0;
@@ -697,8 +704,8 @@ __global__ void smooth_kernel4(const float* __restrict__ flow, const float* __re
 template <bool OF>
 __global__ void smooth_kernel2(const float* __restrict__ flow, const float* __restrict__ du, Dims d, int camlr,
                                float quarter_alpha, int first_iter, float* __restrict__ s) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y, pair = blockIdx.z;
-  if (i >= d.w || j >= d.h) return;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = d.y0 + blockIdx.y * blockDim.y + threadIdx.y, pair = blockIdx.z;
+  if (i >= d.w || j >= d.y1) return;
   constexpr int NOP = OF ? 2 : 1;
   s[(size_t)pair * d.plane + (size_t)j * d.w + i] =
       smooth_pixel<OF>(flow + (size_t)pair * d.w * d.h * NOP, du + (size_t)pair * d.plane * NOP, i, j, d.w, d.h, camlr,
@@ -707,8 +714,8 @@ __global__ void smooth_kernel2(const float* __restrict__ flow, const float* __re
 
 template <bool OF>
 __global__ void finish_kernel(float* __restrict__ flow, const float* __restrict__ du, Dims d, int camlr) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = blockIdx.y * blockDim.y + threadIdx.y, pair = blockIdx.z;
-  if (i >= d.w || j >= d.h) return;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x, j = d.y0 + blockIdx.y * blockDim.y + threadIdx.y, pair = blockIdx.z;
+  if (i >= d.w || j >= d.y1) return;
   constexpr int NOP = OF ? 2 : 1;
   const size_t pix = (size_t)j * d.w + i;
   float u, v;
@@ -834,7 +841,7 @@ template <int C, bool OF>
 void varref_level_impl(const float* im_a, const float* im_b, float* flow, const LevelGeom& g, const DisParams& p,
                        int camlr, const VarRefBuffers& vb, int n, cudaStream_t st, LaunchStats* ls) {
   constexpr int NOP = OF ? 2 : 1;
-  Dims d{g.w, g.h, g.pad, g.tw, g.img_elems, vb.plane_cap};
+  Dims d{g.w, g.h, g.pad, g.tw, g.img_elems, vb.plane_cap, 0, g.h};
   const int n_inner = p.tv_innerit * (g.level + 1);                       // refine_variational.cpp:36
   if (n_inner <= 0) return;
   const float qa = 0.25f * p.tv_alpha, hg3 = p.tv_gamma * 0.5f / 3.0f, hd3 = p.tv_delta * 0.5f / 3.0f;
@@ -892,7 +899,7 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
     }
   }
   // tall levels: one warp per band of 32 rows, bands chained through tagged boundary rows (sor_band.cuh)
-  void (*sorb)(float*, const float4*, const float4*, float4*, float4*, unsigned*, unsigned, unsigned, Dims, int, float) = nullptr;
+  void (*sorb)(float*, const float4*, const float4*, float4*, float4*, float4*, float4*, unsigned*, unsigned, unsigned, Dims, int, int, int, float) = nullptr;
   const int nbands = (g.h + 31) / 32;
   const int sorb_rows = p.tv_solverit + (p.tv_solverit > 1 ? p.tv_solverit - 1 : 1);   // exchange rows per band
   size_t sorb_smem = 0;
@@ -938,7 +945,8 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
     else if (sorb) {
       const unsigned epoch = ++vb.sorb_host[0], base = vb.sorb_host[1];
       vb.sorb_host[1] += (unsigned)(n * nbands);
-      sorb<<<n * nbands, 32, sorb_smem, st>>>(vb.du, cA, cB, sorb_xt, sorb_xb, vb.sorb_ctl, base, epoch, d, nbands, p.tv_sor);
+      sorb<<<n * nbands, 32, sorb_smem, st>>>(vb.du, cA, cB, sorb_xt, sorb_xb, sorb_xt, sorb_xb, vb.sorb_ctl, base, epoch, d, nbands, 0,
+                                              nbands, p.tv_sor);
     }
     else sor_wavefront_kernel<OF><<<n, threads, 0, st>>>(vb.du, cA, cB, d, p.tv_solverit, p.tv_sor, pipelined ? 1 : 0);
     if (ls->mark) ls->mark(ls->ctx, 5, 0);

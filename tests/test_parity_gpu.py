@@ -561,7 +561,7 @@ def test_video_sequence_temporal_warm_start(gpu, port, mode, ch):
     Checked against the CPU oracle called pair by pair with the same initflow (box mean of its own previous level-sc_l
     flow, the INTER_AREA rule of the reference's disabled caller, run_dense.cpp:370-373)."""
     from of_dis_b200.synth import make_sequence
-    h0, w0 = 136, 240
+    h0, w0 = 128, 240          # padded dimensions divisible by 2^(sc_f + 1), as initflow requires (run_dense.cpp:301)
     fr = make_sequence(h0, w0, 5, seed=1)
     frames = np.stack(fr) if ch == 1 else np.stack([np.stack([f, np.roll(f, 3, 0), np.roll(f, 5, 1)], -1) for f in fr])
     q = base_orc(mode, ch, sc_f=3, sc_l=1)
@@ -588,6 +588,10 @@ def test_video_sequence_temporal_warm_start(gpu, port, mode, ch):
     assert not np.array_equal(got[1:], cold[1:])          # the others start somewhere else
     m, mx = epe(got, want)
     assert m <= MEAN_TOL and mx <= 0.05, "EPE(GPU,CPU) mean %g max %g" % (m, mx)
+    # odd coarsest level: initflow would be read out of bounds (by the reference too) - refused
+    with gpu.Handle(p, w0, 136, max_batch=3) as hd:
+        with pytest.raises(gpu.DisError):
+            hd.run_sequence_warm(np.zeros((3, 136, w0) + ((ch,) if ch > 1 else ()), np.uint8))
 
 
 @pytest.mark.parametrize("mode,ch,op,w0,h0", [(1, 1, 2, 1024, 436), (2, 1, 2, 640, 360), (1, 3, 2, 320, 136), (1, 1, 4, 150, 90)])
