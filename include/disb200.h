@@ -192,6 +192,26 @@ int disb200_aggregate_dense(const DisParams* params, int w_l, int h_l, const flo
                             const float* cg_p_iter, const float* cg_pt_iter, const float* cg_pweight, float* flow,
                             int* npatch_out);
 
+/* ---- One frame pair tiled spatially over several GPUs of one node (4K / 8K frames) ----
+ * One host thread, ndev devices with peer access (NVLink).  Small pyramid levels are computed redundantly on every
+ * device; levels taller than 96 rows are cut into strips of whole 32-row bands: patches are owned by the row of their
+ * reference point and all-gathered after the inverse search, densification and refinement run per strip with locally
+ * recomputed halo rows, the lexicographic SOR runs as one wavefront across all devices (boundary rows stored straight
+ * into the neighbour's memory), the refined flow rows are all-gathered for the next level, and every device upsamples and
+ * returns its rows of the result.  Bit-identical to disb200_run_batch* on one device.  `devices` may repeat a device id
+ * (several strips on one GPU; what the single-GPU tests use).  Same parameter domain as disb200_create. */
+typedef struct DisTiled DisTiled;
+int disb200_tiled_create(const DisParams* params, int w0, int h0, int ndev, const int* devices, DisTiled** out);
+int disb200_tiled_destroy(DisTiled* t);
+/* A, B: h0*w0*channels u8 on the host, out: h0*w0*nop f32 on the host; returns when out is complete. */
+int disb200_tiled_run_host(DisTiled* t, const uint8_t* A, const uint8_t* B, float* out);
+/* Latency of the device part: reruns the pipeline `reps` times on the frames the last run_host call left on the devices
+ * (results stay there) and reports the mean device time per pair, measured between two all-device barriers. */
+int disb200_tiled_time(DisTiled* t, int reps, float* ms_per_pair);
+/* How `level` is split: *tiled = 0 (replicated on every device) | 1; rows / patch_rows: ndev + 1 boundaries each. */
+int disb200_tiled_plan(const DisTiled* t, int level, int* tiled, int* rows, int* patch_rows);
+int disb200_tiled_last_launch_count(const DisTiled* t);
+
 /* File writers with the reference's framing (run_dense.cpp:17-82). */
 int disb200_save_flo(const char* path, const float* flow, int w, int h, int nc);
 int disb200_save_pfm(const char* path, const float* disp, int w, int h);

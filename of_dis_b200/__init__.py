@@ -277,6 +277,55 @@ class Handle:
         return r
 
 
+class Tiled:
+    """disb200_tiled_*: one frame pair split spatially over several GPUs (device ids may repeat: strips on one GPU)."""
+
+    def __init__(self, params: DisParams, w0: int, h0: int, devices):
+        self.p = params.copy()
+        self.w0, self.h0, self.devices = w0, h0, list(devices)
+        self.h = C.c_void_p()
+        dv = (C.c_int * len(self.devices))(*self.devices)
+        _check(lib().disb200_tiled_create(C.byref(self.p), w0, h0, len(self.devices), dv, C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            lib().disb200_tiled_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def run(self, A: np.ndarray, B: np.ndarray) -> np.ndarray:
+        A, B = np.ascontiguousarray(A, np.uint8), np.ascontiguousarray(B, np.uint8)
+        out = np.empty((self.h0, self.w0, self.p.nop), np.float32)
+        _check(lib().disb200_tiled_run_host(self.h, _ptr(A, C.c_uint8), _ptr(B, C.c_uint8), _ptr(out)))
+        return out
+
+    def time_ms(self, reps: int = 5) -> float:
+        ms = C.c_float()
+        _check(lib().disb200_tiled_time(self.h, reps, C.byref(ms)))
+        return ms.value
+
+    def plan(self, level: int):
+        """-> (tiled, row boundaries, patch-row boundaries) of one pyramid level"""
+        n = len(self.devices)
+        t, rows, gy = C.c_int(), (C.c_int * (n + 1))(), (C.c_int * (n + 1))()
+        _check(lib().disb200_tiled_plan(self.h, level, C.byref(t), rows, gy))
+        return bool(t.value), list(rows), list(gy)
+
+    def launch_count(self) -> int:
+        return lib().disb200_tiled_last_launch_count(self.h)
+
+
 class DisTuning(C.Structure):
     """Mirror of struct DisTuning (schedule selection; 0 = automatic)."""
     _fields_ = [("streams", C.c_int), ("host_chunk", C.c_int), ("tv_schedule", C.c_int), ("sorb_max", C.c_int), ("patch_map", C.c_int)]

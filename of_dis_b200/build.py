@@ -14,7 +14,7 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libdisb200.so")
-KERNEL_SOURCES = ["pyramid.cu", "patch.cu", "densify.cu", "varref.cu", "upsample.cu", "engine.cu", "flowio.cu"]
+KERNEL_SOURCES = ["pyramid.cu", "patch.cu", "densify.cu", "varref.cu", "upsample.cu", "engine.cu", "tiled.cu", "flowio.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-fmad=false",
     "-Xcompiler", "-fPIC", "-Xptxas", "-v",

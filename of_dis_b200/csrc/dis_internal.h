@@ -131,9 +131,30 @@ void launch_varref_level(const float* im_a, const float* im_b, float* flow, cons
                          int camlr, const VarRefBuffers& vb, int n, cudaStream_t s, LaunchStats* st);
 size_t varref_plane_count(int C, int nop);  // number of float planes VarRefBuffers needs
 
+// ---- stage 4, one pair whose rows are split over several devices (tiled.cu) ----------------------
+// Every device holds the full-size, globally indexed arrays of the level and works on the band-aligned strip
+// g.row0 .. g.row1-1; halo rows of the per-level planes are recomputed locally, the increment's halo rows travel between
+// neighbours after every SOR call, and the lexicographic SOR itself is the banded kernel (sor_band.cuh) whose tagged
+// boundary rows are stored straight into the neighbouring device's memory (NVLink P2P).
+struct TileDev {
+  int device;
+  cudaStream_t stream;
+  const float* im_a;        // padded level images of this direction's template / target frame, on this device
+  const float* im_b;
+  float* flow;              // [h][w][nop], full size; rows row0-4 .. row1+3 valid on entry, rows row0 .. row1-1 refined on exit
+  VarRefBuffers vb;
+  LevelGeom g;              // row0 / row1: this device's strip (multiples of 32 rows)
+  LaunchStats* st;
+  cudaEvent_t ev_sor, ev_halo;
+};
+bool varref_level_tileable(const LevelGeom& g, const DisParams& p, int ndev, size_t plane_cap, int nop);
+// returns a cudaError_t value (0 = ok)
+int launch_varref_level_tiled(TileDev* dv, int ndev, const DisParams& p, int camlr);
+
 // ---- stage 5: upsample + crop ---------------------------------------------------------------
+// out_y0 / out_ny: output rows to produce (out_ny < 0: all h0 of them); `out` always points at row 0 of pair 0
 void launch_upsample_crop(const float* flow, const LevelGeom& g, int nop, int sc_l, int padl, int padt, int w0,
-                          int h0, float* out, int n, cudaStream_t s, LaunchStats* st);
+                          int h0, float* out, int n, cudaStream_t s, LaunchStats* st, int out_y0 = 0, int out_ny = -1);
 
 // level-sc_l flow of one pair -> initflow of the next (box mean over k x k, times scale)
 void launch_warm_init(const float* flow, int wl, int nop, int k, float scale, int wi, int hi, float* init, cudaStream_t s,

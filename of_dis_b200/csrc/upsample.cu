@@ -8,6 +8,8 @@
 // output rows), the vertical pass is one lerp per output value, and stores are 128-bit.
 // The source coordinates are computed in fp32: (d + pad + 0.5) * 2^-sc_l - 0.5 is exact in
 // fp32 for a power-of-two scale, so it equals OpenCV's double computation rounded to float.
+#include <algorithm>
+
 #include "dis_internal.h"
 
 namespace disb200 {
@@ -30,8 +32,8 @@ __device__ __forceinline__ void src_coord(int d, int pad, float inv, int n, int&
 template <int NOP>
 __global__ void __launch_bounds__(128)
 upsample_crop_kernel(const float* __restrict__ flow, int wl, int hl, int sc_l, int padl, int padt, int w0, int h0,
-                     float* __restrict__ out) {
-  const int x0 = (blockIdx.x * blockDim.x + threadIdx.x) * UPS_COLS, y0 = blockIdx.y * UPS_ROWS, pair = blockIdx.z;
+                     float* __restrict__ out, int oy0, int oy1) {
+  const int x0 = (blockIdx.x * blockDim.x + threadIdx.x) * UPS_COLS, y0 = oy0 + blockIdx.y * UPS_ROWS, pair = blockIdx.z;
   if (x0 >= w0) return;
   const float* src = flow + (size_t)pair * wl * hl * NOP;
   const float inv = 1.0f / (float)(1 << sc_l), sc = (float)(1 << sc_l);
@@ -45,7 +47,7 @@ upsample_crop_kernel(const float* __restrict__ flow, int wl, int hl, int sc_l, i
 #pragma unroll 1
   for (int r = 0; r < UPS_ROWS; ++r) {
     const int y = y0 + r;
-    if (y >= h0) break;
+    if (y >= oy1) break;
     int sy0, sy1;
     float fy;
     src_coord(y, padt, inv, hl, sy0, sy1, fy);
@@ -84,8 +86,8 @@ upsample_crop_kernel(const float* __restrict__ flow, int wl, int hl, int sc_l, i
 // sc_l == 0: the flow is already at full resolution, only the crop remains (run_dense.cpp:408,415)
 template <int NOP>
 __global__ void crop_kernel(const float* __restrict__ flow, int wl, int hl, int padl, int padt, int w0, int h0,
-                            float* __restrict__ out) {
-  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = blockIdx.y, pair = blockIdx.z;
+                            float* __restrict__ out, int oy0) {
+  const int x = blockIdx.x * blockDim.x + threadIdx.x, y = oy0 + blockIdx.y, pair = blockIdx.z;
   if (x >= w0) return;
   const float* s = flow + ((size_t)pair * wl * hl + (size_t)(y + padt) * wl + (x + padl)) * NOP;
   float* d = out + ((size_t)pair * w0 * h0 + (size_t)y * w0 + x) * NOP;
@@ -125,16 +127,18 @@ void launch_warm_init(const float* flow, int wl, int nop, int k, float scale, in
 }
 
 void launch_upsample_crop(const float* flow, const LevelGeom& g, int nop, int sc_l, int padl, int padt, int w0,
-                          int h0, float* out, int n, cudaStream_t s, LaunchStats* st) {
+                          int h0, float* out, int n, cudaStream_t s, LaunchStats* st, int out_y0, int out_ny) {
+  const int oy0 = out_y0, oy1 = out_ny < 0 ? h0 : std::min(h0, out_y0 + out_ny), rows = oy1 - oy0;
+  if (rows <= 0) return;
   if (sc_l == 0) {
-    dim3 blk(128), grd((w0 + 127) / 128, h0, n);
-    if (nop == 2) crop_kernel<2><<<grd, blk, 0, s>>>(flow, g.w, g.h, padl, padt, w0, h0, out);
-    else crop_kernel<1><<<grd, blk, 0, s>>>(flow, g.w, g.h, padl, padt, w0, h0, out);
+    dim3 blk(128), grd((w0 + 127) / 128, rows, n);
+    if (nop == 2) crop_kernel<2><<<grd, blk, 0, s>>>(flow, g.w, g.h, padl, padt, w0, h0, out, oy0);
+    else crop_kernel<1><<<grd, blk, 0, s>>>(flow, g.w, g.h, padl, padt, w0, h0, out, oy0);
   } else {
     const int per_block = 128 * UPS_COLS;
-    dim3 blk(128), grd((w0 + per_block - 1) / per_block, (h0 + UPS_ROWS - 1) / UPS_ROWS, n);
-    if (nop == 2) upsample_crop_kernel<2><<<grd, blk, 0, s>>>(flow, g.w, g.h, sc_l, padl, padt, w0, h0, out);
-    else upsample_crop_kernel<1><<<grd, blk, 0, s>>>(flow, g.w, g.h, sc_l, padl, padt, w0, h0, out);
+    dim3 blk(128), grd((w0 + per_block - 1) / per_block, (rows + UPS_ROWS - 1) / UPS_ROWS, n);
+    if (nop == 2) upsample_crop_kernel<2><<<grd, blk, 0, s>>>(flow, g.w, g.h, sc_l, padl, padt, w0, h0, out, oy0, oy1);
+    else upsample_crop_kernel<1><<<grd, blk, 0, s>>>(flow, g.w, g.h, sc_l, padl, padt, w0, h0, out, oy0, oy1);
   }
   st->launches++;
 }

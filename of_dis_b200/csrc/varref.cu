@@ -20,6 +20,8 @@
 #ifdef SORB_STATS
 #include <cstdio>
 #endif
+#include <algorithm>
+
 #include "dis_internal.h"
 
 namespace disb200 {
@@ -956,7 +958,121 @@ void varref_level_impl(const float* im_a, const float* im_b, float* flow, const 
   ls->launches++;
 }
 
+// One level, ONE pair, rows split over ndev devices (see TileDev in dis_internal.h).  The same kernels as the one-device
+// path, each on its row range; per fixed-point iteration the only traffic between neighbours is two rows of the
+// increment (after the SOR) and, inside the SOR, the tagged boundary rows of the bands on either side of a cut.
+template <int C, bool OF>
+int varref_level_tiled_impl(TileDev* dv, int ndev, const DisParams& p, int camlr) {
+  constexpr int NOP = OF ? 2 : 1;
+  const LevelGeom& g0 = dv[0].g;
+  const int n_inner = p.tv_innerit * (g0.level + 1);                      // refine_variational.cpp:36
+  if (n_inner <= 0) return 0;
+  const float qa = 0.25f * p.tv_alpha, hg3 = p.tv_gamma * 0.5f / 3.0f, hd3 = p.tv_delta * 0.5f / 3.0f;
+  const int w = g0.w, h = g0.h, nbands = (h + 31) / 32, NS = p.tv_solverit;
+  const dim3 blk(32, 4);
+  auto grid = [&](const Dims& d, int cols, int planes) { return dim3((cols + 31) / 32, (d.y1 - d.y0 + 3) / 4, planes); };
+#define TILE_CK(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return (int)e__; } while (0)
+  void (*sorb)(float*, const float4*, const float4*, float4*, float4*, float4*, float4*, unsigned*, unsigned, unsigned, Dims, int, int, int, float) =
+      NS == 1 ? sor_band_kernel<OF, 1> : (NS == 2 ? sor_band_kernel<OF, 2> : sor_band_kernel<OF, 3>);
+  const size_t sorb_smem = NS == 1 ? SorbCfg<1>::BYTES : (NS == 2 ? SorbCfg<2>::BYTES : SorbCfg<3>::BYTES);
+  // ---- per level: warp, derivatives (halo rows recomputed locally), increment = 0 ----
+  for (int k = 0; k < ndev; ++k) {
+    TileDev& t = dv[k];
+    TILE_CK(cudaSetDevice(t.device));
+    const Dims d{w, h, t.g.pad, t.g.tw, t.g.img_elems, t.vb.plane_cap, 0, h};
+    const Dims dw = rows(d, t.g.row0 - 4, t.g.row1 + 4), d1 = rows(d, t.g.row0 - 2, t.g.row1 + 2), d2 = rows(d, t.g.row0, t.g.row1);
+    warp_kernel<C, OF><<<grid(dw, w, 1), blk, 0, t.stream>>>(t.im_a, t.im_b, t.flow, dw, t.vb.avg, t.vb.Iz, t.vb.mask);
+    deriv1_kernel<<<grid(d1, w, C), blk, 0, t.stream>>>(t.vb.avg, t.vb.Iz, d1, t.vb.Ix, t.vb.Iy, t.vb.Ixz, t.vb.Iyz);
+    deriv2_kernel<<<grid(d2, w, C), blk, 0, t.stream>>>(t.vb.Ix, t.vb.Iy, d2, t.vb.Ixx, t.vb.Ixy, t.vb.Iyy);
+    TILE_CK(cudaMemsetAsync(t.vb.du, 0, sizeof(float) * (size_t)w * h * NOP, t.stream));
+    TILE_CK(cudaFuncSetAttribute(sorb, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sorb_smem));
+    t.st->launches += 3;
+  }
+  const bool smooth4 = (w & 3) == 0 && (dv[0].vb.plane_cap & 3) == 0;
+  const size_t rowb = (size_t)w * NOP * sizeof(float);
+  for (int it = 0; it < n_inner; ++it) {
+    // ---- halo rows of the increment from the neighbours' last SOR, then diffusivity and linear system ----
+    for (int k = 0; k < ndev; ++k) {
+      TileDev& t = dv[k];
+      TILE_CK(cudaSetDevice(t.device));
+      if (it > 0) {
+        if (k + 1 < ndev) {   // rows row1, row1+1 belong to the next device
+          TILE_CK(cudaStreamWaitEvent(t.stream, dv[k + 1].ev_sor, 0));
+          const int r0 = t.g.row1, r1 = std::min(h, t.g.row1 + 2);
+          if (r1 > r0) TILE_CK(cudaMemcpyAsync(t.vb.du + (size_t)r0 * w * NOP, dv[k + 1].vb.du + (size_t)r0 * w * NOP, rowb * (r1 - r0), cudaMemcpyDefault, t.stream));
+        }
+        if (k > 0) {          // rows row0-2, row0-1 belong to the previous device
+          TILE_CK(cudaStreamWaitEvent(t.stream, dv[k - 1].ev_sor, 0));
+          const int r0 = std::max(0, t.g.row0 - 2), r1 = t.g.row0;
+          if (r1 > r0) TILE_CK(cudaMemcpyAsync(t.vb.du + (size_t)r0 * w * NOP, dv[k - 1].vb.du + (size_t)r0 * w * NOP, rowb * (r1 - r0), cudaMemcpyDefault, t.stream));
+        }
+        TILE_CK(cudaEventRecord(t.ev_halo, t.stream));
+      }
+      const Dims d{w, h, t.g.pad, t.g.tw, t.g.img_elems, t.vb.plane_cap, 0, h};
+      const Dims ds = rows(d, t.g.row0 - 1, t.g.row1 + 1), dy = rows(d, t.g.row0, t.g.row1);
+      if (smooth4) smooth_kernel4<OF><<<dim3((w / 4 + 31) / 32, (ds.y1 - ds.y0 + 3) / 4, 1), blk, 0, t.stream>>>(t.flow, t.vb.du, ds, camlr, qa, it == 0, t.vb.smooth);
+      else smooth_kernel2<OF><<<grid(ds, w, 1), blk, 0, t.stream>>>(t.flow, t.vb.du, ds, camlr, qa, it == 0, t.vb.smooth);
+      DerivPtrs D{t.vb.Ix, t.vb.Iy, t.vb.Iz, t.vb.Ixx, t.vb.Ixy, t.vb.Iyy, t.vb.Ixz, t.vb.Iyz};
+      system_kernel<C, OF><<<grid(dy, w, 1), blk, 0, t.stream>>>(D, t.vb.mask, t.vb.smooth, t.flow, t.vb.du, dy, hd3, hg3,
+                                                                 reinterpret_cast<float4*>(t.vb.coef), reinterpret_cast<float4*>(t.vb.inv));
+      t.st->launches += 2;
+    }
+    // ---- the SOR: every device runs its bands; a cut between two devices is a band boundary like any other, only that
+    //      the tagged rows crossing it are written into the neighbour's memory ----
+    // one launch epoch for all devices, ahead of every epoch any of their exchange arrays has seen
+    unsigned epoch = 0;
+    for (int k = 0; k < ndev; ++k) epoch = std::max(epoch, dv[k].vb.sorb_host[0]);
+    ++epoch;
+    for (int k = 0; k < ndev; ++k) dv[k].vb.sorb_host[0] = epoch;
+    for (int k = 0; k < ndev; ++k) {
+      TileDev& t = dv[k];
+      TILE_CK(cudaSetDevice(t.device));
+      if (it > 0) {   // the neighbours have copied their halo rows out of this device's increment before it is overwritten
+        if (k + 1 < ndev) TILE_CK(cudaStreamWaitEvent(t.stream, dv[k + 1].ev_halo, 0));
+        if (k > 0) TILE_CK(cudaStreamWaitEvent(t.stream, dv[k - 1].ev_halo, 0));
+      }
+      const Dims d{w, h, t.g.pad, t.g.tw, t.g.img_elems, t.vb.plane_cap, 0, h};
+      const int band0 = t.g.row0 / 32, nbl = (t.g.row1 - t.g.row0 + 31) / 32;
+      float4* xt = reinterpret_cast<float4*>(t.vb.rhs);
+      float4* xb = xt + (size_t)nbands * NS * w;
+      float4* xt_next = k + 1 < ndev ? reinterpret_cast<float4*>(dv[k + 1].vb.rhs) : xt;
+      float4* xb_prev = k > 0 ? reinterpret_cast<float4*>(dv[k - 1].vb.rhs) + (size_t)nbands * NS * w : xb;
+      const unsigned base = t.vb.sorb_host[1];
+      t.vb.sorb_host[1] += (unsigned)nbl;
+      if (nbl > 0)
+        sorb<<<nbl, 32, sorb_smem, t.stream>>>(t.vb.du, reinterpret_cast<const float4*>(t.vb.coef), reinterpret_cast<const float4*>(t.vb.inv), xt, xb,
+                                               xt_next, xb_prev, t.vb.sorb_ctl, base, epoch, d, nbands, band0, nbl, p.tv_sor);
+      TILE_CK(cudaEventRecord(t.ev_sor, t.stream));
+      t.st->launches++;
+    }
+  }
+  for (int k = 0; k < ndev; ++k) {
+    TileDev& t = dv[k];
+    TILE_CK(cudaSetDevice(t.device));
+    const Dims d{w, h, t.g.pad, t.g.tw, t.g.img_elems, t.vb.plane_cap, 0, h};
+    const Dims dy = rows(d, t.g.row0, t.g.row1);
+    finish_kernel<OF><<<grid(dy, w, 1), blk, 0, t.stream>>>(t.flow, t.vb.du, dy, camlr);
+    t.st->launches++;
+    TILE_CK(cudaGetLastError());
+  }
+#undef TILE_CK
+  return 0;
+}
+
 }  // namespace
+
+bool varref_level_tileable(const LevelGeom& g, const DisParams& p, int ndev, size_t plane_cap, int nop) {
+  const int nbands = (g.h + 31) / 32;
+  const int sorb_rows = p.tv_solverit + (p.tv_solverit > 1 ? p.tv_solverit - 1 : 1);
+  return ndev > 1 && p.sor_mode == DISB200_SOR_LEXICOGRAPHIC && g.h > 96 && g.w >= 8 && nbands <= 64 && nbands >= ndev &&
+         p.tv_solverit >= 1 && p.tv_solverit <= 3 && (size_t)nbands * g.w * sorb_rows * 4 <= plane_cap * nop;
+}
+
+int launch_varref_level_tiled(TileDev* dv, int ndev, const DisParams& p, int camlr) {
+  const bool of = p.mode == DISB200_MODE_OF;
+  if (p.channels == 1) return of ? varref_level_tiled_impl<1, true>(dv, ndev, p, camlr) : varref_level_tiled_impl<1, false>(dv, ndev, p, camlr);
+  return of ? varref_level_tiled_impl<3, true>(dv, ndev, p, camlr) : varref_level_tiled_impl<3, false>(dv, ndev, p, camlr);
+}
 
 int sor_band_resident_ctas(bool of, int solverit) {
   int dev = 0, sms = 0, per_sm = 0;

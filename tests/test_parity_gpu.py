@@ -684,3 +684,49 @@ def test_full_batch_properties(gpu, port):
         assert all(np.array_equal(out[s], out[i]) for i in range(s, nb, 2))
         assert epe(out[s], port.run_dense(to_orc(p), *pairs[s]))[0] <= MEAN_TOL
     assert np.array_equal(host, out[:6])
+
+
+# ------------------------------------------------------------------------------ one pair tiled over several strips / GPUs
+TILED_CASES = [
+    # id, mode, ch, w0, h0, overrides (sc_f = 2, sc_l = 0: levels of h0 / 4, h0 / 2, h0 rows)
+    ("of_int", 1, 1, 640, 512, {}),
+    ("of_int_fb_l1", 1, 1, 640, 512, dict(usefbcon=1, costfct=1)),
+    ("de_int", 2, 1, 640, 512, {}),
+    ("of_rgb_fb", 1, 3, 320, 416, dict(usefbcon=1)),
+    ("of_int_no_tv", 1, 1, 640, 512, dict(usetvref=0, usefbcon=1)),
+    ("of_int_psz12_2sweeps", 1, 1, 500, 390, dict(patchsz=12, patove=0.75, tv_solverit=2, tv_innerit=2)),
+    ("of_int_solverit1_odd", 1, 1, 333, 407, dict(tv_solverit=1)),
+]
+
+
+@pytest.mark.parametrize("cfg", TILED_CASES, ids=[c[0] for c in TILED_CASES])
+def test_tiled_strips_on_one_gpu_are_bit_identical(gpu, cfg):
+    """disb200_tiled_* with the same device named 2, 3 and 4 times: the strips, the patch ownership, the all-gathers, the
+    halo rows and the cross-strip banded SOR are the code path of real multi-GPU tiling (tests/test_tiled_multi_gpu.py
+    runs it on distinct devices); the result must equal the untiled handle bit for bit."""
+    _, mode, ch, w0, h0, kw = cfg
+    A, B, _ = make_pair(h0, w0, channels=ch, mode="OF" if mode == 1 else "DE", seed=6)
+    p = to_dis(gpu, base_orc(mode, ch, sc_f=2, sc_l=0, **kw))
+    with gpu.Handle(p, w0, h0, max_batch=1) as hd:
+        want = hd.run_host(A[None], B[None])[0]
+    for ndev in (2, 3, 4):
+        with gpu.Tiled(p, w0, h0, [0] * ndev) as td:
+            tiled0, rows0, gy0 = td.plan(0)
+            assert tiled0 and rows0[0] == 0
+            got = td.run(A, B)
+            got2 = td.run(A, B)              # exchange rows are reused under a new epoch
+            assert td.launch_count() > 0
+        assert all(r % 32 == 0 for r in rows0[:-1]) and rows0 == sorted(rows0) and gy0 == sorted(gy0)
+        assert np.array_equal(got, want), (ndev, float(np.abs(got - want).max()))
+        assert np.array_equal(got2, want)
+
+
+def test_tiled_small_frame_is_replicated(gpu):
+    """Levels of up to 96 rows are not cut: every device computes them; the result is the untiled one."""
+    A, B, _ = make_pair(120, 200, seed=2)
+    p = gpu.operating_point(2, 200).copy(verbosity=0)
+    with gpu.Handle(p, 200, 120, 1) as hd:
+        want = hd.run_host(A[None], B[None])[0]
+    with gpu.Tiled(p, 200, 120, [0, 0]) as td:
+        assert not any(td.plan(l)[0] for l in range(p.sc_l, p.sc_f + 1))
+        assert np.array_equal(td.run(A, B), want)
