@@ -13,6 +13,7 @@
 #include <mutex>
 #include <string>
 #include <thread>
+#include <new>
 #include <vector>
 
 #include "../../include/disb200.h"
@@ -75,6 +76,9 @@ int disb200_save_pfm(const char* path, const float* disp, int w, int h) {
   return ok ? DISB200_OK : DISB200_EIO;
 }
 
+// Largest image the readers accept (w * h), like disb200_read_flo: bounds every allocation derived from a file header.
+static const long long DISB200_MAX_PIXELS = 1ll << 31;
+
 static bool pnm_token(FILE* f, int* v) {
   int c = std::fgetc(f);
   while (c != EOF) {
@@ -83,9 +87,13 @@ static bool pnm_token(FILE* f, int* v) {
     else break;
   }
   if (c == EOF || c < '0' || c > '9') return false;
-  int x = 0;
-  while (c >= '0' && c <= '9') { x = x * 10 + (c - '0'); c = std::fgetc(f); }
-  *v = x;
+  long long x = 0;
+  while (c >= '0' && c <= '9') {
+    x = x * 10 + (c - '0');
+    if (x > (1ll << 30)) return false;   // no header field is that large: refuse instead of overflowing
+    c = std::fgetc(f);
+  }
+  *v = (int)x;
   return true;  // the single whitespace after the token has been consumed
 }
 
@@ -100,9 +108,11 @@ int disb200_read_pnm(const char* path, int want_channels, uint8_t** data, int* w
   int W = 0, H = 0, maxv = 0;
   bool ok = std::fread(magic, 1, 2, f) == 2 && magic[0] == 'P' && (magic[1] == '5' || magic[1] == '6');
   ok = ok && pnm_token(f, &W) && pnm_token(f, &H) && pnm_token(f, &maxv) && W > 0 && H > 0 && maxv == 255;
+  if (ok && (long long)W * H > DISB200_MAX_PIXELS) { std::fclose(f); return DISB200_EUNSUPPORTED; }
   if (!ok) { std::fclose(f); return DISB200_EIO; }
   const int sc = magic[1] == '6' ? 3 : 1;
-  std::vector<uint8_t> raw((size_t)W * H * sc);
+  std::vector<uint8_t> raw;
+  try { raw.resize((size_t)W * H * sc); } catch (const std::bad_alloc&) { std::fclose(f); return DISB200_ENOMEM; }
   ok = std::fread(raw.data(), 1, raw.size(), f) == raw.size();
   std::fclose(f);
   if (!ok) return DISB200_EIO;
@@ -164,6 +174,7 @@ int decode_png(const std::vector<uint8_t>& file, bool want_grey, std::vector<uin
     pos += 12 + (size_t)len;
   }
   if (ctype < 0 || w == 0 || h == 0 || w > (1u << 20) || h > (1u << 20) || idat.empty()) return DISB200_EIO;
+  if ((long long)w * h > DISB200_MAX_PIXELS) return DISB200_EUNSUPPORTED;
   if (interlace != 0) return DISB200_EUNSUPPORTED;     // Adam7
   int spp;                                              // samples per pixel in the file
   switch (ctype) {
@@ -185,12 +196,28 @@ int decode_png(const std::vector<uint8_t>& file, bool want_grey, std::vector<uin
     z_stream z;
     std::memset(&z, 0, sizeof(z));
     if (inflateInit(&z) != Z_OK) return DISB200_ENOMEM;
-    z.next_in = idat.data(); z.avail_in = (uInt)idat.size();
-    z.next_out = raw.data(); z.avail_out = (uInt)raw.size();
-    const int zr = inflate(&z, Z_FINISH);
-    const bool full = z.total_out == raw.size();
+    // zlib counts in 32-bit uInt: feed and drain in chunks so that buffers beyond 4 GiB are not truncated
+    size_t in_pos = 0, out_pos = 0;
+    int zr = Z_OK;
+    const size_t CH = (size_t)1 << 30;
+    while (zr == Z_OK || zr == Z_BUF_ERROR) {
+      if (z.avail_in == 0 && in_pos < idat.size()) {
+        const size_t n = std::min(CH, idat.size() - in_pos);
+        z.next_in = idat.data() + in_pos; z.avail_in = (uInt)n; in_pos += n;
+      }
+      if (z.avail_out == 0 && out_pos < raw.size()) {
+        const size_t n = std::min(CH, raw.size() - out_pos);
+        z.next_out = raw.data() + out_pos; z.avail_out = (uInt)n; out_pos += n;
+      }
+      const uInt in_before = z.avail_in, out_before = z.avail_out;
+      zr = inflate(&z, Z_NO_FLUSH);
+      if (zr == Z_BUF_ERROR && in_before == z.avail_in && out_before == z.avail_out &&
+          (in_pos >= idat.size() || z.avail_in > 0) && (out_pos >= raw.size() || z.avail_out > 0))
+        break;   // no progress possible: truncated stream or more data than the image holds
+    }
+    const bool full = (size_t)(out_pos - z.avail_out) == raw.size();
     inflateEnd(&z);
-    if ((zr != Z_STREAM_END && zr != Z_OK && zr != Z_BUF_ERROR) || !full) return DISB200_EIO;
+    if (zr != Z_STREAM_END || !full) return DISB200_EIO;
   }
   // undo the row filters in place (PNG spec 9.2)
   std::vector<uint8_t> zero(rowbytes, 0);
@@ -262,13 +289,19 @@ int disb200_read_image(const char* path, int want_channels, uint8_t** data, int*
   const long sz = std::ftell(f);
   std::fseek(f, 0, SEEK_SET);
   if (sz <= 0) { std::fclose(f); return DISB200_EIO; }
-  std::vector<uint8_t> file((size_t)sz);
-  const bool ok = std::fread(file.data(), 1, file.size(), f) == file.size();
-  std::fclose(f);
-  if (!ok) return DISB200_EIO;
-  std::vector<uint8_t> pix;
-  int W = 0, H = 0, ch = 0;
-  const int rc = decode_png(file, want_channels == 1, &pix, &W, &H, &ch);
+  std::vector<uint8_t> file, pix;
+  int W = 0, H = 0, ch = 0, rc = DISB200_OK;
+  try {   // no C++ exception may cross the C ABI: an image too large for this host is an error code
+    file.resize((size_t)sz);
+    const bool ok = std::fread(file.data(), 1, file.size(), f) == file.size();
+    std::fclose(f);
+    f = nullptr;
+    if (!ok) return DISB200_EIO;
+    rc = decode_png(file, want_channels == 1, &pix, &W, &H, &ch);
+  } catch (const std::bad_alloc&) {
+    if (f) std::fclose(f);
+    return DISB200_ENOMEM;
+  }
   if (rc) return rc;
   uint8_t* out = (uint8_t*)std::malloc((size_t)W * H * want_channels);
   if (!out) return DISB200_ENOMEM;

@@ -65,6 +65,26 @@ def test_interlaced_png_is_reported_unsupported(dis, tmp_path):
     assert e.value.code == 4          # DISB200_EUNSUPPORTED
 
 
+def test_readers_survive_hostile_headers(dis, tmp_path):
+    """The readers sit behind a C ABI and are fed user-listed files: a header that declares an absurd size, a truncated
+    stream or an endless digit run must come back as an error code, never as an allocation failure or a crash."""
+    import struct
+    import zlib
+    good = bytearray(open(os.path.join(PNG, "grey8.png"), "rb").read())
+    huge = bytearray(good)
+    huge[16:24] = struct.pack(">II", 1 << 20, 1 << 20)      # IHDR width, height: 2^40 pixels
+    huge[29:33] = struct.pack(">I", zlib.crc32(bytes(huge[12:29])) & 0xFFFFFFFF)
+    (tmp_path / "huge.png").write_bytes(bytes(huge))
+    i = bytes(good).index(b"IDAT")
+    (tmp_path / "cut.png").write_bytes(bytes(good[:i + 4 + 10]) + bytes(good[-12:]))   # IDAT body cut short (chunk length now lies)
+    (tmp_path / "digits.pgm").write_bytes(b"P5\n" + b"9" * 4000 + b" 4\n255\n" + bytes(16))
+    (tmp_path / "huge.pgm").write_bytes(b"P5\n1000000 1000000\n255\n" + bytes(16))
+    for name in ("huge.png", "cut.png", "digits.pgm", "huge.pgm"):
+        with pytest.raises(dis.DisError) as e:
+            dis.read_image(str(tmp_path / name), 1)
+        assert e.value.code in (3, 4, 5), (name, e.value.code)     # EIO / EUNSUPPORTED / ENOMEM
+
+
 def test_writer_pool_writes_the_same_bytes_as_the_synchronous_writers(dis, tmp_path):
     rng = np.random.default_rng(0)
     flows = [rng.standard_normal((17 + i, 31, 2)).astype(np.float32) for i in range(24)]
