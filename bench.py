@@ -324,6 +324,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--streams", type=int, default=0, help="DisTuning.streams (0 = automatic); 1 for a serialised ncu launch list")
     ap.add_argument("--tv-schedule", type=int, default=0, help="DisTuning.tv_schedule (0 auto, 1 fused, 2 split, 3 general wavefront)")
+    ap.add_argument("--antiphase", type=int, default=0, help="DisTuning.antiphase (two sub-batches, refinements in anti-phase)")
     ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--sor", default="lexicographic", choices=["lexicographic", "redblack"],
@@ -400,8 +401,8 @@ def main():
     dA, dB = hA.cuda(non_blocking=False), hB.cuda(non_blocking=False)
     dOut = torch.empty((nb, h0, w0, nop), dtype=torch.float32, device="cuda")
     torch.cuda.synchronize()
-    if args.streams or args.tv_schedule:
-        dis.set_tuning(streams=args.streams, tv_schedule=args.tv_schedule)
+    if args.streams or args.tv_schedule or args.antiphase:
+        dis.set_tuning(streams=args.streams, tv_schedule=args.tv_schedule, antiphase=args.antiphase)
     hd = dis.Handle(p, w0, h0, max_batch=nb, device=local_rank)
 
     def barrier():

@@ -80,6 +80,7 @@ typedef struct DisTuning {
                         general CTA wavefront SOR */
   int sorb_max;      /* largest n * bands the banded SOR takes (auto and upper bound: the number of co-resident CTAs) */
   int patch_map;     /* 1: value-interleaved lane mapping of the inverse search where the block mapping is the default */
+  int antiphase;     /* 1: with two sub-batches, run their refinements in anti-phase (one assembles while the other solves) */
 } DisTuning;
 int disb200_set_tuning(const DisTuning* t);   /* NULL restores the automatic choices */
 

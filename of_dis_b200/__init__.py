@@ -328,7 +328,8 @@ class Tiled:
 
 class DisTuning(C.Structure):
     """Mirror of struct DisTuning (schedule selection; 0 = automatic)."""
-    _fields_ = [("streams", C.c_int), ("host_chunk", C.c_int), ("tv_schedule", C.c_int), ("sorb_max", C.c_int), ("patch_map", C.c_int)]
+    _fields_ = [("streams", C.c_int), ("host_chunk", C.c_int), ("tv_schedule", C.c_int), ("sorb_max", C.c_int), ("patch_map", C.c_int),
+                ("antiphase", C.c_int)]
 
 
 TV_AUTO, TV_FUSED, TV_SPLIT, TV_GENERAL = 0, 1, 2, 3

@@ -130,6 +130,17 @@ int sor_band_resident_ctas(bool of, int solverit);
 void launch_varref_level(const float* im_a, const float* im_b, float* flow, const LevelGeom& g, const DisParams& p,
                          int camlr, const VarRefBuffers& vb, int n, cudaStream_t s, LaunchStats* st);
 size_t varref_plane_count(int C, int nop);  // number of float planes VarRefBuffers needs
+// The same for one or two sub-batches ("lanes") at once; two lanes run their fixed-point iterations in anti-phase (one
+// assembles its linear system while the other solves, varref.cu).  ev: an event of the lane's device (two-lane calls).
+struct TvLane {
+  const float* im_a; const float* im_b; float* flow;
+  VarRefBuffers vb;
+  int n;
+  cudaStream_t st;
+  LaunchStats* ls;
+  cudaEvent_t ev;
+};
+void launch_varref_level_lanes(TvLane* lanes, int nl, const LevelGeom& g, const DisParams& p, int camlr);
 
 // ---- stage 4, one pair whose rows are split over several devices (tiled.cu) ----------------------
 // Every device holds the full-size, globally indexed arrays of the level and works on the band-aligned strip

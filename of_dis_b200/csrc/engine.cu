@@ -15,7 +15,7 @@
 namespace disb200 {
 
 static thread_local std::string g_err;
-DisTuning g_tuning = {0, 0, 0, 0, 0};
+DisTuning g_tuning = {0, 0, 0, 0, 0, 0};
 int fail(int code, const std::string& msg) {
   g_err = msg;
   return code;
@@ -94,6 +94,8 @@ struct DisHandle {
   std::vector<Engine*> extra;     // sub-batch engines 1.. (own stream each), created on demand
   int nsub = 1;                   // sub-batches run concurrently on separate streams
   int host_chunk = 0;             // DisTuning::host_chunk
+  bool duo = false;               // two sub-batches enqueued side by side, refinements in anti-phase (DisTuning::streams == -2)
+  cudaEvent_t ev_lane[2] = {nullptr, nullptr};
   int cap = 0;                    // pairs per sub-batch engine
   int max_batch = 0;              // pairs per call
   int last_per = 0;               // sub-batch size of the most recent run (for disb200_fetch)
@@ -142,6 +144,8 @@ struct DisHandle {
       ev_join.push_back(ev);
     }
     if (!ev_fork) CU(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+    for (int k = 0; k < 2; ++k)
+      if (!ev_lane[k]) CU(cudaEventCreateWithFlags(&ev_lane[k], cudaEventDisableTiming));
     return DISB200_OK;
   }
 
@@ -154,6 +158,43 @@ struct DisHandle {
     } else {
       Engine::StageScope sc(&E, 4);
       launch_upsample_crop(E.flow[0][E.p.sc_l], E.geom[E.p.sc_l], E.nop, E.p.sc_l, padl, padt, w0, h0, out, n, E.stream, &E.stats);
+    }
+    return DISB200_OK;
+  }
+
+  // Two sub-batches through the scale loop together (same stages as enqueue_one, level by level for both): the host
+  // order lets the two refinements of a level interleave their iterations (launch_varref_level_lanes, anti-phase).
+  int enqueue_two(Engine& A, const uint8_t* aA, const uint8_t* bA, int nA, float* outA, Engine& B, const uint8_t* aB,
+                  const uint8_t* bB, int nB, float* outB) {
+    Engine* E[2] = {&A, &B};
+    const uint8_t* fa[2] = {aA, aB};
+    const uint8_t* fb[2] = {bA, bB};
+    const int nn[2] = {nA, nB};
+    float* out[2] = {outA, outB};
+    for (int k = 0; k < 2; ++k) E[k]->build_pyramids(fa[k], fb[k], nn[k], w0, h0, padl, padt);
+    const DisParams& p = A.p;
+    for (int sl = p.sc_f; sl >= p.sc_l; --sl) {
+      for (int k = 0; k < 2; ++k) {
+        int rc = E[k]->search_level(sl, nn[k], E[k]->geom[sl]);
+        if (rc) return rc;
+        E[k]->densify_level(sl, nn[k]);
+      }
+      if (p.usetvref) {
+        const int ndir = (p.usefbcon && sl > p.sc_l) ? 2 : 1;
+        for (int d = 0; d < ndir; ++d) {
+          TvLane lanes[2];
+          for (int k = 0; k < 2; ++k)
+            lanes[k] = TvLane{E[k]->P(d, 0, sl), E[k]->P(1 - d, 0, sl), E[k]->flow[d][sl], E[k]->vb, nn[k], E[k]->stream, &E[k]->stats, ev_lane[k]};
+          launch_varref_level_lanes(lanes, 2, A.geom[sl], p, d);
+        }
+      }
+    }
+    for (int k = 0; k < 2; ++k) {
+      if (lowres) {
+        CU(cudaMemcpyAsync(out[k], E[k]->flow[0][p.sc_l], low_bytes * nn[k], cudaMemcpyDeviceToDevice, E[k]->stream));
+      } else {
+        launch_upsample_crop(E[k]->flow[0][p.sc_l], E[k]->geom[p.sc_l], E[k]->nop, p.sc_l, padl, padt, w0, h0, out[k], nn[k], E[k]->stream, &E[k]->stats);
+      }
     }
     return DISB200_OK;
   }
@@ -175,6 +216,23 @@ struct DisHandle {
       CU(cudaEventRecord(ev_fork, e.stream));
     }
     const size_t out_elems = (lowres ? low_bytes : out_bytes) / sizeof(float);
+    if (S == 2 && !serial && duo && n - per > 0) {
+      // two sub-batches, enqueued level by level side by side so that their refinements can run in anti-phase
+      Engine& A = sub(0);
+      Engine& B = sub(1);
+      B.begin_run();
+      CU(cudaStreamWaitEvent(B.stream, ev_fork, 0));
+      A.stats.launches = B.stats.launches = 0;
+      int rc = enqueue_two(A, a, b, per, out, B, a + (size_t)per * in_bytes, b ? b + (size_t)per * in_bytes : nullptr, n - per,
+                           out + (size_t)per * out_elems);
+      if (rc) return rc;
+      launches = A.stats.launches + B.stats.launches;
+      CU(cudaEventRecord(ev_join[0], B.stream));
+      CU(cudaStreamWaitEvent(e.stream, ev_join[0], 0));
+      cudaError_t ce2 = cudaGetLastError();
+      if (ce2 != cudaSuccess) return fail(DISB200_ECUDA, std::string("kernel launch: ") + cudaGetErrorString(ce2));
+      return DISB200_OK;
+    }
     for (int i = 0; i < S; ++i) {
       const int lo = i * per, m = std::min(per, n - lo);
       if (m <= 0) break;
@@ -308,8 +366,8 @@ const char* disb200_last_error(void) { return g_err.c_str(); }
 const char* disb200_version(void) { return "disb200 0.1 (sm_100a)"; }
 
 int disb200_set_tuning(const DisTuning* t) {
-  if (!t) { g_tuning = DisTuning{0, 0, 0, 0, 0}; return DISB200_OK; }
-  if (t->streams < 0 || t->host_chunk < 0 || t->tv_schedule < 0 || t->tv_schedule > 3 || t->sorb_max < 0 || t->patch_map < 0 || t->patch_map > 1)
+  if (!t) { g_tuning = DisTuning{0, 0, 0, 0, 0, 0}; return DISB200_OK; }
+  if (t->streams < 0 || t->host_chunk < 0 || t->tv_schedule < 0 || t->tv_schedule > 3 || t->sorb_max < 0 || t->patch_map < 0 || t->patch_map > 1 || t->antiphase < 0 || t->antiphase > 1)
     return fail(DISB200_EINVAL, "bad tuning value");
   g_tuning = *t;
   return DISB200_OK;
@@ -372,6 +430,7 @@ int disb200_create(const DisParams* params, int w0, int h0, int max_batch, int d
     const int want = g_tuning.streams > 0 ? g_tuning.streams : (max_batch >= 1184 ? 2 : 1);
     h->nsub = std::max(1, std::min(std::min(want, 16), max_batch));
     h->host_chunk = g_tuning.host_chunk;
+    h->duo = g_tuning.antiphase == 1 && h->nsub == 2;
   }
   h->cap = (max_batch + h->nsub - 1) / h->nsub;
   if (!rc) rc = h->e.init(*params, W, H, h->cap, device);
@@ -397,6 +456,8 @@ int disb200_destroy(DisHandle* h) {
   if (h->t0) cudaEventDestroy(h->t0);
   if (h->t1) cudaEventDestroy(h->t1);
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+  for (int k = 0; k < 2; ++k)
+    if (h->ev_lane[k]) cudaEventDestroy(h->ev_lane[k]);
   for (cudaEvent_t ev : h->ev_join) cudaEventDestroy(ev);
   for (Engine* x : h->extra) { x->destroy(); delete x; }
   h->e.destroy();

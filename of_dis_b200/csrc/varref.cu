@@ -839,123 +839,184 @@ __global__ void tv_narrow_kernel(DerivPtrs D, const float* __restrict__ mask_all
   }
 }
 
+// One level of refinement for one or two "lanes" (sub-batches of a batch, each with its own stream and planes).
+// Two lanes run in ANTI-PHASE: the fixed-point iteration alternates a throughput-bound part (diffusivity + system
+// assembly: full-grid streaming kernels) and a latency-bound part (the one-warp-per-pair SOR: six warps per SM waiting on
+// their own dependency chains), so lane 1 assembles while lane 0 solves and vice versa, kept in step by two events per
+// iteration.  The assembly kernels ask for the SOR's shared-memory carve-out so that both can be resident on one SM.
 template <int C, bool OF>
-void varref_level_impl(const float* im_a, const float* im_b, float* flow, const LevelGeom& g, const DisParams& p,
-                       int camlr, const VarRefBuffers& vb, int n, cudaStream_t st, LaunchStats* ls) {
+void varref_level_lanes(TvLane* lanes, int nl, const LevelGeom& g, const DisParams& p, int camlr) {
   constexpr int NOP = OF ? 2 : 1;
-  Dims d{g.w, g.h, g.pad, g.tw, g.img_elems, vb.plane_cap, 0, g.h};
   const int n_inner = p.tv_innerit * (g.level + 1);                       // refine_variational.cpp:36
   if (n_inner <= 0) return;
   const float qa = 0.25f * p.tv_alpha, hg3 = p.tv_gamma * 0.5f / 3.0f, hd3 = p.tv_delta * 0.5f / 3.0f;
   // 32 x 4 pixel tiles: every warp of a block is a full row segment at all level widths
-  dim3 blk(32, 4), grd((g.w + 31) / 32, (g.h + 3) / 4, n), grdc((g.w + 31) / 32, (g.h + 3) / 4, n * C);
-  warp_kernel<C, OF><<<grd, blk, 0, st>>>(im_a, im_b, flow, d, vb.avg, vb.Iz, vb.mask);
-  deriv1_kernel<<<grdc, blk, 0, st>>>(vb.avg, vb.Iz, d, vb.Ix, vb.Iy, vb.Ixz, vb.Iyz);
-  deriv2_kernel<<<grdc, blk, 0, st>>>(vb.Ix, vb.Iy, d, vb.Ixx, vb.Ixy, vb.Iyy);
-  ls->launches += 3;
-  DerivPtrs D{vb.Ix, vb.Iy, vb.Iz, vb.Ixx, vb.Ixy, vb.Iyy, vb.Ixz, vb.Iyz};
-  float4* cA = reinterpret_cast<float4*>(vb.coef);
-  float4* cB = reinterpret_cast<float4*>(vb.inv);
-  if (g.w < 2) {   // one-pixel-wide level: the reference's point-wise fallback (solver.c:86-89)
-    tv_narrow_kernel<C, OF><<<(n + 31) / 32, 32, 0, st>>>(D, vb.mask, flow, vb.du, vb.smooth, d, camlr, qa, hd3, hg3, n_inner,
-                                                          p.tv_solverit, p.tv_sor, cA, cB, n);
-    ls->launches++;
-    return;
-  }
-  if (p.tv_solverit < 1) {
-    // sor_coupled / sor_coupled_slow_but_readable_DE with zero sweeps leave the increment at 0: the level's result is
-    // uu = wx + 0, which for depth still applies the sign clamp (refine_variational.cpp:301-323)
-    cudaMemsetAsync(vb.du, 0, sizeof(float) * vb.plane_cap * NOP * n, st);
-    finish_kernel<OF><<<grd, blk, 0, st>>>(flow, vb.du, d, camlr);
-    ls->launches++;
-    return;
-  }
+  const dim3 blk(32, 4);
   const bool pipelined = g.h * p.tv_solverit <= 512;
   const size_t fused_smem = (size_t)g.w * g.h * (NOP + 1) * sizeof(float);
-  const int sched = vb.tv_schedule;   // 0 auto, 1 fused, 2 split, 3 split + general wavefront SOR (DisTuning)
-  // "fused": one CTA per pair runs the whole level (best latency while every pair of the batch is resident,
-  // i.e. up to two CTAs per SM); larger batches take the split path, whose one-warp-per-pair SOR keeps
-  // thousands of pairs resident.  DisTuning::tv_schedule overrides.
-  const bool want_split = p.sor_mode == DISB200_SOR_REDBLACK || (sched ? sched != 1 : n > 2 * 148);
-  if (!want_split && pipelined && fused_smem <= 100 * 1024) {
-    int threads = ((g.h * p.tv_solverit + 31) / 32) * 32;
-    if (threads < 256) threads = 256;
-    cudaFuncSetAttribute(tv_fused_kernel<C, OF>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
-    if (ls->mark) ls->mark(ls->ctx, 5, 1);
-    tv_fused_kernel<C, OF><<<n, threads, fused_smem, st>>>(D, vb.mask, flow, d, camlr, qa, hd3, hg3, n_inner,
-                                                           p.tv_solverit, p.tv_sor, cA, cB);
-    if (ls->mark) ls->mark(ls->ctx, 5, 0);
-    ls->launches++;
-    return;
-  }
-  cudaMemsetAsync(vb.du, 0, sizeof(float) * vb.plane_cap * NOP * n, st);
-  // SOR launcher: one warp per pair (levels of up to 96 rows, up to 5 sweeps), else the general wavefront
-  void (*sorw)(float*, const float4*, const float4*, Dims, float) = nullptr;
-  if (g.h <= 96 && sched != 3) {
-    const int nb = (g.h + 31) / 32;
-    switch (p.tv_solverit) {
-#define DISB200_SORW_CASE(NS_) case NS_: sorw = nb == 3 ? sor_warp_kernel<OF, NS_, 3> : (nb == 2 ? sor_warp_kernel<OF, NS_, 2> : sor_warp_kernel<OF, NS_, 1>); break;
-      DISB200_SORW_CASE(1) DISB200_SORW_CASE(2) DISB200_SORW_CASE(3) DISB200_SORW_CASE(4) DISB200_SORW_CASE(5)
-#undef DISB200_SORW_CASE
-      default: break;
-    }
-  }
-  // tall levels: one warp per band of 32 rows, bands chained through tagged boundary rows (sor_band.cuh)
-  void (*sorb)(float*, const float4*, const float4*, float4*, float4*, float4*, float4*, unsigned*, unsigned, unsigned, Dims, int, int, int, float) = nullptr;
   const int nbands = (g.h + 31) / 32;
   const int sorb_rows = p.tv_solverit + (p.tv_solverit > 1 ? p.tv_solverit - 1 : 1);   // exchange rows per band
-  size_t sorb_smem = 0;
-  // (latency mode: measured 1.35-1.5x over the general wavefront while all bands of the batch are resident, 2 per
-  //  SM — one 4K pair: 27.6 -> 19.8 ms of SOR; with more bands than that the general wavefront, one CTA per
-  //  pair, has the better throughput: 64 4K pairs 33 vs 45 ms)
-  // vb.sorb_max = co-resident CTAs of the band kernel on this device (occupancy API, engine.cu) or less: bands spin on
-  // their neighbours, so every band of the launch must be resident - never more CTAs than that
-  if (!sorw && vb.sorb_ctl && g.h > 96 && g.w >= 8 && nbands <= 64 && p.tv_solverit <= 3 && n * nbands <= vb.sorb_max &&
-      (size_t)nbands * g.w * sorb_rows * 4 <= vb.plane_cap * NOP && sched != 3) {
-    switch (p.tv_solverit) {
-      case 1: sorb = sor_band_kernel<OF, 1>; sorb_smem = SorbCfg<1>::BYTES; break;
-      case 2: sorb = sor_band_kernel<OF, 2>; sorb_smem = SorbCfg<2>::BYTES; break;
-      default: sorb = sor_band_kernel<OF, 3>; sorb_smem = SorbCfg<3>::BYTES; break;
-    }
-    cudaFuncSetAttribute(sorb, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sorb_smem);
-  }
-  float4* sorb_xt = reinterpret_cast<float4*>(vb.rhs);
-  float4* sorb_xb = sorb_xt + (size_t)n * nbands * p.tv_solverit * g.w;
   const size_t sorw_smem = sorw_smem_bytes(g.h, p.tv_solverit);
-  if (sorw) cudaFuncSetAttribute(sorw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sorw_smem);
   int threads = pipelined ? g.h * p.tv_solverit : (g.h < 512 ? g.h : 512);
   threads = ((threads + 31) / 32) * 32;
-  // four pixels per thread need 16-byte aligned rows in every plane: w % 4 == 0 (plane_cap is a multiple of 4)
-  const bool smooth4 = (g.w & 3) == 0 && (vb.plane_cap & 3) == 0;
-  const dim3 grd4((g.w / 4 + 31) / 32, (g.h + 3) / 4, n);
-  for (int it = 0; it < n_inner; ++it) {
+
+  struct Plan {
+    Dims d;
+    dim3 grd, grdc, grd4;
+    DerivPtrs D;
+    float4 *cA, *cB;
+    bool done = false, smooth4 = false;
+    void (*sorw)(float*, const float4*, const float4*, Dims, float) = nullptr;
+    void (*sorb)(float*, const float4*, const float4*, float4*, float4*, float4*, float4*, unsigned*, unsigned, unsigned, Dims, int, int, int, float) = nullptr;
+    size_t sorb_smem = 0;
+  } pl[2];
+
+  // ---- per level: warp, derivatives; levels that one kernel handles whole (narrow, zero sweeps, fused) end here ----
+  for (int l = 0; l < nl; ++l) {
+    TvLane& L = lanes[l];
+    Plan& P = pl[l];
+    const VarRefBuffers& vb = L.vb;
+    const int n = L.n;
+    cudaStream_t st = L.st;
+    LaunchStats* ls = L.ls;
+    P.d = Dims{g.w, g.h, g.pad, g.tw, g.img_elems, vb.plane_cap, 0, g.h};
+    P.grd = dim3((g.w + 31) / 32, (g.h + 3) / 4, n);
+    P.grdc = dim3((g.w + 31) / 32, (g.h + 3) / 4, n * C);
+    P.grd4 = dim3((g.w / 4 + 31) / 32, (g.h + 3) / 4, n);
+    warp_kernel<C, OF><<<P.grd, blk, 0, st>>>(L.im_a, L.im_b, L.flow, P.d, vb.avg, vb.Iz, vb.mask);
+    deriv1_kernel<<<P.grdc, blk, 0, st>>>(vb.avg, vb.Iz, P.d, vb.Ix, vb.Iy, vb.Ixz, vb.Iyz);
+    deriv2_kernel<<<P.grdc, blk, 0, st>>>(vb.Ix, vb.Iy, P.d, vb.Ixx, vb.Ixy, vb.Iyy);
+    ls->launches += 3;
+    P.D = DerivPtrs{vb.Ix, vb.Iy, vb.Iz, vb.Ixx, vb.Ixy, vb.Iyy, vb.Ixz, vb.Iyz};
+    P.cA = reinterpret_cast<float4*>(vb.coef);
+    P.cB = reinterpret_cast<float4*>(vb.inv);
+    if (g.w < 2) {   // one-pixel-wide level: the reference's point-wise fallback (solver.c:86-89)
+      tv_narrow_kernel<C, OF><<<(n + 31) / 32, 32, 0, st>>>(P.D, vb.mask, L.flow, vb.du, vb.smooth, P.d, camlr, qa, hd3, hg3, n_inner,
+                                                            p.tv_solverit, p.tv_sor, P.cA, P.cB, n);
+      ls->launches++;
+      P.done = true;
+      continue;
+    }
+    if (p.tv_solverit < 1) {
+      // sor_coupled / sor_coupled_slow_but_readable_DE with zero sweeps leave the increment at 0: the level's result is
+      // uu = wx + 0, which for depth still applies the sign clamp (refine_variational.cpp:301-323)
+      cudaMemsetAsync(vb.du, 0, sizeof(float) * vb.plane_cap * NOP * n, st);
+      finish_kernel<OF><<<P.grd, blk, 0, st>>>(L.flow, vb.du, P.d, camlr);
+      ls->launches++;
+      P.done = true;
+      continue;
+    }
+    const int sched = vb.tv_schedule;   // 0 auto, 1 fused, 2 split, 3 split + general wavefront SOR (DisTuning)
+    // "fused": one CTA per pair runs the whole level (best latency while every pair of the batch is resident,
+    // i.e. up to two CTAs per SM); larger batches take the split path, whose one-warp-per-pair SOR keeps
+    // thousands of pairs resident.  DisTuning::tv_schedule overrides.
+    const bool want_split = p.sor_mode == DISB200_SOR_REDBLACK || (sched ? sched != 1 : n > 2 * 148);
+    if (!want_split && pipelined && fused_smem <= 100 * 1024) {
+      int fthreads = ((g.h * p.tv_solverit + 31) / 32) * 32;
+      if (fthreads < 256) fthreads = 256;
+      cudaFuncSetAttribute(tv_fused_kernel<C, OF>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+      if (ls->mark) ls->mark(ls->ctx, 5, 1);
+      tv_fused_kernel<C, OF><<<n, fthreads, fused_smem, st>>>(P.D, vb.mask, L.flow, P.d, camlr, qa, hd3, hg3, n_inner,
+                                                              p.tv_solverit, p.tv_sor, P.cA, P.cB);
+      if (ls->mark) ls->mark(ls->ctx, 5, 0);
+      ls->launches++;
+      P.done = true;
+      continue;
+    }
+    cudaMemsetAsync(vb.du, 0, sizeof(float) * vb.plane_cap * NOP * n, st);
+    // SOR launcher: one warp per pair (levels of up to 96 rows, up to 5 sweeps), else the general wavefront
+    if (g.h <= 96 && sched != 3) {
+      const int nb = (g.h + 31) / 32;
+      switch (p.tv_solverit) {
+#define DISB200_SORW_CASE(NS_) case NS_: P.sorw = nb == 3 ? sor_warp_kernel<OF, NS_, 3> : (nb == 2 ? sor_warp_kernel<OF, NS_, 2> : sor_warp_kernel<OF, NS_, 1>); break;
+        DISB200_SORW_CASE(1) DISB200_SORW_CASE(2) DISB200_SORW_CASE(3) DISB200_SORW_CASE(4) DISB200_SORW_CASE(5)
+#undef DISB200_SORW_CASE
+        default: break;
+      }
+    }
+    // tall levels: one warp per band of 32 rows, bands chained through tagged boundary rows (sor_band.cuh)
+    // (latency mode: measured 1.35-1.5x over the general wavefront while all bands of the batch are resident, 2 per
+    //  SM — one 4K pair: 27.6 -> 19.8 ms of SOR; with more bands than that the general wavefront, one CTA per
+    //  pair, has the better throughput: 64 4K pairs 33 vs 45 ms)
+    // vb.sorb_max = co-resident CTAs of the band kernel on this device (occupancy API, engine.cu) or less: bands spin on
+    // their neighbours, so every band of the launch must be resident - never more CTAs than that
+    if (!P.sorw && vb.sorb_ctl && g.h > 96 && g.w >= 8 && nbands <= 64 && p.tv_solverit <= 3 && n * nbands <= vb.sorb_max &&
+        (size_t)nbands * g.w * sorb_rows * 4 <= vb.plane_cap * NOP && sched != 3) {
+      switch (p.tv_solverit) {
+        case 1: P.sorb = sor_band_kernel<OF, 1>; P.sorb_smem = SorbCfg<1>::BYTES; break;
+        case 2: P.sorb = sor_band_kernel<OF, 2>; P.sorb_smem = SorbCfg<2>::BYTES; break;
+        default: P.sorb = sor_band_kernel<OF, 3>; P.sorb_smem = SorbCfg<3>::BYTES; break;
+      }
+      cudaFuncSetAttribute(P.sorb, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P.sorb_smem);
+    }
+    if (P.sorw) cudaFuncSetAttribute(P.sorw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sorw_smem);
+    // four pixels per thread need 16-byte aligned rows in every plane: w % 4 == 0 (plane_cap is a multiple of 4)
+    P.smooth4 = (g.w & 3) == 0 && (vb.plane_cap & 3) == 0;
+  }
+  const bool antiphase = nl == 2 && !pl[0].done && !pl[1].done && pl[0].sorw && pl[1].sorw;
+  if (antiphase) {   // assembly next to the SOR warps on one SM: same carve-out for both
+    cudaFuncSetAttribute(system_kernel<C, OF>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(smooth_kernel4<OF>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    cudaFuncSetAttribute(smooth_kernel2<OF>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  }
+  auto assemble = [&](int l, int it) {
+    TvLane& L = lanes[l];
+    Plan& P = pl[l];
+    LaunchStats* ls = L.ls;
     // (a fused diffusivity + system kernel over shared-memory tiles was measured slower: 2.00 vs 1.88 ms per
     //  1480-pair step; the halo re-evaluation and the barrier cost more than the 8 B / pixel they save)
     if (ls->mark) ls->mark(ls->ctx, 7, 1);
-    if (smooth4) smooth_kernel4<OF><<<grd4, blk, 0, st>>>(flow, vb.du, d, camlr, qa, it == 0, vb.smooth);
-    else smooth_kernel2<OF><<<grd, blk, 0, st>>>(flow, vb.du, d, camlr, qa, it == 0, vb.smooth);
+    if (P.smooth4) smooth_kernel4<OF><<<P.grd4, blk, 0, L.st>>>(L.flow, L.vb.du, P.d, camlr, qa, it == 0, L.vb.smooth);
+    else smooth_kernel2<OF><<<P.grd, blk, 0, L.st>>>(L.flow, L.vb.du, P.d, camlr, qa, it == 0, L.vb.smooth);
     if (ls->mark) { ls->mark(ls->ctx, 7, 0); ls->mark(ls->ctx, 6, 1); }
-    system_kernel<C, OF><<<grd, blk, 0, st>>>(D, vb.mask, vb.smooth, flow, vb.du, d, hd3, hg3, cA, cB);
+    system_kernel<C, OF><<<P.grd, blk, 0, L.st>>>(P.D, L.vb.mask, L.vb.smooth, L.flow, L.vb.du, P.d, hd3, hg3, P.cA, P.cB);
     if (ls->mark) ls->mark(ls->ctx, 6, 0);
+    ls->launches += 2;
+  };
+  auto solve = [&](int l) {
+    TvLane& L = lanes[l];
+    Plan& P = pl[l];
+    LaunchStats* ls = L.ls;
+    const VarRefBuffers& vb = L.vb;
+    const int n = L.n;
     if (ls->mark) ls->mark(ls->ctx, 5, 1);
     if (p.sor_mode == DISB200_SOR_REDBLACK) {
       dim3 rblk(32, 4), rgrd((g.w / 2 + 1 + 31) / 32, (g.h + 3) / 4, n);
       for (int sw = 0; sw < 2 * p.tv_solverit; ++sw)
-        sor_redblack_kernel<OF><<<rgrd, rblk, 0, st>>>(vb.du, cA, cB, d, p.tv_sor, sw & 1);
+        sor_redblack_kernel<OF><<<rgrd, rblk, 0, L.st>>>(vb.du, P.cA, P.cB, P.d, p.tv_sor, sw & 1);
       ls->launches += 2 * p.tv_solverit - 1;
-    } else if (sorw) sorw<<<n, 32, sorw_smem, st>>>(vb.du, cA, cB, d, p.tv_sor);
-    else if (sorb) {
+    } else if (P.sorw) P.sorw<<<n, 32, sorw_smem, L.st>>>(vb.du, P.cA, P.cB, P.d, p.tv_sor);
+    else if (P.sorb) {
+      float4* sorb_xt = reinterpret_cast<float4*>(vb.rhs);
+      float4* sorb_xb = sorb_xt + (size_t)n * nbands * p.tv_solverit * g.w;
       const unsigned epoch = ++vb.sorb_host[0], base = vb.sorb_host[1];
       vb.sorb_host[1] += (unsigned)(n * nbands);
-      sorb<<<n * nbands, 32, sorb_smem, st>>>(vb.du, cA, cB, sorb_xt, sorb_xb, sorb_xt, sorb_xb, vb.sorb_ctl, base, epoch, d, nbands, 0,
-                                              nbands, p.tv_sor);
+      P.sorb<<<n * nbands, 32, P.sorb_smem, L.st>>>(vb.du, P.cA, P.cB, sorb_xt, sorb_xb, sorb_xt, sorb_xb, vb.sorb_ctl, base, epoch, P.d,
+                                                    nbands, 0, nbands, p.tv_sor);
     }
-    else sor_wavefront_kernel<OF><<<n, threads, 0, st>>>(vb.du, cA, cB, d, p.tv_solverit, p.tv_sor, pipelined ? 1 : 0);
+    else sor_wavefront_kernel<OF><<<n, threads, 0, L.st>>>(vb.du, P.cA, P.cB, P.d, p.tv_solverit, p.tv_sor, pipelined ? 1 : 0);
     if (ls->mark) ls->mark(ls->ctx, 5, 0);
-    ls->launches += 3;
+    ls->launches++;
+  };
+  for (int it = 0; it < n_inner; ++it) {
+    for (int l = 0; l < nl; ++l) {
+      if (pl[l].done) continue;
+      if (antiphase) {
+        // lane 0 assembles iteration `it` once lane 1 has assembled it-1 (and therefore solves it-1 meanwhile);
+        // lane 1 assembles `it` once lane 0 has (and solves `it` meanwhile)
+        if (l == 0 && it > 0) cudaStreamWaitEvent(lanes[0].st, lanes[1].ev, 0);
+        if (l == 1) cudaStreamWaitEvent(lanes[1].st, lanes[0].ev, 0);
+      }
+      assemble(l, it);
+      if (antiphase) cudaEventRecord(lanes[l].ev, lanes[l].st);
+      solve(l);
+    }
   }
-  finish_kernel<OF><<<grd, blk, 0, st>>>(flow, vb.du, d, camlr);
-  ls->launches++;
+  for (int l = 0; l < nl; ++l) {
+    if (pl[l].done) continue;
+    finish_kernel<OF><<<pl[l].grd, blk, 0, lanes[l].st>>>(lanes[l].flow, lanes[l].vb.du, pl[l].d, camlr);
+    lanes[l].ls->launches++;
+  }
 }
 
 // One level, ONE pair, rows split over ndev devices (see TileDev in dis_internal.h).  The same kernels as the one-device
@@ -1095,16 +1156,21 @@ size_t varref_plane_count(int C, int nop) {
   return (size_t)9 * C + 2 + nop + 4 + 4 + nop;
 }
 
-void launch_varref_level(const float* im_a, const float* im_b, float* flow, const LevelGeom& g, const DisParams& p,
-                         int camlr, const VarRefBuffers& vb, int n, cudaStream_t s, LaunchStats* st) {
+void launch_varref_level_lanes(TvLane* lanes, int nl, const LevelGeom& g, const DisParams& p, int camlr) {
   const bool of = p.mode == DISB200_MODE_OF;
   if (p.channels == 1) {
-    if (of) varref_level_impl<1, true>(im_a, im_b, flow, g, p, camlr, vb, n, s, st);
-    else varref_level_impl<1, false>(im_a, im_b, flow, g, p, camlr, vb, n, s, st);
+    if (of) varref_level_lanes<1, true>(lanes, nl, g, p, camlr);
+    else varref_level_lanes<1, false>(lanes, nl, g, p, camlr);
   } else {
-    if (of) varref_level_impl<3, true>(im_a, im_b, flow, g, p, camlr, vb, n, s, st);
-    else varref_level_impl<3, false>(im_a, im_b, flow, g, p, camlr, vb, n, s, st);
+    if (of) varref_level_lanes<3, true>(lanes, nl, g, p, camlr);
+    else varref_level_lanes<3, false>(lanes, nl, g, p, camlr);
   }
+}
+
+void launch_varref_level(const float* im_a, const float* im_b, float* flow, const LevelGeom& g, const DisParams& p,
+                         int camlr, const VarRefBuffers& vb, int n, cudaStream_t s, LaunchStats* st) {
+  TvLane lane{im_a, im_b, flow, vb, n, s, st, nullptr};
+  launch_varref_level_lanes(&lane, 1, g, p, camlr);
 }
 
 }  // namespace disb200

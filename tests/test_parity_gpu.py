@@ -201,9 +201,9 @@ def test_ofclass_against_reference_golden(gpu, port, ref_golden, name):
 
 
 def test_ofclass_initflow(gpu, port):
-    A, B, _ = make_pair(90, 150, seed=11)
+    A, B, _ = make_pair(96, 152, seed=11)      # W, H divisible by 2^(sc_f + 1): what initflow requires (run_dense.cpp:301)
     q = base_orc(1, 1, sc_f=2, sc_l=1)
-    W, H, _, _ = port.pad_dims(150, 90, 2)
+    W, H, _, _ = port.pad_dims(152, 96, 2)
     PA, PB = port.pyramid(A, 2, 1, 8), port.pyramid(B, 2, 1, 8)
     init = np.zeros((H >> 3, W >> 3, 2), np.float32)
     init[..., 0] = 0.4
@@ -585,7 +585,8 @@ def test_video_sequence_temporal_warm_start(gpu, port, mode, ch):
         cold = hd.run_sequence(frames)
         assert hd.launch_count() > 0
     assert np.array_equal(got[0], cold[0])                # pair 0 starts cold
-    assert not np.array_equal(got[1:], cold[1:])          # the others start somewhere else
+    if mode == 1:
+        assert not np.array_equal(got[1:], cold[1:])      # the others start somewhere else
     m, mx = epe(got, want)
     assert m <= MEAN_TOL and mx <= 0.05, "EPE(GPU,CPU) mean %g max %g" % (m, mx)
     # odd coarsest level: initflow would be read out of bounds (by the reference too) - refused
@@ -730,3 +731,23 @@ def test_tiled_small_frame_is_replicated(gpu):
     with gpu.Tiled(p, 200, 120, [0, 0]) as td:
         assert not any(td.plan(l)[0] for l in range(p.sc_l, p.sc_f + 1))
         assert np.array_equal(td.run(A, B), want)
+
+
+@pytest.mark.parametrize("mode,ch,kw", [(1, 1, {}), (2, 1, {}), (1, 3, dict(usefbcon=1))])
+def test_antiphase_sub_batches_give_the_same_bits(gpu, mode, ch, kw):
+    """DisTuning.antiphase: two sub-batches enqueued level by level side by side, their refinements alternating (one
+    assembles its linear system while the other runs the one-warp SOR).  A schedule, not an algorithm: identical output."""
+    w0, h0, n = 320, 200, 7
+    pairs = [make_pair(h0, w0, channels=ch, mode="OF" if mode == 1 else "DE", seed=30 + s)[:2] for s in range(n)]
+    A, B = np.stack([a for a, _ in pairs]), np.stack([b for _, b in pairs])
+    p = gpu.operating_point(2, w0, mode, ch).copy(verbosity=0, sc_f=3, sc_l=1, **kw)
+    with gpu.Handle(p, w0, h0, n) as hd:
+        want = hd.run_host(A, B)
+    try:
+        gpu.set_tuning(streams=2, antiphase=1, tv_schedule=gpu.TV_SPLIT)
+        with gpu.Handle(p, w0, h0, n) as hd:
+            got = hd.run_host(A, B)
+            got2 = hd.run_host(A[:3], B[:3])
+    finally:
+        gpu.set_tuning()
+    assert np.array_equal(got, want) and np.array_equal(got2, want[:3])
