@@ -76,8 +76,9 @@ typedef struct DisHandle DisHandle;
 typedef struct DisTuning {
   int streams;       /* sub-batches of one run_batch call on their own streams (auto: 2 from 1184 pairs up) */
   int host_chunk;    /* pairs per pipelined chunk of the host-pointer entry points (auto: n / 8, at least 16) */
-  int tv_schedule;   /* refinement of a level: 1 fused (one CTA per pair), 2 split (one-warp / banded SOR), 3 split with the
-                        general CTA wavefront SOR */
+  int tv_schedule;   /* refinement of a level: 1 fused (one CTA per pair runs the whole level), 2 split with system_kernel and
+                        the stand-alone one-warp / banded SOR, 3 split with the general CTA wavefront SOR, 4 split with the
+                        system assembled inside the one-warp SOR kernel (what large batches take by default) */
   int sorb_max;      /* largest n * bands the banded SOR takes (auto and upper bound: the number of co-resident CTAs) */
   int patch_map;     /* 1: value-interleaved lane mapping of the inverse search where the block mapping is the default */
   int antiphase;     /* 1: with two sub-batches, run their refinements in anti-phase (one assembles while the other solves) */

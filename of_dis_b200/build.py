@@ -50,8 +50,9 @@ TOL_FLAGS = ["-prec-div=false", "-prec-sqrt=false"]
 def build(force: bool = False, verbose: bool = False, variant: str = "parity") -> str:
     nvcc = _nvcc()
     tol = variant == "tol"
-    LIB = TOL_LIB if tol else globals()["LIB"]
-    objdir = os.path.join(HERE, "build_tol" if tol else "build")
+    tag = os.environ.get("DISB200_BUILD_TAG", "")          # A/B builds: libdisb200_<tag>.so with DISB200_NVCC_EXTRA flags
+    LIB = TOL_LIB if tol else (os.path.join(HERE, "libdisb200_%s.so" % tag) if tag else globals()["LIB"])
+    objdir = os.path.join(HERE, "build_tol" if tol else ("build_" + tag if tag else "build"))
     os.makedirs(objdir, exist_ok=True)
     headers = [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".h", ".cuh"))]
     headers.append(os.path.join(HERE, "..", "include", "disb200.h"))
@@ -75,7 +76,7 @@ def build(force: bool = False, verbose: bool = False, variant: str = "parity") -
                            capture_output=True, text=True)
         if r.returncode != 0:
             raise RuntimeError("link failed:\n" + r.stderr)
-    if tol:
+    if tol or tag:
         return LIB
     # the four CLIs of the reference (CMakeLists.txt:35-61), thin mains over the library
     cli_src = os.path.join(CSRC, "run_dense.cpp")

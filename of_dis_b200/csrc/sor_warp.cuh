@@ -112,9 +112,15 @@ __device__ __forceinline__ float2 sorw_shfl(float2 v, int src) {
 // du: global increment plane of this pair, [h][w] float2 (OF) / float (DE), updated in place.
 // smem: sorw_smem_bytes(h, NS) bytes owned by this warp.  cA / cB: global coefficient planes of
 // this pair (row stride w).  Called by exactly one full warp; h <= 32 * NB.
-template <bool OF, int NS, int NB>
+//
+// FUSED (sor_fused.cuh): the rings are not streamed from global memory by this warp but FILLED by producer warps of the
+// same CTA, which evaluate the linear system of each 8-pixel chunk (system_pixel) straight into its ring slots - the
+// coefficient planes never exist in memory.  sync[0] = number of fetch phases this warp has finished, sync[1 + b] = last
+// production step band b's producer has finished; production step tn holds exactly what request(tn) would have copied.
+template <bool OF, int NS, int NB, bool FUSED = false>
 __device__ __forceinline__ void sor_warp(float* __restrict__ du, unsigned smem, const float4* __restrict__ cA,
-                                         const float4* __restrict__ cB, int w, int h, float omega) {
+                                         const float4* __restrict__ cB, int w, int h, float omega,
+                                         volatile int* sync = nullptr) {
   typedef SorwCfg<NS> Cfg;
   constexpr int NOP = OF ? 2 : 1, RPX = Cfg::RPX, LEADPX = Cfg::LEADPX;
   const int lane = threadIdx.x & 31;
@@ -185,18 +191,33 @@ __device__ __forceinline__ void sor_warp(float* __restrict__ du, unsigned smem, 
     if ((unsigned)(i0[b] + 1) < uw) nr0[b] = sorw_lds_du<OF>(rD[b] + ((unsigned)(i0[b] + 1) & (RPX - 1)) * 8u);
     if (i0[b] == 0) cur0[b] = sorw_lds_du<OF>(rD[b]);
   };
-  // prologue: chunk 0 of every row, plus whatever is due at step 0
+  // the fetch that prepares step t1 reads what production steps <= t1 - 3 delivered (first pixel of a chunk: the right
+  // neighbour of sweep 0, LEADPX - 1 steps after its request)
+  auto wait_produced = [&](int t1) {
+    if (FUSED) {
 #pragma unroll
-  for (int rr = 0; rr < 8; ++rr) {
+      for (int b = 0; b < NB; ++b)
+        while (sync[1 + b] < t1 - 3) __nanosleep(64);
+      __threadfence_block();
+    }
+  };
+  if (FUSED) {
+    wait_produced(0);
+  } else {
+    // prologue: chunk 0 of every row, plus whatever is due at step 0
 #pragma unroll
-    for (int b = 0; b < NB; ++b) copy_chunk(b, rr + 8 * cg, 0);
+    for (int rr = 0; rr < 8; ++rr) {
+#pragma unroll
+      for (int b = 0; b < NB; ++b) copy_chunk(b, rr + 8 * cg, 0);
+    }
+    request(0, 1);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    __syncwarp();
   }
-  request(0, 1);
-  asm volatile("cp.async.commit_group;" ::: "memory");
-  asm volatile("cp.async.wait_group 0;" ::: "memory");
-  __syncwarp();
 #pragma unroll
   for (int b = 0; b < NB; ++b) fetch(b);
+  if (FUSED) { __syncwarp(); if (lane == 0) { __threadfence_block(); sync[0] = 0; } }
 
 #pragma unroll 2
   for (int t = 0; t < T; ++t) {
@@ -252,12 +273,17 @@ __device__ __forceinline__ void sor_warp(float* __restrict__ du, unsigned smem, 
       if ((unsigned)(i0[b] + 1) < uw) cur0[b] = nr0[b];   // centre of the next pixel = this step's right neighbour
       ++i0[b]; gD[b] += NOP;
     }
-    request(t + 1, 1);
-    asm volatile("cp.async.commit_group;" ::: "memory");
-    asm volatile("cp.async.wait_group %0;" ::"n"(Cfg::WAITN) : "memory");
-    __syncwarp();
+    if (FUSED) {
+      wait_produced(t + 1);
+    } else {
+      request(t + 1, 1);
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      asm volatile("cp.async.wait_group %0;" ::"n"(Cfg::WAITN) : "memory");
+      __syncwarp();
+    }
 #pragma unroll
     for (int b = 0; b < NB; ++b) fetch(b);
+    if (FUSED) { __syncwarp(); if (lane == 0) { __threadfence_block(); sync[0] = t + 1; } }   // ring slots read by this fetch are free from now on
   }
 }
 

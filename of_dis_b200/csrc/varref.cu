@@ -583,6 +583,7 @@ __device__ __forceinline__ void sor_wavefront(float* du, const float4* cA, const
 }
 
 #include "sor_warp.cuh"
+#include "sor_fused.cuh"
 #include "sor_band.cuh"
 
 // General path: one CTA per frame pair, increment du in global memory.  When rows x sweeps
@@ -869,6 +870,9 @@ void varref_level_lanes(TvLane* lanes, int nl, const LevelGeom& g, const DisPara
     void (*sorw)(float*, const float4*, const float4*, Dims, float) = nullptr;
     void (*sorb)(float*, const float4*, const float4*, float4*, float4*, float4*, float4*, unsigned*, unsigned, unsigned, Dims, int, int, int, float) = nullptr;
     size_t sorb_smem = 0;
+    // system assembly inside the SOR kernel (sor_fused.cuh): replaces system_kernel + sorw
+    void (*solvef)(DerivPtrs, const float*, const float*, const float*, float*, Dims, float, float, float) = nullptr;
+    int solvef_threads = 0;
   } pl[2];
 
   // ---- per level: warp, derivatives; levels that one kernel handles whole (narrow, zero sweeps, fused) end here ----
@@ -950,6 +954,14 @@ void varref_level_lanes(TvLane* lanes, int nl, const LevelGeom& g, const DisPara
       cudaFuncSetAttribute(P.sorb, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P.sorb_smem);
     }
     if (P.sorw) cudaFuncSetAttribute(P.sorw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sorw_smem);
+    // the one-warp SOR with the system assembled by producer warps of its CTA (three sweeps: every operating point);
+    // DisTuning::tv_schedule = 2 keeps system_kernel + the stand-alone SOR
+    if (P.sorw && p.tv_solverit == 3 && sched != 2) {
+      const int nb = (g.h + 31) / 32;
+      P.solvef = nb == 3 ? tv_solve_fused_kernel<C, OF, 3, 3> : (nb == 2 ? tv_solve_fused_kernel<C, OF, 3, 2> : tv_solve_fused_kernel<C, OF, 3, 1>);
+      P.solvef_threads = 32 * (1 + nb);
+      cudaFuncSetAttribute(P.solvef, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sorf_smem_bytes(g.h, 3));
+    }
     // four pixels per thread need 16-byte aligned rows in every plane: w % 4 == 0 (plane_cap is a multiple of 4)
     P.smooth4 = (g.w & 3) == 0 && (vb.plane_cap & 3) == 0;
   }
@@ -968,10 +980,13 @@ void varref_level_lanes(TvLane* lanes, int nl, const LevelGeom& g, const DisPara
     if (ls->mark) ls->mark(ls->ctx, 7, 1);
     if (P.smooth4) smooth_kernel4<OF><<<P.grd4, blk, 0, L.st>>>(L.flow, L.vb.du, P.d, camlr, qa, it == 0, L.vb.smooth);
     else smooth_kernel2<OF><<<P.grd, blk, 0, L.st>>>(L.flow, L.vb.du, P.d, camlr, qa, it == 0, L.vb.smooth);
-    if (ls->mark) { ls->mark(ls->ctx, 7, 0); ls->mark(ls->ctx, 6, 1); }
+    if (ls->mark) ls->mark(ls->ctx, 7, 0);
+    ls->launches++;
+    if (P.solvef) return;   // the system is assembled inside the solve kernel
+    if (ls->mark) ls->mark(ls->ctx, 6, 1);
     system_kernel<C, OF><<<P.grd, blk, 0, L.st>>>(P.D, L.vb.mask, L.vb.smooth, L.flow, L.vb.du, P.d, hd3, hg3, P.cA, P.cB);
     if (ls->mark) ls->mark(ls->ctx, 6, 0);
-    ls->launches += 2;
+    ls->launches++;
   };
   auto solve = [&](int l) {
     TvLane& L = lanes[l];
@@ -985,6 +1000,8 @@ void varref_level_lanes(TvLane* lanes, int nl, const LevelGeom& g, const DisPara
       for (int sw = 0; sw < 2 * p.tv_solverit; ++sw)
         sor_redblack_kernel<OF><<<rgrd, rblk, 0, L.st>>>(vb.du, P.cA, P.cB, P.d, p.tv_sor, sw & 1);
       ls->launches += 2 * p.tv_solverit - 1;
+    } else if (P.solvef) {
+      P.solvef<<<n, P.solvef_threads, sorf_smem_bytes(g.h, 3), L.st>>>(P.D, vb.mask, vb.smooth, L.flow, vb.du, P.d, hd3, hg3, p.tv_sor);
     } else if (P.sorw) P.sorw<<<n, 32, sorw_smem, L.st>>>(vb.du, P.cA, P.cB, P.d, p.tv_sor);
     else if (P.sorb) {
       float4* sorb_xt = reinterpret_cast<float4*>(vb.rhs);

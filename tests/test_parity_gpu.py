@@ -140,7 +140,7 @@ def test_varref_tall_level_uses_band_mode(gpu, port):
 
 @pytest.mark.parametrize("mode,ch", [(1, 1), (1, 3), (2, 1), (2, 3)])
 @pytest.mark.parametrize("w0,h0,level,solverit", [(1024, 436, 3, 3), (500, 218, 2, 3), (260, 128, 1, 5), (250, 120, 2, 2), (1920, 1080, 4, 3), (300, 180, 1, 1),
-                                                  (500, 436, 1, 3), (640, 400, 0, 2), (333, 300, 0, 1)])
+                                                  (500, 436, 1, 3), (640, 400, 0, 2), (333, 300, 0, 1), (256, 120, 2, 3), (1024, 436, 4, 3)])
 def test_tv_paths_agree_bit_for_bit(gpu, port, monkeypatch, mode, ch, w0, h0, level, solverit):
     """The three schedules of the lexicographic SOR — one CTA per pair (fused), one warp per pair with shuffles
     and cp.async row streams (split, used for large batches; levels taller than 96 rows: one warp per band of 32
@@ -156,7 +156,7 @@ def test_tv_paths_agree_bit_for_bit(gpu, port, monkeypatch, mode, ch, w0, h0, le
         fl = -np.abs(fl)
     want = port.varref_level(q, a, b, wl, hl, level, 0, fl)
     try:
-        for sched in (gpu.TV_FUSED, gpu.TV_SPLIT, gpu.TV_GENERAL):
+        for sched in (gpu.TV_FUSED, gpu.TV_SPLIT, gpu.TV_GENERAL, gpu.TV_SOLVEF):
             gpu.set_tuning(tv_schedule=sched)
             got = gpu.varref_level(to_dis(gpu, q), a, b, wl, hl, level, 0, fl)
             assert np.array_equal(got, want), (sched, float(np.abs(got - want).max()))
