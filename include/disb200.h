@@ -78,7 +78,7 @@ typedef struct DisTuning {
   int host_chunk;    /* pairs per pipelined chunk of the host-pointer entry points (auto: n / 8, at least 16) */
   int tv_schedule;   /* refinement of a level: 1 fused (one CTA per pair runs the whole level), 2 split with system_kernel and
                         the stand-alone one-warp / banded SOR, 3 split with the general CTA wavefront SOR, 4 split with the
-                        system assembled inside the one-warp SOR kernel (what large batches take by default) */
+                        system assembled inside the one-warp SOR kernel (an experiment that measured 2.9x slower; never automatic) */
   int sorb_max;      /* largest n * bands the banded SOR takes (auto and upper bound: the number of co-resident CTAs) */
   int patch_map;     /* 1: value-interleaved lane mapping of the inverse search where the block mapping is the default */
   int antiphase;     /* 1: with two sub-batches, run their refinements in anti-phase (one assembles while the other solves) */

@@ -99,6 +99,7 @@ struct DisHandle {
   int cap = 0;                    // pairs per sub-batch engine
   int max_batch = 0;              // pairs per call
   int last_per = 0;               // sub-batch size of the most recent run (for disb200_fetch)
+  int last_n = 0;                 // pairs of the most recent enqueue
   cudaEvent_t ev_fork = nullptr;
   std::vector<cudaEvent_t> ev_join;
   int launches = 0;
@@ -209,6 +210,7 @@ struct DisHandle {
     const int per = (n + S - 1) / S;
     if (per > cap) return fail(DISB200_EINVAL, "internal: sub-batch exceeds engine capacity");
     last_per = per;
+    last_n = n;
     launches = 0;
     if (S > 1 && !serial) {
       int rc = ensure_subs();
@@ -661,7 +663,12 @@ int disb200_fetch(DisHandle* h, int kind, int which, int level, int pair, void* 
   int si = pair / h->last_per;
   if (si > (int)h->extra.size()) return fail(DISB200_EINVAL, "pair was not part of the last run");
   pair -= si * h->last_per;
-  if (h->e.stage_timing) si = 0;
+  if (h->e.stage_timing && h->nsub > 1) {
+    // the per-stage stopwatch runs the sub-batches one after another on engine 0: only the last one's intermediates exist
+    const int last_si = (h->last_n - 1) / h->last_per;
+    if (si != last_si) return fail(DISB200_EINVAL, "with stage timing on, only pairs of the last sub-batch can be fetched");
+    si = 0;
+  }
   CU(cudaSetDevice(h->e.device));
   CU(cudaStreamSynchronize(h->e.stream));
   Engine& e = h->sub(si);

@@ -954,9 +954,14 @@ void varref_level_lanes(TvLane* lanes, int nl, const LevelGeom& g, const DisPara
       cudaFuncSetAttribute(P.sorb, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P.sorb_smem);
     }
     if (P.sorw) cudaFuncSetAttribute(P.sorw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sorw_smem);
-    // the one-warp SOR with the system assembled by producer warps of its CTA (three sweeps: every operating point);
-    // DisTuning::tv_schedule = 2 keeps system_kernel + the stand-alone SOR
-    if (P.sorw && p.tv_solverit == 3 && sched != 2) {
+    // DisTuning::tv_schedule = 4: the one-warp SOR with the system assembled by producer warps of its CTA (sor_fused.cuh;
+    // three sweeps).  Bit-identical, removes 64 B per pixel and iteration of HBM traffic - and is 2.9x SLOWER than
+    // system_kernel + the stand-alone SOR (C1, 1776 pairs: 8.57 ms against 1.41 + 1.59; profiles/r02f_solvef.txt): one
+    // producer warp per band cannot hide the latency of 20 dependent loads and 13 divisions per pixel inside the five
+    // steps of slack a 16-pixel ring gives it, and neither registers (128 per thread, five CTAs per SM) nor shared
+    // memory (35 KB of rings per pair) leave room for the dozens of warps the stand-alone kernel hides it with.
+    // Kept as a tested schedule for that evidence; never chosen automatically.
+    if (P.sorw && p.tv_solverit == 3 && sched == 4) {
       const int nb = (g.h + 31) / 32;
       P.solvef = nb == 3 ? tv_solve_fused_kernel<C, OF, 3, 3> : (nb == 2 ? tv_solve_fused_kernel<C, OF, 3, 2> : tv_solve_fused_kernel<C, OF, 3, 1>);
       P.solvef_threads = 32 * (1 + nb);

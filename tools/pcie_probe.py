@@ -10,6 +10,7 @@ must cross to the host).  Rank 0 prints one JSON line.
 """
 import json
 import os
+import sys
 import time
 
 import torch
@@ -20,6 +21,14 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    affinity = "spread" if "--affinity-spread" in sys.argv else "none"
+    if affinity == "spread":       # each rank on its own slice of the host cores BEFORE it allocates (first-touch placement)
+        ncpu = os.cpu_count() or 1
+        per = max(1, ncpu // world)
+        try:
+            os.sched_setaffinity(0, set(range(rank * per, min(ncpu, (rank + 1) * per))))
+        except OSError:
+            affinity = "spread (sched_setaffinity refused)"
     torch.cuda.set_device(local)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -60,7 +69,7 @@ def main():
         slowest = max(float(x[1]) for x in lst)
         out[name] = {"per_gpu_gbs": [round(x, 2) for x in per], "aggregate_gbs": round(blk * nblk * (2 if name == "both" else 1) * world / slowest / 1e9, 2)}
     if rank == 0:
-        print(json.dumps({"probe": "pinned cudaMemcpyAsync, 64 MB blocks, %d blocks per direction" % nblk, "n_gpus": world, "cpu_count": os.cpu_count(), **out}))
+        print(json.dumps({"probe": "pinned cudaMemcpyAsync, 64 MB blocks, %d blocks per direction" % nblk, "n_gpus": world, "cpu_count": os.cpu_count(), "affinity": affinity, **out}))
     if world > 1:
         dist.destroy_process_group()
 
