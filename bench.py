@@ -483,8 +483,9 @@ def main():
         # per fixed-point iteration: 8C derivative planes + mask + diffusivity + flow + increment in, two float4 packs out
         "system": tv * ndir * sum(n_in(l) * 4 * w * h * (8 * ch + 1 + 2 + 2 * nop + 8) for w, h, l in lv),
         "upsample": 4 * nop * lv[0][0] * lv[0][1] + 4 * nop * w0 * h0,
-        # per sweep read 9 planes (a11 a12 a22 b1 b2 h v du dv), write 2 (DE: 5 + 1)
-        "sor": tv * ndir * sum(n_in(l) * p.tv_solverit * (4 * w * h) * (11 if nop == 2 else 6) for w, h, l in lv),
+        # per fixed-point iteration the SOR makes ONE pass over memory whatever the number of sweeps (they are pipelined
+        # inside the kernel): two float4 coefficient packs + the increment in, the increment out
+        "sor": tv * ndir * sum(n_in(l) * 4 * w * h * (8 + 2 * nop) for w, h, l in lv),
     }
     nl = len(lv) * ndir
     n_it = ndir * sum(n_in(l) for _, _, l in lv)
@@ -499,12 +500,15 @@ def main():
     dom = max(stage_share, key=stage_share.get)
     dom_ms = stage_share[dom]
     dom_bytes = alg.get(dom)
-    # DRAM traffic per pair and stage from the committed ncu --set full captures (profiles/r01_traffic.json; C1 only)
-    traffic = {}
-    tpath = os.path.join(ROOT, "profiles", "r01_traffic.json")
+    # DRAM traffic per pair and stage, and the issue-slot utilisation of each stage, from the committed ncu --set full
+    # capture of the shipped kernels (profiles/r02_kernels.json, built by tools/ncu_summary.py; C1 only)
+    traffic, issue = {}, {}
+    tpath = os.path.join(ROOT, "profiles", "r02_kernels.json")
     if args.workload == "C1" and os.path.exists(tpath):
         with open(tpath) as f:
-            traffic = {k: v["dram_read_bytes_per_pair"] + v["dram_write_bytes_per_pair"] for k, v in json.load(f)["per_stage"].items()}
+            ks = json.load(f)["per_stage"]
+        traffic = {k: v["dram_read_bytes_per_pair"] + v["dram_write_bytes_per_pair"] for k, v in ks.items()}
+        issue = {k: v.get("issue_active_pct") for k, v in ks.items()}
     roof = {"bound": "hbm", "kernel": kernels[dom], "stage": dom, "unit": "GB/s", "peak": peak, "peak_source": peak_src,
             "share_of_step": dom_ms / step_ms if step_ms else None,
             "traffic": traffic[dom] * nb if dom in traffic else None}
@@ -518,7 +522,11 @@ def main():
     # every stage: algorithmic GB/s against the same peak (the launch set of the stage, per step)
     roof["per_stage"] = {k: {"ms": round(v, 4), "algorithmic_bytes": alg[k] * nb, "achieved": round(alg[k] * nb / (v / 1e3) / 1e9, 1) if v > 0 else None,
                              "frac": round(alg[k] * nb / (v / 1e3) / 1e9 / peak, 4) if v > 0 else None,
-                             "traffic": traffic[k] * nb if k in traffic else None} for k, v in stage_share.items()}
+                             "traffic": traffic[k] * nb if k in traffic else None,
+                             # issue-slot roofline (the one that bounds the latency / instruction-bound stages): share of the
+                             # SM sub-partitions' issue cycles in which an instruction was issued, ncu smsp__issue_active
+                             "issue_active_frac": round(issue[k] / 100.0, 4) if issue.get(k) is not None else None} for k, v in stage_share.items()}
+    roof["issue_active_frac"] = roof["per_stage"][dom]["issue_active_frac"]
     path_gbs = value / world * bytes_per_pair / 1e9
     roof["whole_path"] = {"algorithmic_bytes_per_pair": bytes_per_pair, "achieved": path_gbs, "frac": path_gbs / peak}
     roof["stage_ms_per_step"] = {k: round(v, 4) for k, v in stage_share.items()}
