@@ -383,6 +383,34 @@ def test_c4_4k_cost_variants_with_fb_consistency(gpu, port):
         assert epe(out, gt)[0] < 0.5
 
 
+def test_c4_heavy_line_reduced_size(gpu, port):
+    """The heavy C4 line of SURVEY.md 8(d) (`7 1 16 16 .05 .95 0 12 .75 1 1 1 ...`: 12 x 12 patches at overlap .75 down to
+    level 1, forward-backward consistency, L1) against the oracle, on a 1920x1080 frame so that the CPU side stays within
+    seconds; the full 3840x2160 pair is in bench.py --workload C4h (parity object: mean 7.5e-6 px) and in
+    tests/test_tiled_multi_gpu.py."""
+    A, B, gt = make_pair(1080, 1920, seed=0)
+    p = gpu.operating_point(2, 1920).copy(verbosity=0, sc_f=6, sc_l=1, max_iter=16, min_iter=16, patchsz=12, patove=0.75, usefbcon=1, costfct=1)
+    want = port.run_dense(to_orc(p), A, B)
+    with gpu.Handle(p, 1920, 1080, 1) as hd:
+        out = hd.run_host(A[None], B[None])[0]
+    m, mx = epe(out, want)
+    assert m <= MEAN_TOL and mx <= MAX_TOL_DENSE, (m, mx)
+    assert abs(epe(out, gt)[0] - epe(want, gt)[0]) < 5e-3
+
+
+def test_c5_full_size_video_against_the_oracle(gpu, port):
+    """BASELINE.json configs[4] at its real frame size: consecutive 1920x1080 frames through the sequence entry point
+    (pyramids shared between pairs), every pair against the CPU oracle - op2 grey is bit-identical."""
+    from of_dis_b200.synth import make_sequence
+    fr = np.stack(make_sequence(1080, 1920, 4, seed=0))
+    p = gpu.operating_point(2, 1920).copy(verbosity=0)
+    with gpu.Handle(p, 1920, 1080, max_batch=3) as hd:
+        got = hd.run_sequence(fr)
+    for i in range(3):
+        want = port.run_dense(to_orc(p), fr[i], fr[i + 1])
+        assert np.array_equal(got[i], want), (i, epe(got[i], want))
+
+
 def test_run_list_and_chunking(gpu, port):
     """disb200_run_batch (pointer lists) and n > max_batch chunking give the same answers."""
     pairs = [make_pair(100, 180, seed=s)[:2] for s in range(5)]
