@@ -26,7 +26,7 @@ __global__ void __maxnreg__(DISB200_SORF_REGS)
 tv_solve_fused_kernel(DerivPtrs D, const float* __restrict__ mask_all, const float* __restrict__ s_all,
                       const float* __restrict__ flow_all, float* __restrict__ du_all, Dims d, float hd3, float hg3, float omega) {
   typedef SorwCfg<NS> Cfg;
-  constexpr int NOP = OF ? 2 : 1, RPX = Cfg::RPX, LEADPX = Cfg::LEADPX, NCH = Cfg::NCH;
+  constexpr int NOP = OF ? 2 : 1, RPX = Cfg::RPX, LEADPX = Cfg::LEADPX, NCH = Cfg::NCH, CH = Cfg::CH, CHS = Cfg::CHS;
   extern __shared__ float4 sorf_smem[];
   const int pair = blockIdx.x, w = d.w, h = d.h, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const unsigned smem = (unsigned)__cvta_generic_to_shared(sorf_smem);
@@ -41,7 +41,7 @@ tv_solve_fused_kernel(DerivPtrs D, const float* __restrict__ mask_all, const flo
   }
   // ---- producer of band `band` ----
   const int band = warp - 1;
-  const int cg = lane >> 3, ce = lane & 7;
+  const int cg = lane >> CHS, ce = lane & (CH - 1);
   const float* mask = mask_all + (size_t)pair * d.plane;
   const float* sp = s_all + (size_t)pair * d.plane;
   const float* fl = flow_all + (size_t)pair * w * h * NOP;
@@ -49,8 +49,8 @@ tv_solve_fused_kernel(DerivPtrs D, const float* __restrict__ mask_all, const flo
   const unsigned offB = (unsigned)h * (RPX * 16u);
   const int T = w + h - 1 + 2 * (NS - 1);
   for (int tn = -LEADPX; tn <= T - 3; ++tn) {
-    const int r = ((tn + LEADPX) & 7) + 8 * cg;
-    const int j = band * 32 + r, q = (tn - j + LEADPX) >> 3, px = 8 * q + ce;
+    const int r = ((tn + LEADPX) & (CH - 1)) + CH * cg;
+    const int j = band * 32 + r, q = (tn - j + LEADPX) >> CHS, px = CH * q + ce;
     const bool valid = q >= 0 && j < h && px < w;
     if (__any_sync(0xffffffffu, valid)) {
       // a chunk beyond the ring depth overwrites the slot of chunk q - NCH: wait until the consumer's last sweep has read it
@@ -61,7 +61,7 @@ tv_solve_fused_kernel(DerivPtrs D, const float* __restrict__ mask_all, const flo
       if (valid) {
         float4 a, b;
         system_pixel<C, OF>(D, mask, sp, fl, du, px, j, w, h, d.plane, o, hd3, hg3, a, b);
-        const unsigned slot = (unsigned)(j * RPX + (px & (RPX - 1)));
+        const unsigned slot = (unsigned)(j * RPX) + sorw_ring<RPX>((unsigned)px);
         asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(smem + slot * 16u), "f"(a.x), "f"(a.y), "f"(a.z), "f"(a.w) : "memory");
         asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(smem + offB + slot * 16u), "f"(b.x), "f"(b.y), "f"(b.z), "f"(b.w) : "memory");
         const size_t g = (size_t)j * w + px;

@@ -28,23 +28,39 @@
 #ifndef DISB200_SOR_WARP_CUH_
 #define DISB200_SOR_WARP_CUH_
 
-// Row streams are cut into chunks of 8 pixels.  Chunk q of a row is requested when the row's
-// sweep-0 pixel reaches 8 q - LEADPX; at every step the rows that reach such a point are
-// j = (t + LEADPX) mod 8 + 8 g, four per band, so ONE cp.async per stream serves them all:
-// lane = 8 g + e copies pixel 8 q + e of row j — four fully used 128-byte segments per
-// instruction instead of 32 scattered sectors.  The owner lane of a row reads its pixels from
-// the row's ring of NCH chunks one step before use.
+// Row streams are cut into chunks of CH pixels.  Chunk q of a row is requested when the row's sweep-0 pixel reaches
+// CH q - LEADPX; at every step the rows that reach such a point are j = (t + LEADPX) mod CH + CH g, 32 / CH per band, so ONE
+// cp.async per stream serves them all: lane = CH g + e copies pixel CH q + e of row j — fully used 64- or 128-byte segments
+// per instruction instead of 32 scattered sectors.  The owner lane of a row reads its pixels from the row's ring of RPX
+// pixels one step before use.  The ring must hold the pixels between the last sweep (2 (NS - 1) behind sweep 0) and the
+// chunk being filled (LEADPX + CH ahead): 4 + 4 + 4 = 12 pixels for up to three sweeps.  Shared memory per pair is what
+// bounds the number of resident warps, and the warps are what bounds this kernel (one warp issues an instruction every
+// 2.4 cycles; with 1.4 warps per scheduler the issue slots are 57 % busy, profiles/r02h_hot_details_b1776.txt): the
+// 12-pixel ring (27 KB at 56 rows, 8 pairs per SM) replaced a 16-pixel one (35 KB, 6 pairs per SM).
 template <int NS>
 struct SorwCfg {
   static constexpr int H = 2 * (NS - 1);             // pixels the last sweep trails sweep 0
-  static constexpr int NCH = NS <= 3 ? 2 : 4;        // chunk slots per row
-  static constexpr int RPX = NCH * 8;                // ring pixels per row
+#ifdef DISB200_SORW_RING16                           // A/B build: the 16-pixel ring of round 1 (two 8-pixel chunks)
+  static constexpr int CH = 8, CHS = 3;
+  static constexpr int NCH = NS <= 3 ? 2 : 4;
+#else
+  static constexpr int CH = NS <= 3 ? 4 : 8;         // pixels per chunk
+  static constexpr int CHS = NS <= 3 ? 2 : 3;        // log2(CH)
+  static constexpr int NCH = NS <= 3 ? 3 : 4;        // chunk slots per row
+#endif
+  static constexpr int RPX = NCH * CH;               // ring pixels per row (12: not a power of two, see sorw_ring)
   static constexpr int LEADPX = NS <= 3 ? 4 : 8;     // request distance in pixels
   static constexpr int WAITN = LEADPX - 2;           // cp.async groups that may stay in flight
   static constexpr int ROW_BYTES = RPX * (16 + 16 + 8);   // one row's rings: cA, cB (float4) and the increment
+  static_assert(H + LEADPX + CH <= RPX, "ring too short for the sweeps in flight");
 };
+// ring slot of pixel i (i >= 0)
+template <int RPX>
+__device__ __forceinline__ unsigned sorw_ring(unsigned i) {
+  if ((RPX & (RPX - 1)) == 0) return i & (RPX - 1);
+  return i - RPX * __umulhi(i, (unsigned)(0x100000000ull / RPX) + 1u);   // i mod RPX, exact for i < 2^31 / RPX
+}
 // Rings exist for the h rows of the level only (not for whole 32-row bands): three regions, [h][RPX] each.
-// A 56-row level needs 35 KB instead of 40, which is the difference between 5 and 6 resident pairs per SM.
 __host__ __device__ inline size_t sorw_smem_bytes(int h, int ns) {
   return (size_t)h * (ns <= 3 ? SorwCfg<3>::ROW_BYTES : SorwCfg<5>::ROW_BYTES);
 }
@@ -122,13 +138,13 @@ __device__ __forceinline__ void sor_warp(float* __restrict__ du, unsigned smem, 
                                          const float4* __restrict__ cB, int w, int h, float omega,
                                          volatile int* sync = nullptr) {
   typedef SorwCfg<NS> Cfg;
-  constexpr int NOP = OF ? 2 : 1, RPX = Cfg::RPX, LEADPX = Cfg::LEADPX;
+  constexpr int NOP = OF ? 2 : 1, RPX = Cfg::RPX, LEADPX = Cfg::LEADPX, CH = Cfg::CH, CHS = Cfg::CHS;
   const int lane = threadIdx.x & 31;
   const unsigned uw = (unsigned)w;
   const unsigned offB = (unsigned)h * (RPX * 16u);       // cB region; the increment region starts at 2 offB
   const int T = w + h - 1 + 2 * (NS - 1);
   const int up = (lane + 31) & 31, dn = (lane + 1) & 31;
-  const int cg = lane >> 3, ce = lane & 7;           // cooperative copies: row group, pixel in chunk
+  const int cg = lane >> CHS, ce = lane & (CH - 1);   // cooperative copies: row group, pixel in chunk
 
   int i0[NB];                  // pixel of sweep 0 at the current step (row j = b * 32 + lane)
   bool mid[NB];
@@ -158,10 +174,10 @@ __device__ __forceinline__ void sor_warp(float* __restrict__ du, unsigned smem, 
   }
   // cooperative copy of chunk q of row `r` (of band b) — this lane moves pixel 8 q + ce
   auto copy_chunk = [&](int b, int r, int q) {
-    const int j = b * 32 + r, px = 8 * q + ce;
+    const int j = b * 32 + r, px = CH * q + ce;
     if (q >= 0 && j < h && px < w) {
       const size_t g = (size_t)j * w + px;
-      const unsigned slot = (unsigned)(j * RPX + (px & (RPX - 1)));
+      const unsigned slot = (unsigned)(j * RPX) + sorw_ring<RPX>((unsigned)px);
       sorw_cp16(smem + slot * 16u, cA + g);
       sorw_cp16(smem + offB + slot * 16u, cB + g);
       if (OF) sorw_cp8(smem + 2u * offB + slot * 8u, du + g * 2);
@@ -172,8 +188,8 @@ __device__ __forceinline__ void sor_warp(float* __restrict__ du, unsigned smem, 
   auto request = [&](int tn, int qmin) {
 #pragma unroll
     for (int b = 0; b < NB; ++b) {
-      const int r = ((tn + LEADPX) & 7) + 8 * cg;
-      const int q = (tn - (b * 32 + r) + LEADPX) >> 3;
+      const int r = ((tn + LEADPX) & (CH - 1)) + CH * cg;
+      const int q = (tn - (b * 32 + r) + LEADPX) >> CHS;
       if (q >= qmin) copy_chunk(b, r, q);
     }
   };
@@ -182,13 +198,13 @@ __device__ __forceinline__ void sor_warp(float* __restrict__ du, unsigned smem, 
     for (int s = 0; s < NS; ++s) {
       const int i = i0[b] - 2 * s;
       if ((unsigned)i < uw) {
-        const unsigned sc = rA[b] + ((unsigned)i & (RPX - 1)) * 16u;
+        const unsigned sc = rA[b] + sorw_ring<RPX>((unsigned)i) * 16u;
         a[b][s] = sorw_lds128(sc);
         c[b][s] = sorw_lds128(sc + offB);
       }
     }
     // sweep 0: right neighbour (j, i0 + 1); pixel 0 also seeds the centre carry
-    if ((unsigned)(i0[b] + 1) < uw) nr0[b] = sorw_lds_du<OF>(rD[b] + ((unsigned)(i0[b] + 1) & (RPX - 1)) * 8u);
+    if ((unsigned)(i0[b] + 1) < uw) nr0[b] = sorw_lds_du<OF>(rD[b] + sorw_ring<RPX>((unsigned)(i0[b] + 1)) * 8u);
     if (i0[b] == 0) cur0[b] = sorw_lds_du<OF>(rD[b]);
   };
   // the fetch that prepares step t1 reads what production steps <= t1 - 3 delivered (first pixel of a chunk: the right
@@ -206,9 +222,9 @@ __device__ __forceinline__ void sor_warp(float* __restrict__ du, unsigned smem, 
   } else {
     // prologue: chunk 0 of every row, plus whatever is due at step 0
 #pragma unroll
-    for (int rr = 0; rr < 8; ++rr) {
+    for (int rr = 0; rr < CH; ++rr) {
 #pragma unroll
-      for (int b = 0; b < NB; ++b) copy_chunk(b, rr + 8 * cg, 0);
+      for (int b = 0; b < NB; ++b) copy_chunk(b, rr + CH * cg, 0);
     }
     request(0, 1);
     asm volatile("cp.async.commit_group;" ::: "memory");
