@@ -30,23 +30,23 @@
 
 // Row streams are cut into chunks of CH pixels.  Chunk q of a row is requested when the row's sweep-0 pixel reaches
 // CH q - LEADPX; at every step the rows that reach such a point are j = (t + LEADPX) mod CH + CH g, 32 / CH per band, so ONE
-// cp.async per stream serves them all: lane = CH g + e copies pixel CH q + e of row j — fully used 64- or 128-byte segments
+// cp.async per stream serves them all: lane = CH g + e copies pixel CH q + e of row j — fully used 128-byte segments
 // per instruction instead of 32 scattered sectors.  The owner lane of a row reads its pixels from the row's ring of RPX
 // pixels one step before use.  The ring must hold the pixels between the last sweep (2 (NS - 1) behind sweep 0) and the
-// chunk being filled (LEADPX + CH ahead): 4 + 4 + 4 = 12 pixels for up to three sweeps.  Shared memory per pair is what
-// bounds the number of resident warps, and the warps are what bounds this kernel (one warp issues an instruction every
-// 2.4 cycles; with 1.4 warps per scheduler the issue slots are 57 % busy, profiles/r02h_hot_details_b1776.txt): the
-// 12-pixel ring (27 KB at 56 rows, 8 pairs per SM) replaced a 16-pixel one (35 KB, 6 pairs per SM).
+// chunk being filled (LEADPX + CH ahead).  Shared memory per pair bounds the resident warps (6 per SM at 56 rows with
+// 16-pixel rings).  A 12-pixel ring of three 4-pixel chunks (-DDISB200_SORW_RING12: 27 KB, 8 pairs per SM) was measured:
+// the SOR stage gains 5 % at batches that fill 8 per SM (2368 pairs: 255.5 k against 251.9 k pairs/s) and LOSES 9 % at the
+// 1776-pair batch (twice as many 64-byte row segments per step); not adopted (profiles/r02i_ring.txt).
 template <int NS>
 struct SorwCfg {
   static constexpr int H = 2 * (NS - 1);             // pixels the last sweep trails sweep 0
-#ifdef DISB200_SORW_RING16                           // A/B build: the 16-pixel ring of round 1 (two 8-pixel chunks)
-  static constexpr int CH = 8, CHS = 3;
-  static constexpr int NCH = NS <= 3 ? 2 : 4;
-#else
+#ifdef DISB200_SORW_RING12                           // A/B build: 12-pixel ring, three 4-pixel chunks (27 KB at 56 rows, 8 pairs / SM)
   static constexpr int CH = NS <= 3 ? 4 : 8;         // pixels per chunk
   static constexpr int CHS = NS <= 3 ? 2 : 3;        // log2(CH)
   static constexpr int NCH = NS <= 3 ? 3 : 4;        // chunk slots per row
+#else
+  static constexpr int CH = 8, CHS = 3;              // 16-pixel ring, two 8-pixel chunks (35 KB at 56 rows, 6 pairs / SM)
+  static constexpr int NCH = NS <= 3 ? 2 : 4;
 #endif
   static constexpr int RPX = NCH * CH;               // ring pixels per row (12: not a power of two, see sorw_ring)
   static constexpr int LEADPX = NS <= 3 ? 4 : 8;     // request distance in pixels
