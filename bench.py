@@ -206,14 +206,16 @@ class CpuArm:
         worker (the reference's default build has no OpenMP: per-pair ms of the core and of pre/post), then `workers`
         of them = the whole host.  `value` = core + pre/post on all cores, median over `windows` windows."""
         w1 = max(1.0, seconds_budget * 0.08)
-        a1, c1 = run_cpu_workers(self, 1, w1, 1)
-        core1 = w1 / max(c1[0], 1)
-        all1 = w1 / max(a1[0], 1)
+        a1, c1, ra1, rc1 = run_cpu_workers(self, 1, w1, 1)
+        core1, all1 = 1.0 / rc1, 1.0 / ra1
         nwin = windows + warm_windows
         wN = max(0.5, seconds_budget * 0.3 / nwin)
-        aN, cN = run_cpu_workers(self, workers, wN, nwin)
-        v_all = statistics.median(aN[warm_windows:]) / wN
-        v_core = statistics.median(cN[warm_windows:]) / wN
+        aN, cN, raN, rcN = run_cpu_workers(self, workers, wN, nwin)
+        if nwin == 1:      # one window: the workers' own rates (exact also when a pair takes longer than the window)
+            v_all, v_core = raN, rcN
+        else:
+            v_all = statistics.median(aN[warm_windows:]) / wN
+            v_core = statistics.median(cN[warm_windows:]) / wN
         return {"value": v_all, "unit": "pairs/s", "cores": workers, "kind": self.kind, "kind_prepost": self.kind_prepost,
                 "core_ms_1t": core1 * 1e3, "prepost_ms_1t": (all1 - core1) * 1e3, "pairs_per_s_1t": 1.0 / all1, "core_pairs_per_s_1t": 1.0 / core1,
                 "core_pairs_per_s": v_core, "core_plus_prepost_pairs_per_s": v_all,
@@ -240,6 +242,7 @@ def run_cpu_workers(arm, workers, window, nwin):
         procs = [subprocess.Popen([sys.executable, os.path.abspath(__file__), "--cpu-worker", npz, repr(start), repr(window), str(nwin)],
                                   stdout=subprocess.PIPE, env=env) for _ in range(workers)]
         n_all, n_core = [0] * nwin, [0] * nwin
+        rate_all = rate_core = 0.0
         for pr in procs:
             out = pr.communicate()[0].decode().strip().splitlines()
             if pr.returncode != 0 or not out:
@@ -249,7 +252,9 @@ def run_cpu_workers(arm, workers, window, nwin):
                 raise RuntimeError("CPU baseline worker started after the common start time; raise the start-up margin")
             n_all = [x + y for x, y in zip(n_all, r["n_all"])]
             n_core = [x + y for x, y in zip(n_core, r["n_core"])]
-    return n_all, n_core
+            rate_all += r["n_all_rate"]
+            rate_core += r["n_core_rate"]
+    return n_all, n_core, rate_all, rate_core
 
 
 def cpu_worker_main(npz, start, window, nwin):
@@ -267,14 +272,18 @@ def cpu_worker_main(npz, start, window, nwin):
             pass
         cnt = [0] * nwin
         end = start + nwin * window
+        done, t = 0, start
         while True:
             fn(i); i += 1
             t = time.time()
-            if t >= end:
+            done += 1
+            if t < end:
+                cnt[int((t - start) / window)] += 1      # a pair counts for the window it finishes in
+            elif done >= 2:                              # slow workloads (seconds per pair): at least two pairs, whatever the window
                 break
-            cnt[int((t - start) / window)] += 1          # a pair counts for the window it finishes in
         res[name] = cnt
-        start = end + 0.5
+        res[name + "_rate"] = done / (t - start)         # pairs/s of this worker over its whole phase
+        start = max(end, t) + 0.5
     res["late"] = late
     print(json.dumps(res))
     return 0
