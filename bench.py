@@ -334,6 +334,7 @@ def main():
     ap.add_argument("--streams", type=int, default=0, help="DisTuning.streams (0 = automatic); 1 for a serialised ncu launch list")
     ap.add_argument("--tv-schedule", type=int, default=0, help="DisTuning.tv_schedule (0 auto, 1 fused, 2 split, 3 general wavefront)")
     ap.add_argument("--antiphase", type=int, default=0, help="DisTuning.antiphase (two sub-batches, refinements in anti-phase)")
+    ap.add_argument("--patch-map", type=int, default=0, help="DisTuning.patch_map (A/B of the inverse-search lane mappings)")
     ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--sor", default="lexicographic", choices=["lexicographic", "redblack"],
@@ -410,8 +411,8 @@ def main():
     dA, dB = hA.cuda(non_blocking=False), hB.cuda(non_blocking=False)
     dOut = torch.empty((nb, h0, w0, nop), dtype=torch.float32, device="cuda")
     torch.cuda.synchronize()
-    if args.streams or args.tv_schedule or args.antiphase:
-        dis.set_tuning(streams=args.streams, tv_schedule=args.tv_schedule, antiphase=args.antiphase)
+    if args.streams or args.tv_schedule or args.antiphase or args.patch_map:
+        dis.set_tuning(streams=args.streams, tv_schedule=args.tv_schedule, antiphase=args.antiphase, patch_map=args.patch_map)
     hd = dis.Handle(p, w0, h0, max_batch=nb, device=local_rank)
 
     def barrier():

@@ -80,7 +80,8 @@ typedef struct DisTuning {
                         the stand-alone one-warp / banded SOR, 3 split with the general CTA wavefront SOR, 4 split with the
                         system assembled inside the one-warp SOR kernel (an experiment that measured 2.9x slower; never automatic) */
   int sorb_max;      /* largest n * bands the banded SOR takes (auto and upper bound: the number of co-resident CTAs) */
-  int patch_map;     /* 1: value-interleaved lane mapping of the inverse search where the block mapping is the default */
+  int patch_map;     /* 1: value-interleaved lane mapping of the inverse search where the block mapping is the default,
+                        and direct global tap loads where the 8x8 grey search stages its tap windows in shared memory */
   int antiphase;     /* 1: with two sub-batches, run their refinements in anti-phase (one assembles while the other solves) */
 } DisTuning;
 int disb200_set_tuning(const DisTuning* t);   /* NULL restores the automatic choices */

@@ -86,8 +86,13 @@ __device__ __forceinline__ void loss(float d, float bsq, float bsq2, float& pd, 
 // bilinear taps of a block row are CW + C consecutive floats and the lower taps of one row are the upper taps of the
 // next, so an iteration loads (RPL + 1)(CW + C) values for RPL CW results instead of four per result:
 // 28 for 18 (12 x 12 grey, 8 lanes) and 48 for 27 (12 x 12 BGR, 16 lanes).
-template <int PSZ, int C, int G, bool OF, int LPR = 0, bool FM = false>
-__global__ void __launch_bounds__(128)   // (capping the column-pair variant at 96 registers for 5 CTAs per SM spills inside the loop: 1.60 -> 2.00 ms)
+//
+// STAGE (8 x 8 grey column-pair mapping, the default; DisTuning::patch_map = 1 selects the direct global loads): the 9 x 9 tap window of each of the warp's eight
+// patches is first copied to shared memory by the WHOLE warp (81 consecutive-per-row floats: 3 cp.async of 4 bytes per lane
+// and patch, each warp instruction covering 32 consecutive window elements = 4 image rows), then every lane reads its 27
+// taps from there.  Same values, same arithmetic: bit-identical.  Measured against the direct loads in DESIGN.md 3.1b.
+template <int PSZ, int C, int G, bool OF, int LPR = 0, bool FM = false, bool STAGE = false>
+__global__ void __launch_bounds__(128, STAGE ? 4 : 1)   // (capping the column-pair variant at 96 registers for 5 CTAs per SM spills inside the loop: 1.60 -> 2.00 ms)
 patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
   constexpr int NV = PSZ * PSZ * C;
   constexpr int VPL = (NV + G - 1) / G;
@@ -103,6 +108,12 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
   static_assert(!BLK || (FULL && !CP && !ROWMAP && CW * LPR == ROWLEN && RPL * (G / LPR) == PSZ && CW * RPL == VPL),
                 "block mapping must tile the patch exactly");
   typedef PSum<G, CP> Sum;
+  static_assert(!STAGE || (CP && PSZ == 8 && G == 4), "tap-window staging is written for the 8 x 8 grey column-pair mapping");
+  // per warp: 8 windows of 81 floats, two per 200-float slab at offsets 0 and 97 (bank-conflict-free tap reads)
+  __shared__ float win_all[STAGE ? 4 * 800 : 1];
+  float* const win = win_all + (STAGE ? (threadIdx.x >> 5) * 800 : 0);
+  const int win_base = ((threadIdx.x >> 3) & 3) * 200 + ((threadIdx.x >> 2) & 1) * 97;
+  const int lane32 = threadIdx.x & 31;
 
   const int lane = threadIdx.x % G;
   const int blk_col = BLK ? (lane % LPR) * CW : 0, blk_row = BLK ? (lane / LPR) * RPL : 0;   // first float / row of the lane's block
@@ -134,6 +145,13 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
     const int row = nn / ROWLEN;
     off[k] = ROWMAP ? k * rowstride + lane : CP ? (k >> 1) * rowstride + 2 * lane + (k & 1)
            : BLK ? (blk_row + k / CW) * rowstride + blk_col + k % CW : row * rowstride + (nn - row * ROWLEN);
+  }
+  // image offset of window element e = lane32 + 32 k (row e / 9, column e % 9 of the 9 x 9 window)
+  int stage_off[3];
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const int e = lane32 + 32 * k;
+    stage_off[k] = (e / 9) * rowstride + e % 9;
   }
   // index of slot k in the row-major patch (pweight layout)
   auto slot_index = [&](int k) {
@@ -265,7 +283,35 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
     const float* qb = qimg + ((iy1 + g.pad + LB) * g.tw + (ix1 + g.pad + LB)) * C;
     float q[VPL];
     Sum qs;
-    if (CP) {
+    if (CP && STAGE) {
+      const int my_off = (int)(qb - qimg) - rowstride - 1;       // the window's first element (row -1, column -1)
+#pragma unroll
+      for (int gp = 0; gp < 8; ++gp) {
+        const float* src = qimg + __shfl_sync(0xffffffffu, my_off, gp * 4);
+        float* dst = win + (gp >> 1) * 200 + (gp & 1) * 97 + lane32;
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+          if (k < 2 || lane32 + 64 < 81) {
+            const unsigned sa = (unsigned)__cvta_generic_to_shared(dst + 32 * k);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(src + stage_off[k]) : "memory");
+          }
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");
+      asm volatile("cp.async.wait_group 0;" ::: "memory");
+      __syncwarp();
+      const float* wp = win + win_base + 2 * lane;
+      float u0 = wp[0], u1 = wp[1], u2 = wp[2];
+#pragma unroll
+      for (int r = 0; r < VPL / 2; ++r) {
+        const float l0 = wp[9 * (r + 1)], l1 = wp[9 * (r + 1) + 1], l2 = wp[9 * (r + 1) + 2];
+        q[2 * r] = w0 * l1 + w1 * l0 + w2 * u1 + w3 * u0;
+        q[2 * r + 1] = w0 * l2 + w1 * l1 + w2 * u2 + w3 * u1;
+        qs.add(2 * r, q[2 * r]);
+        qs.add(2 * r + 1, q[2 * r + 1]);
+        u0 = l0; u1 = l1; u2 = l2;
+      }
+      __syncwarp();                                              // all taps read before the next evaluation overwrites them
+    } else if (CP) {
       // three taps per row serve both columns of the lane; the lower row of one step is the upper row of the next
       const float* p = qb + 2 * lane;
       float u0 = __ldg(p - rowstride - 1), u1 = __ldg(p - rowstride), u2 = __ldg(p - rowstride + 1);
@@ -618,14 +664,14 @@ static void launch_generic(const PatchArgs& a, const LevelGeom& g, const OptCons
   else patch_search_generic_kernel<false, VPL><<<grd, threads, 0, s>>>(a, g, o);
 }
 
-template <int PSZ, int C, int G, int LPR = 0, bool FM = false>
+template <int PSZ, int C, int G, int LPR = 0, bool FM = false, bool STAGE = false>
 static void launch_one(const PatchArgs& a, const LevelGeom& g, const OptConst& o, int n, cudaStream_t s) {
   const int threads = 128, per_block = threads / G;
   dim3 grd((g.nopw * g.ngy + per_block - 1) / per_block, n);
   if (o.mode == DISB200_MODE_OF)
-    patch_search_kernel<PSZ, C, G, true, LPR, FM><<<grd, threads, 0, s>>>(a, g, o);
+    patch_search_kernel<PSZ, C, G, true, LPR, FM, STAGE><<<grd, threads, 0, s>>>(a, g, o);
   else
-    patch_search_kernel<PSZ, C, G, false, LPR, FM><<<grd, threads, 0, s>>>(a, g, o);
+    patch_search_kernel<PSZ, C, G, false, LPR, FM, STAGE><<<grd, threads, 0, s>>>(a, g, o);
 }
 
 bool launch_patch_search(const PatchArgs& a, const LevelGeom& g, const OptConst& o, int n, cudaStream_t s,
@@ -633,13 +679,17 @@ bool launch_patch_search(const PatchArgs& a, const LevelGeom& g, const OptConst&
   if (g.ngy <= 0) return true;   // tiled pair: no patch row of this level belongs to this device
   const int key = o.psz * 10 + o.noc;
   // A/B switch (DisTuning::patch_map = 1): the value-interleaved mapping (value n in lane n % G) wherever the block mapping
-  // is the default.  The 12 x 12 kernels (op3 / op4, compared with a tolerance anyway: different reduction order) also
+  // is the default, and taps read straight from global memory where the staged windows are (8 x 8 grey).  The 12 x 12 kernels (op3 / op4, compared with a tolerance anyway: different reduction order) also
   // contract the interpolation and the two projections into FMAs: op4 588 -> 728 pairs/s.  8 x 8 BGR (op2 of run_*_RGB)
   // keeps separate multiplies and adds: FMA gains 3 % of that kernel there.
   const bool blockmap = o.patch_map != 1;
   switch (key) {
     case 41: launch_one<4, 1, 8>(a, g, o, n, s); break;
-    case 81: launch_one<8, 1, 4>(a, g, o, n, s); break;
+    case 81:
+      // tap windows staged in shared memory: 1.74 -> 1.54 ms at C1, 0.96 -> 0.84 at C3, 0.72 -> 0.63 at C5, 1.35 -> 1.38 at op1
+      if (blockmap) launch_one<8, 1, 4, 0, false, true>(a, g, o, n, s);
+      else launch_one<8, 1, 4>(a, g, o, n, s);
+      break;
     case 121:   // 4 columns x 2 row groups: 6 rows x 3 floats per lane (4 x 1 with 12 rows per lane: 233 registers, 6 % slower)
       if (blockmap) launch_one<12, 1, 8, 4, true>(a, g, o, n, s);
       else launch_one<12, 1, 16>(a, g, o, n, s);

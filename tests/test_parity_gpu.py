@@ -779,3 +779,23 @@ def test_antiphase_sub_batches_give_the_same_bits(gpu, mode, ch, kw):
     finally:
         gpu.set_tuning()
     assert np.array_equal(got, want) and np.array_equal(got2, want[:3])
+
+
+@pytest.mark.parametrize("mode,kw", [(1, {}), (2, {}), (1, dict(usefbcon=1, costfct=1)), (1, dict(costfct=2, patnorm=0, max_iter=24, min_iter=2))])
+def test_staged_tap_windows_give_the_same_bits(gpu, mode, kw):
+    """The 8 x 8 grey inverse search reads its bilinear taps from a shared-memory copy of each patch's 9 x 9 window;
+    DisTuning.patch_map = 1 reads them from global memory.  Same values in the same order: identical output, also where
+    the groups of a warp need different iteration counts (min_iter < max_iter)."""
+    w0, h0, n = 328, 204, 5
+    pairs = [make_pair(h0, w0, channels=1, mode="OF" if mode == 1 else "DE", seed=50 + s)[:2] for s in range(n)]
+    A, B = np.stack([a for a, _ in pairs]), np.stack([b for _, b in pairs])
+    p = gpu.operating_point(2, w0, mode, 1).copy(verbosity=0, sc_f=3, sc_l=0, **kw)
+    with gpu.Handle(p, w0, h0, n) as hd:
+        want = hd.run_host(A, B)
+    try:
+        gpu.set_tuning(patch_map=1)
+        with gpu.Handle(p, w0, h0, n) as hd:
+            got = hd.run_host(A, B)
+    finally:
+        gpu.set_tuning()
+    assert np.array_equal(got, want) and np.abs(want).max() > 0.5
