@@ -195,6 +195,20 @@ int disb200_aggregate_dense(const DisParams* params, int w_l, int h_l, const flo
                             const float* cg_p_iter, const float* cg_pt_iter, const float* cg_pweight, float* flow,
                             int* npatch_out);
 
+/* Allocation-free variant of disb200_aggregate_dense.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Calls no cudaMalloc / cudaFree / allocating routine.  All array arguments are DEVICE pointers on the current
+ * device, laid out as for disb200_aggregate_dense (d_cg_* all NULL: no forward-backward merge); the work is enqueued on
+ * `stream` (a cudaStream_t; NULL = the default stream) and the call returns without synchronising.  The binning scratch of
+ * the merge lives in a static device array of DISB200_STATIC_SCRATCH_BYTES that every GPU loading the library holds until
+ * exit: a level needing more - 3 * cells + npatch ints, cells = ((w_l+2psz)/psz+2) * ((h_l+2psz)/psz+2) - is refused
+ * with DISB200_EINVAL (1 MiB covers e.g. 1920 x 1080 with 8 x 8 patches at 0.4 overlap: 231 k of the 262 k ints).  Every call shares
+ * the array: calls that overlap on one GPU (different streams, or threads) race on it - serialise them. */
+#define DISB200_STATIC_SCRATCH_BYTES (1 << 20)
+int disb200_aggregate_dense_static(const DisParams* params, int w_l, int h_l, const float* d_p_iter, const float* d_pweight,
+                                   const float* d_cg_p_iter, const float* d_cg_pt_iter, const float* d_cg_pweight,
+                                   float* d_flow, void* stream);
+
 /* ---- One frame pair tiled spatially over several GPUs of one node (4K / 8K frames) ----
  * One host thread, ndev devices with peer access (NVLink).  Small pyramid levels are computed redundantly on every
  * device; levels taller than 96 rows are cut into strips of whole 32-row bands: patches are owned by the row of their

@@ -380,6 +380,20 @@ def aggregate_dense(params: DisParams, w_l: int, h_l: int, p_iter, pweight, cg=N
     return out
 
 
+STATIC_SCRATCH_BYTES = 1 << 20     # DISB200_STATIC_SCRATCH_BYTES
+
+
+def aggregate_dense_static(params: DisParams, w_l: int, h_l: int, d_p_iter: int, d_pweight: int, d_cg=None, d_flow: int = 0,
+                           stream: int = 0):
+    """disb200_aggregate_dense_static: the allocation-free variant of aggregate_dense.  Every array argument is a DEVICE
+    address (an int, e.g. torch.Tensor.data_ptr()); d_cg = (p_iter, pt_iter, pweight) addresses or None.  Enqueues on
+    `stream` (a cudaStream_t handle, 0 = default stream) and returns without synchronising."""
+    vp = lambda x: C.c_void_p(x) if x else None
+    cg = tuple(d_cg) if d_cg else (0, 0, 0)
+    _check(lib().disb200_aggregate_dense_static(C.byref(params), w_l, h_l, vp(d_p_iter), vp(d_pweight), vp(cg[0]), vp(cg[1]), vp(cg[2]),
+                                                vp(d_flow), vp(stream)))
+
+
 def patch_count(params: DisParams, w_l: int, h_l: int) -> int:
     n = C.c_int()
     _check(lib().disb200_aggregate_dense(C.byref(params), w_l, h_l, None, None, None, None, None, None, C.byref(n)))

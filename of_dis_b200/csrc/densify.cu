@@ -14,7 +14,9 @@
 // lists are sorted by patch index, and each pixel then visits the (at most) four cells that
 // can reach it, in a fixed cell order.  The result is deterministic; its summation order
 // differs from the reference's global patch order only by fp32 rounding.
-#include "dis_internal.h"
+#include <mutex>
+
+#include "engine.h"
 
 namespace disb200 {
 
@@ -248,3 +250,67 @@ void launch_densify(const DensifyArgs& a, const LevelGeom& g, const OptConst& o,
 }
 
 }  // namespace disb200
+
+// ---------------------------------------------------------------------------------------------------------
+// Allocation-free variant of the AggregateFlowDense cut (disb200_aggregate_dense_static, include/disb200.h).  No
+// counterpart in the reference: added for callers that cannot call cudaMalloc
+// (CUDA graph capture, tight serving loops, harnesses that forbid it).  Inputs and outputs are the CALLER's device
+// arrays; the CSR binning scratch of the forward-backward merge (cell counts, starts, fill cursors, the cell lists)
+// lives in the file-scope device array below - DISB200_STATIC_SCRATCH_BYTES on every GPU that loads the library, until
+// the process exits.  Every call on a device shares that array and finds the previous call's contents in it: the counts
+// are cleared at the start of every call (launch_densify), starts / cursors / lists are fully rewritten before they are
+// read.  Calls that overlap on one GPU (different streams) race on it.
+namespace {
+constexpr size_t kStaticScratchInts = DISB200_STATIC_SCRATCH_BYTES / sizeof(int);
+static __device__ __align__(256) int g_static_scratch[kStaticScratchInts];
+constexpr int kMaxDevices = 64;
+int* g_static_scratch_dev[kMaxDevices] = {};   // device address of g_static_scratch per device (the symbol itself is a host-side stand-in)
+std::mutex g_static_scratch_mu;
+}  // namespace
+
+extern "C" int disb200_aggregate_dense_static(const DisParams* params, int w_l, int h_l, const float* d_p_iter,
+                                              const float* d_pweight, const float* d_cg_p_iter, const float* d_cg_pt_iter,
+                                              const float* d_cg_pweight, float* d_flow, void* stream) {
+  using namespace disb200;
+  if (!params || !d_p_iter || !d_pweight || !d_flow) return fail(DISB200_EINVAL, "null argument");
+  int rc = validate(*params);
+  if (rc) return rc;
+  if (w_l < 1 || h_l < 1) return fail(DISB200_EINVAL, "bad level size");
+  const bool fb = d_cg_p_iter || d_cg_pt_iter || d_cg_pweight;
+  if (fb && !(d_cg_p_iter && d_cg_pt_iter && d_cg_pweight)) return fail(DISB200_EINVAL, "complementary grid: all three arrays or none");
+  DisParams q = *params;
+  q.sc_f = q.sc_l = 0;
+  q.usetvref = 0;
+  q.usefbcon = fb ? 1 : 0;
+  const OptConst o = make_optconst(q);
+  const LevelGeom g = make_levelgeom(q, w_l, h_l, 0);
+  // the layout launch_densify expects: cell_count | cell_start | cell_end (ncell each) | cell_list (npatch)
+  const size_t ncell = (size_t)((g.w + 2 * o.psz) / o.psz + 2) * (size_t)((g.h + 2 * o.psz) / o.psz + 2);
+  const size_t need = fb ? 3 * ncell + (size_t)g.npatch : 0;
+  if (need > kStaticScratchInts)
+    return fail(DISB200_EINVAL, "disb200_aggregate_dense_static: level needs " + std::to_string(need * sizeof(int)) +
+                                    " bytes of scratch (3 * cells + patches ints), the static array holds " +
+                                    std::to_string((size_t)DISB200_STATIC_SCRATCH_BYTES) + " (DISB200_STATIC_SCRATCH_BYTES); use disb200_aggregate_dense");
+  int dev = -1;
+  CU(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return fail(DISB200_EINVAL, "device ordinal out of range");
+  int* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_static_scratch_mu);
+    if (!g_static_scratch_dev[dev]) {   // once per device, with that device current
+      void* ptr = nullptr;
+      CU(cudaGetSymbolAddress(&ptr, g_static_scratch));
+      g_static_scratch_dev[dev] = static_cast<int*>(ptr);
+    }
+    scratch = g_static_scratch_dev[dev];
+  }
+  DensifyArgs a;
+  a.p_iter = d_p_iter; a.pweight = d_pweight;
+  a.cg_p_iter = d_cg_p_iter; a.cg_pt_iter = d_cg_pt_iter; a.cg_pweight = d_cg_pweight;
+  a.flow = d_flow;
+  a.cell_count = scratch; a.cell_start = scratch + ncell; a.cell_end = scratch + 2 * ncell; a.cell_list = scratch + 3 * ncell;
+  LaunchStats st;
+  launch_densify(a, g, o, 1, static_cast<cudaStream_t>(stream), &st);
+  CU(cudaGetLastError());
+  return DISB200_OK;
+}
