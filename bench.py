@@ -334,6 +334,8 @@ def main():
     ap.add_argument("--streams", type=int, default=0, help="DisTuning.streams (0 = automatic); 1 for a serialised ncu launch list")
     ap.add_argument("--tv-schedule", type=int, default=0, help="DisTuning.tv_schedule (0 auto, 1 fused, 2 split, 3 general wavefront)")
     ap.add_argument("--antiphase", type=int, default=0, help="DisTuning.antiphase (two sub-batches, refinements in anti-phase)")
+    ap.add_argument("--set", default="", help="kernel experiments only: DisParams overrides k=v[,k=v] for the GPU arm (needs --no-parity "
+                    "--no-cpu-baseline --no-e2e; the line's config names them)")
     ap.add_argument("--patch-map", type=int, default=0, help="DisTuning.patch_map (A/B of the inverse-search lane mappings)")
     ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -394,6 +396,15 @@ def main():
         p = p.copy(**C4_LINES[args.workload])
     if args.sor == "redblack":
         p = p.copy(sor_mode=dis.SOR_REDBLACK)
+    overrides = {}
+    if args.set:
+        if not (args.no_parity and args.no_cpu_baseline and args.no_e2e):
+            ap.error("--set is for kernel experiments: pass --no-parity --no-cpu-baseline --no-e2e with it")
+        for kv in args.set.split(","):
+            k, v = kv.split("=")
+            overrides[k] = float(v) if "." in v else int(v)
+        p = p.copy(**overrides)
+        config["param_overrides"] = overrides
 
     # ------------------------------------------------------------------ our arm (GPU)
     import torch

@@ -24,9 +24,9 @@
 namespace disb200 {
 
 // sum / NV; for a power-of-two NV the product with the exact reciprocal is the same bits as the division
-template <int NV>
+template <int NV, bool APPROX = false>
 __device__ __forceinline__ float mean_of(float sum) {
-  if ((NV & (NV - 1)) == 0) return sum * (1.0f / (float)NV);
+  if (APPROX || (NV & (NV - 1)) == 0) return sum * (1.0f / (float)NV);
   return sum / (float)NV;
 }
 
@@ -66,6 +66,15 @@ struct PSum {
   }
 };
 
+// Packed fp32 pairs (FMUL2 / FADD2 / FFMA2, sm_100): one issue slot for two values.  ptxas 12.9 contracts a packed multiply
+// feeding a packed add into FFMA2 whatever the rounding suffix and -fmad say, so these are only used where the result is
+// compared with a tolerance (the FM mappings).
+__device__ __forceinline__ float2 f2fma(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ float2 f2mul(float2 a, float2 b) { return __fmul2_rn(a, b); }
+__device__ __forceinline__ float2 f2add(float2 a, float2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ float2 f2sub(float2 a, float2 b) { return __fadd2_rn(a, make_float2(-b.x, -b.y)); }
+__device__ __forceinline__ float2 f2dup(float a) { return make_float2(a, a); }
+
 // LossComputeErrorImage for one value (patch.cpp:221-273): d = query - template
 template <int COST>
 __device__ __forceinline__ void loss(float d, float bsq, float bsq2, float& pd, float& pw) {
@@ -87,12 +96,15 @@ __device__ __forceinline__ void loss(float d, float bsq, float bsq2, float& pd, 
 // next, so an iteration loads (RPL + 1)(CW + C) values for RPL CW results instead of four per result:
 // 28 for 18 (12 x 12 grey, 8 lanes) and 48 for 27 (12 x 12 BGR, 16 lanes).
 //
-// STAGE (8 x 8 grey column-pair mapping, the default; DisTuning::patch_map = 1 selects the direct global loads): the 9 x 9 tap window of each of the warp's eight
+// STAGE (8 x 8 grey column-pair mapping, the default for grid steps <= 4; DisTuning::patch_map = 1 selects the direct global loads): the 9 x 9 tap window of each of the warp's eight
 // patches is first copied to shared memory by the WHOLE warp (81 consecutive-per-row floats: 3 cp.async of 4 bytes per lane
 // and patch, each warp instruction covering 32 consecutive window elements = 4 image rows), then every lane reads its 27
 // taps from there.  Same values, same arithmetic: bit-identical.  Measured against the direct loads in DESIGN.md 3.1b.
 template <int PSZ, int C, int G, bool OF, int LPR = 0, bool FM = false, bool STAGE = false>
-__global__ void __launch_bounds__(128, STAGE ? 4 : 1)   // (capping the column-pair variant at 96 registers for 5 CTAs per SM spills inside the loop: 1.60 -> 2.00 ms)
+// (0 = no occupancy request: an explicit 1 made ptxas spend up to 228 registers on the other mappings, -15 %.  Four CTAs per SM
+//  = 128 registers for the staged 8 x 8 and the packed 12 x 12 grey mappings, which fit without spilling inside the loop;
+//  capping the column-pair variant at 96 registers for 5 CTAs per SM spills there: 1.60 -> 2.00 ms)
+__global__ void __launch_bounds__(128, (STAGE || (PSZ == 12 && C == 1 && G == 8 && FM)) ? 4 : 0)
 patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
   constexpr int NV = PSZ * PSZ * C;
   constexpr int VPL = (NV + G - 1) / G;
@@ -103,10 +115,23 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
   constexpr bool ROWMAP = ROWLEN == G;       // slot k == patch row k
   constexpr bool CP = C == 1 && ROWLEN == 2 * G && FULL;   // slot k == (row k / 2, column 2 lane + k % 2)
   constexpr bool BLK = LPR > 0;
+#ifdef DISB200_FM_EXACT_DIV
+  constexpr bool RCP = false;
+#else
+  constexpr bool RCP = FM;                   // reciprocals instead of divisions in the 2 x 2 solve (FM mappings are tolerance-compared)
+#endif
   constexpr int CW = BLK ? ROWLEN / LPR : 1;            // floats of a row per lane
   constexpr int RPL = BLK ? PSZ / (G / LPR) : 1;        // rows per lane
   static_assert(!BLK || (FULL && !CP && !ROWMAP && CW * LPR == ROWLEN && RPL * (G / LPR) == PSZ && CW * RPL == VPL),
                 "block mapping must tile the patch exactly");
+  // PK (12 x 12 grey, 6 rows x 3 floats per lane): slots k and k + VPL / 2 - rows r and r + 3 of the lane's block - travel
+  // as one packed pair through the interpolation, the residual and the three projections
+#ifdef DISB200_NO_PACKED
+  constexpr bool PK = false;
+#else
+  constexpr bool PK = BLK && FM && C == 1 && RPL == 6 && CW == 3;
+#endif
+  constexpr int HV = VPL / 2;
   typedef PSum<G, CP> Sum;
   static_assert(!STAGE || (CP && PSZ == 8 && G == 4), "tap-window staging is written for the 8 x 8 grey column-pair mapping");
   // per warp: 8 windows of 81 floats, two per 200-float slab at offsets 0 and 97 (bank-conflict-free tap reads)
@@ -172,7 +197,7 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
       s.add(k, t[k]);
     }
     if (o.patnorm > 0 || o.costfct == 10) {
-      const float m = mean_of<NV>(s.total());
+      const float m = mean_of<NV, RCP>(s.total());
 #pragma unroll
       for (int k = 0; k < VPL; ++k) t[k] = val[k] ? t[k] - m : 0.f;
     }
@@ -213,6 +238,8 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
     if (l00 > 0.f) l00 = sqrtf(l00);
   }
 
+  const float il00 = RCP ? 1.0f / l00 : 0.f, il11 = (RCP && OF) ? 1.0f / l11 : 0.f;
+
   // ---- start (patchgrid.cpp:195-211, patch.cpp:97-154) ----
   float p_in0 = 0.f, p_in1 = 0.f;
   if (a.flow_prev) {
@@ -252,7 +279,14 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
     if (!first) {
       ncnt = cnt + 1;
       // delta_p = Hes.llt().solve(delta_p) (patch.cpp:175-182)
-      if (OF) {
+      if (OF && RCP) {       // tolerance-compared mappings: the four divisions of the solve (a serial chain) as products
+        const float y0 = s0 * il00;
+        const float y1 = (s1 - l10 * y0) * il11;
+        const float x1 = y1 * il11;
+        const float x0 = (y0 - l10 * x1) * il00;
+        ndp0 = x0; ndp1 = x1;
+        np0 = p0 - ndp0; np1 = p1 - ndp1;
+      } else if (OF) {
         const float y0 = s0 / l00;
         const float y1 = (s1 - l10 * y0) / l11;
         const float x1 = y1 / l11;
@@ -260,14 +294,14 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
         ndp0 = x0; ndp1 = x1;
         np0 = p0 - ndp0; np1 = p1 - ndp1;
       } else {
-        ndp0 = (s0 / l00) / l00;
+        ndp0 = RCP ? (s0 * il00) * il00 : (s0 / l00) / l00;
         np0 = p0 - ndp0;
         np0 = (a.camlr == 0) ? fminf(np0, 0.f) : fmaxf(np0, 0.f);      // patch.cpp:186-191
       }
       nptx = ptrx + np0;
       if (OF) npty = ptry + np1;
       const float ddx = stx - nptx, ddy = sty - npty;
-      if (sqrtf(ddx * ddx + ddy * ddy) > o.outlierthresh || nptx < g.lb || npty < g.lb || nptx > g.ubw || npty > g.ubh) {
+      if ((RCP ? ddx * ddx + ddy * ddy > o.outlierthresh * o.outlierthresh : sqrtf(ddx * ddx + ddy * ddy) > o.outlierthresh) || nptx < g.lb || npty < g.lb || nptx > g.ubw || npty > g.ubh) {
         np0 = p_in0; np1 = p_in1;                                    // patch.cpp:202-205
         nptx = ptrx + np0;
         if (OF) npty = ptry + np1;
@@ -324,6 +358,28 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
         qs.add(2 * r + 1, q[2 * r + 1]);
         u0 = l0; u1 = l1; u2 = l2;
       }
+    } else if (PK) {
+      const float* p = qb + blk_row * rowstride + blk_col - C;   // left tap of the block's first value
+      const float2 W0 = f2dup(w0), W1 = f2dup(w1), W2 = f2dup(w2), W3 = f2dup(w3);
+      float2 u[CW + C], qs2 = make_float2(0.f, 0.f);
+#pragma unroll
+      for (int i = 0; i < CW + C; ++i) u[i] = make_float2(__ldg(p - rowstride + i), __ldg(p + (RPL / 2 - 1) * rowstride + i));
+#pragma unroll
+      for (int r = 0; r < RPL / 2; ++r) {
+        float2 l[CW + C];
+#pragma unroll
+        for (int i = 0; i < CW + C; ++i) l[i] = make_float2(__ldg(p + r * rowstride + i), __ldg(p + (r + RPL / 2) * rowstride + i));
+#pragma unroll
+        for (int c = 0; c < CW; ++c) {
+          const float2 v = f2fma(W0, l[c + C], f2fma(W1, l[c], f2fma(W2, u[c + C], f2mul(W3, u[c]))));
+          q[r * CW + c] = v.x;
+          q[r * CW + c + HV] = v.y;
+          qs2 = f2add(qs2, v);
+        }
+#pragma unroll
+        for (int i = 0; i < CW + C; ++i) u[i] = l[i];
+      }
+      qs.a0 = qs2.x + qs2.y;
     } else if (BLK) {
       const float* p = qb + blk_row * rowstride + blk_col - C;   // left tap of the block's first value
       float u[CW + C];
@@ -364,7 +420,7 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
       }
     }
     float m = 0.f;
-    if (o.patnorm > 0 || o.costfct == 10) m = mean_of<NV>(qs.total());
+    if (o.patnorm > 0 || o.costfct == 10) m = mean_of<NV, RCP>(qs.total());
     Sum as0, as1, aws;
     float npw[VPL];
 #define DISB200_RESIDUAL(COST, QV)                                 \
@@ -385,7 +441,23 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
       const float qn = sqrtf(s2.total());
       qscale = qn > 0.f ? tnorm / qn : 0.f;
     }
-    if (o.costfct == 0) { DISB200_RESIDUAL(0, (q[k] - m)) }
+    if (PK && o.costfct == 0) {
+      const float2 M = f2dup(m);
+      float2 a0 = make_float2(0.f, 0.f), a1 = a0, aw = a0;
+#pragma unroll
+      for (int k = 0; k < HV; ++k) {
+        const float2 d = f2sub(f2sub(make_float2(q[k], q[k + HV]), M), make_float2(t[k], t[k + HV]));
+        const float2 ad = make_float2(fabsf(d.x), fabsf(d.y));
+        npw[k] = ad.x;
+        npw[k + HV] = ad.y;
+        a0 = f2fma(make_float2(dx[k], dx[k + HV]), d, a0);
+        if (OF) a1 = f2fma(make_float2(dy[k], dy[k + HV]), d, a1);
+        aw = f2add(aw, ad);
+      }
+      as0.a0 = a0.x + a0.y;
+      as1.a0 = a1.x + a1.y;
+      aws.a0 = aw.x + aw.y;
+    } else if (o.costfct == 0) { DISB200_RESIDUAL(0, (q[k] - m)) }
     else if (o.costfct == 10) { DISB200_RESIDUAL(0, (q[k] - m) * qscale) }
     else if (o.costfct == 1) { DISB200_RESIDUAL(1, (q[k] - m)) }
     else { DISB200_RESIDUAL(2, (q[k] - m)) }
@@ -398,7 +470,7 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
       const float dpsq = OF ? ndp0 * ndp0 + ndp1 * ndp1 : ndp0 * ndp0;
       if (ncnt == 1) dpsq_init = dpsq;
       const float mares_old = mares;
-      const float nmares = mean_of<NV>(wsum);
+      const float nmares = mean_of<NV, RCP>(wsum);
       // patch.cpp:290-293; the two rate tests (one division each) only matter once min_iter is reached
       bool go_on = (ncnt < o.max_iter) & (nmares > o.res_thresh);
       if (go_on && ncnt >= o.min_iter)
@@ -686,8 +758,9 @@ bool launch_patch_search(const PatchArgs& a, const LevelGeom& g, const OptConst&
   switch (key) {
     case 41: launch_one<4, 1, 8>(a, g, o, n, s); break;
     case 81:
-      // tap windows staged in shared memory: 1.74 -> 1.54 ms at C1, 0.96 -> 0.84 at C3, 0.72 -> 0.63 at C5, 1.35 -> 1.38 at op1
-      if (blockmap) launch_one<8, 1, 4, 0, false, true>(a, g, o, n, s);
+      // tap windows staged in shared memory where the patch grid is dense (grid step <= 4: overlap 0.4 and up); with a
+      // step of 5 (op1) the direct loads are 10 % faster.  profiles/r02o_stage.txt, r02p_stage_params.txt
+      if (blockmap && g.steps <= 4) launch_one<8, 1, 4, 0, false, true>(a, g, o, n, s);
       else launch_one<8, 1, 4>(a, g, o, n, s);
       break;
     case 121:   // 4 columns x 2 row groups: 6 rows x 3 floats per lane (4 x 1 with 12 rows per lane: 233 registers, 6 % slower)
