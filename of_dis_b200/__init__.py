@@ -332,7 +332,7 @@ class DisTuning(C.Structure):
                 ("antiphase", C.c_int)]
 
 
-TV_AUTO, TV_FUSED, TV_SPLIT, TV_GENERAL, TV_SOLVEF = 0, 1, 2, 3, 4
+TV_AUTO, TV_FUSED, TV_SPLIT, TV_GENERAL, TV_SOLVEF, TV_TEAM = 0, 1, 2, 3, 4, 5
 
 
 def set_tuning(**kw):

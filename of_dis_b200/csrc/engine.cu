@@ -369,7 +369,7 @@ const char* disb200_version(void) { return "disb200 0.1 (sm_100a)"; }
 
 int disb200_set_tuning(const DisTuning* t) {
   if (!t) { g_tuning = DisTuning{0, 0, 0, 0, 0, 0}; return DISB200_OK; }
-  if (t->streams < 0 || t->host_chunk < 0 || t->tv_schedule < 0 || t->tv_schedule > 4 || t->sorb_max < 0 || t->patch_map < 0 || t->patch_map > 1 || t->antiphase < 0 || t->antiphase > 1)
+  if (t->streams < 0 || t->host_chunk < 0 || t->tv_schedule < 0 || t->tv_schedule > 5 || t->sorb_max < 0 || t->patch_map < 0 || t->patch_map > 1 || t->antiphase < 0 || t->antiphase > 1)
     return fail(DISB200_EINVAL, "bad tuning value");
   g_tuning = *t;
   return DISB200_OK;

@@ -133,12 +133,23 @@ __device__ __forceinline__ float2 sorw_shfl(float2 v, int src) {
 // same CTA, which evaluate the linear system of each 8-pixel chunk (system_pixel) straight into its ring slots - the
 // coefficient planes never exist in memory.  sync[0] = number of fetch phases this warp has finished, sync[1 + b] = last
 // production step band b's producer has finished; production step tn holds exactly what request(tn) would have copied.
-template <bool OF, int NS, int NB, bool FUSED = false>
+//
+// TEAM (sor_team_kernel): the NBT = NB bands of the pair are run by NBT WARPS of one CTA, warp b = band b, in lock-step - same
+// step counter, same registers per band, same order of operations as the one-warp schedule, so the result is the same
+// bits.  What the one-warp schedule moves between bands with a shuffle inside the warp (row 32 b - 1 to the first lane of
+// band b, row 32 (b + 1) to the last lane of band b) goes through a double-buffered mailbox in shared memory, one CTA
+// barrier per step.  A step is NS updates instead of NB x NS, and an SM holds NB times as many warps for the same
+// shared memory: twice to three times the warps to hide the latency of the dependent chain with.
+template <bool OF, int NS, int NBT, bool FUSED = false, bool TEAM = false>
 __device__ __forceinline__ void sor_warp(float* __restrict__ du, unsigned smem, const float4* __restrict__ cA,
                                          const float4* __restrict__ cB, int w, int h, float omega,
-                                         volatile int* sync = nullptr) {
+                                         volatile int* sync = nullptr, float2* mbox = nullptr) {
   typedef SorwCfg<NS> Cfg;
   constexpr int NOP = OF ? 2 : 1, RPX = Cfg::RPX, LEADPX = Cfg::LEADPX, CH = Cfg::CH, CHS = Cfg::CHS;
+  constexpr int NB = TEAM ? 1 : NBT;                       // bands of THIS warp
+  const int b0 = TEAM ? (int)(threadIdx.x >> 5) : 0;      // first band of this warp
+  // mailbox [parity][band][top | bottom][sweep]
+  auto mb = [&](int par, int band, int which, int sw) -> float2* { return mbox + ((par * NBT + band) * 2 + which) * NS + sw; };
   const int lane = threadIdx.x & 31;
   const unsigned uw = (unsigned)w;
   const unsigned offB = (unsigned)h * (RPX * 16u);       // cB region; the increment region starts at 2 offB
@@ -156,7 +167,7 @@ __device__ __forceinline__ void sor_warp(float* __restrict__ du, unsigned smem, 
   float2 cur0[NB], nr0[NB];
 #pragma unroll
   for (int b = 0; b < NB; ++b) {
-    const int j = b * 32 + lane;
+    const int j = (b0 + b) * 32 + lane;
     const bool row = j < h;
     i0[b] = row ? -j : -(1 << 28);
     mid[b] = j > 0 && j < h - 1;
@@ -174,7 +185,7 @@ __device__ __forceinline__ void sor_warp(float* __restrict__ du, unsigned smem, 
   }
   // cooperative copy of chunk q of row `r` (of band b) — this lane moves pixel 8 q + ce
   auto copy_chunk = [&](int b, int r, int q) {
-    const int j = b * 32 + r, px = CH * q + ce;
+    const int j = (b0 + b) * 32 + r, px = CH * q + ce;
     if (q >= 0 && j < h && px < w) {
       const size_t g = (size_t)j * w + px;
       const unsigned slot = (unsigned)(j * RPX) + sorw_ring<RPX>((unsigned)px);
@@ -189,7 +200,7 @@ __device__ __forceinline__ void sor_warp(float* __restrict__ du, unsigned smem, 
 #pragma unroll
     for (int b = 0; b < NB; ++b) {
       const int r = ((tn + LEADPX) & (CH - 1)) + CH * cg;
-      const int q = (tn - (b * 32 + r) + LEADPX) >> CHS;
+      const int q = (tn - ((b0 + b) * 32 + r) + LEADPX) >> CHS;
       if (q >= qmin) copy_chunk(b, r, q);
     }
   };
@@ -234,6 +245,21 @@ __device__ __forceinline__ void sor_warp(float* __restrict__ du, unsigned smem, 
 #pragma unroll
   for (int b = 0; b < NB; ++b) fetch(b);
   if (FUSED) { __syncwarp(); if (lane == 0) { __threadfence_block(); sync[0] = 0; } }
+  // TEAM: offer the rows the neighbouring bands read at the next step (the values the one-warp schedule shuffles)
+  auto post = [&](int par) {
+    if (TEAM) {
+      if (lane == 31 && b0 + 1 < NBT) {
+#pragma unroll
+        for (int s = 0; s < NS; ++s) *mb(par, b0 + 1, 0, s) = R[0][s];
+      }
+      if (lane == 0 && b0 > 0) {
+#pragma unroll
+        for (int s = 0; s < NS; ++s) *mb(par, b0 - 1, 1, s) = s > 0 ? R[0][s > 0 ? s - 1 : 0] : nr0[0];
+      }
+      __syncthreads();
+    }
+  };
+  post(0);
 
 #pragma unroll 2
   for (int t = 0; t < T; ++t) {
@@ -252,6 +278,10 @@ __device__ __forceinline__ void sor_warp(float* __restrict__ du, unsigned smem, 
         float2 sb = s > 0 ? R[b][s - 1] : nr0[b];
         if (b + 1 < NB && lane == 0) sb = s > 0 ? R[b + 1 < NB ? b + 1 : b][s - 1] : nr0[b + 1 < NB ? b + 1 : b];
         bot[b][s] = sorw_shfl<OF>(sb, dn);
+        if (TEAM) {
+          if (lane == 0 && b0 > 0) top[b][s] = *mb(t & 1, b0, 0, s);
+          if (lane == 31 && b0 + 1 < NBT) bot[b][s] = *mb(t & 1, b0, 1, s);
+        }
       }
     }
     // ---- updates ----
@@ -300,7 +330,24 @@ __device__ __forceinline__ void sor_warp(float* __restrict__ du, unsigned smem, 
 #pragma unroll
     for (int b = 0; b < NB; ++b) fetch(b);
     if (FUSED) { __syncwarp(); if (lane == 0) { __threadfence_block(); sync[0] = t + 1; } }   // ring slots read by this fetch are free from now on
+    post((t + 1) & 1);
   }
+}
+
+// mailbox bytes of the team schedule (behind the rings)
+__host__ __device__ inline size_t sorw_team_bytes(int ns) { return (size_t)2 * 3 * 2 * ns * sizeof(float2); }
+
+// One CTA of NB warps per frame pair, warp b = band b (TEAM above).
+template <bool OF, int NS, int NB>
+__global__ void __launch_bounds__(32 * NB)
+sor_team_kernel(float* __restrict__ du_all, const float4* __restrict__ cA_all, const float4* __restrict__ cB_all, Dims d,
+                float omega, unsigned mbox_off) {
+  extern __shared__ float4 sorw_smem[];
+  constexpr int NOP = OF ? 2 : 1;
+  const int pair = blockIdx.x;
+  sor_warp<OF, NS, NB, false, true>(du_all + (size_t)pair * d.plane * NOP, (unsigned)__cvta_generic_to_shared(sorw_smem),
+                                    cA_all + (size_t)pair * d.plane, cB_all + (size_t)pair * d.plane, d.w, d.h, omega, nullptr,
+                                    reinterpret_cast<float2*>(reinterpret_cast<char*>(sorw_smem) + mbox_off));
 }
 
 // One warp (= one CTA) per frame pair.

@@ -861,6 +861,7 @@ void varref_level_lanes(TvLane* lanes, int nl, const LevelGeom& g, const DisPara
   int threads = pipelined ? g.h * p.tv_solverit : (g.h < 512 ? g.h : 512);
   threads = ((threads + 31) / 32) * 32;
 
+#define DISB200_TEAM_SELECT (sched == 5)
   struct Plan {
     Dims d;
     dim3 grd, grdc, grd4;
@@ -868,6 +869,8 @@ void varref_level_lanes(TvLane* lanes, int nl, const LevelGeom& g, const DisPara
     float4 *cA, *cB;
     bool done = false, smooth4 = false;
     void (*sorw)(float*, const float4*, const float4*, Dims, float) = nullptr;
+    void (*sort)(float*, const float4*, const float4*, Dims, float, unsigned) = nullptr;   // team schedule: one warp per band, one CTA per pair
+    int sort_threads = 0;
     void (*sorb)(float*, const float4*, const float4*, float4*, float4*, float4*, float4*, unsigned*, unsigned, unsigned, Dims, int, int, int, float) = nullptr;
     size_t sorb_smem = 0;
     // system assembly inside the SOR kernel (sor_fused.cuh): replaces system_kernel + sorw
@@ -954,6 +957,19 @@ void varref_level_lanes(TvLane* lanes, int nl, const LevelGeom& g, const DisPara
       cudaFuncSetAttribute(P.sorb, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)P.sorb_smem);
     }
     if (P.sorw) cudaFuncSetAttribute(P.sorw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sorw_smem);
+    // levels of two or three bands: the same schedule with one WARP per band (sor_team_kernel) - same bits, NS updates per
+    // step and warp instead of NB x NS, NB times the warps per SM for the same shared memory
+    if (P.sorw && g.h > 32 && p.tv_solverit <= 3 && DISB200_TEAM_SELECT) {
+      const int nb = (g.h + 31) / 32;
+      switch (p.tv_solverit) {
+#define DISB200_SORT_CASE(NS_) case NS_: P.sort = nb == 3 ? sor_team_kernel<OF, NS_, 3> : sor_team_kernel<OF, NS_, 2>; break;
+        DISB200_SORT_CASE(1) DISB200_SORT_CASE(2) DISB200_SORT_CASE(3)
+#undef DISB200_SORT_CASE
+        default: break;
+      }
+      P.sort_threads = 32 * nb;
+      if (P.sort) cudaFuncSetAttribute(P.sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sorw_smem + sorw_team_bytes(p.tv_solverit)));
+    }
     // DisTuning::tv_schedule = 4: the one-warp SOR with the system assembled by producer warps of its CTA (sor_fused.cuh;
     // three sweeps).  Bit-identical, removes 64 B per pixel and iteration of HBM traffic - and is 2.9x SLOWER than
     // system_kernel + the stand-alone SOR (C1, 1776 pairs: 8.57 ms against 1.41 + 1.59; profiles/r02f_solvef.txt): one
@@ -1007,7 +1023,8 @@ void varref_level_lanes(TvLane* lanes, int nl, const LevelGeom& g, const DisPara
       ls->launches += 2 * p.tv_solverit - 1;
     } else if (P.solvef) {
       P.solvef<<<n, P.solvef_threads, sorf_smem_bytes(g.h, 3), L.st>>>(P.D, vb.mask, vb.smooth, L.flow, vb.du, P.d, hd3, hg3, p.tv_sor);
-    } else if (P.sorw) P.sorw<<<n, 32, sorw_smem, L.st>>>(vb.du, P.cA, P.cB, P.d, p.tv_sor);
+    } else if (P.sort) P.sort<<<n, P.sort_threads, sorw_smem + sorw_team_bytes(p.tv_solverit), L.st>>>(vb.du, P.cA, P.cB, P.d, p.tv_sor, (unsigned)sorw_smem);
+    else if (P.sorw) P.sorw<<<n, 32, sorw_smem, L.st>>>(vb.du, P.cA, P.cB, P.d, p.tv_sor);
     else if (P.sorb) {
       float4* sorb_xt = reinterpret_cast<float4*>(vb.rhs);
       float4* sorb_xb = sorb_xt + (size_t)n * nbands * p.tv_solverit * g.w;

@@ -156,7 +156,7 @@ def test_tv_paths_agree_bit_for_bit(gpu, port, monkeypatch, mode, ch, w0, h0, le
         fl = -np.abs(fl)
     want = port.varref_level(q, a, b, wl, hl, level, 0, fl)
     try:
-        for sched in (gpu.TV_FUSED, gpu.TV_SPLIT, gpu.TV_GENERAL, gpu.TV_SOLVEF):
+        for sched in (gpu.TV_FUSED, gpu.TV_SPLIT, gpu.TV_GENERAL, gpu.TV_SOLVEF, gpu.TV_TEAM):
             gpu.set_tuning(tv_schedule=sched)
             got = gpu.varref_level(to_dis(gpu, q), a, b, wl, hl, level, 0, fl)
             assert np.array_equal(got, want), (sched, float(np.abs(got - want).max()))
