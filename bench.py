@@ -514,7 +514,7 @@ def main():
                "densify": "densify_kernel (%d launches)" % nl, "varref_prep": "warp_kernel, deriv1_kernel, deriv2_kernel, finish_kernel (%d launches each)" % nl,
                "smooth": "smooth_kernel2 (%d launches)" % n_it, "system": "system_kernel (%d launches)" % n_it,
                "sor": ("tv_fused_kernel (%d launches: diffusivity + system + SOR of a level in one CTA per pair)" % nl) if fused_tv
-                      else "sor_warp_kernel / sor_band_kernel / sor_wavefront_kernel (%d launches)" % n_it,
+                      else "sor_team_kernel / sor_warp_kernel / sor_band_kernel / sor_wavefront_kernel (%d launches)" % n_it,
                "upsample": "upsample_crop_kernel (1 launch)"}
     if fused_tv:
         alg["sor"] += alg["smooth"] + alg["system"]

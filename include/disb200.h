@@ -78,7 +78,9 @@ typedef struct DisTuning {
   int host_chunk;    /* pairs per pipelined chunk of the host-pointer entry points (auto: n / 8, at least 16) */
   int tv_schedule;   /* refinement of a level: 1 fused (one CTA per pair runs the whole level), 2 split with system_kernel and
                         the stand-alone one-warp / banded SOR, 3 split with the general CTA wavefront SOR, 4 split with the
-                        system assembled inside the one-warp SOR kernel (an experiment that measured 2.9x slower; never automatic) */
+                        system assembled inside the one-warp SOR kernel (an experiment that measured 2.9x slower; never automatic),
+                        5 split with the team SOR (one warp per 32-row band, one CTA per pair: what 0 chooses for levels of 33 - 96
+                        rows; 2 keeps one warp per pair there) */
   int sorb_max;      /* largest n * bands the banded SOR takes (auto and upper bound: the number of co-resident CTAs) */
   int patch_map;     /* 1: value-interleaved lane mapping of the inverse search where the block mapping is the default,
                         and direct global tap loads where the 8x8 grey search stages its tap windows in shared memory */

@@ -861,7 +861,7 @@ void varref_level_lanes(TvLane* lanes, int nl, const LevelGeom& g, const DisPara
   int threads = pipelined ? g.h * p.tv_solverit : (g.h < 512 ? g.h : 512);
   threads = ((threads + 31) / 32) * 32;
 
-#define DISB200_TEAM_SELECT (sched == 5)
+#define DISB200_TEAM_SELECT (sched == 0 || sched == 5)   // DisTuning::tv_schedule = 2 keeps one warp per pair (A/B)
   struct Plan {
     Dims d;
     dim3 grd, grdc, grd4;
@@ -914,10 +914,14 @@ void varref_level_lanes(TvLane* lanes, int nl, const LevelGeom& g, const DisPara
       continue;
     }
     const int sched = vb.tv_schedule;   // 0 auto, 1 fused, 2 split, 3 split + general wavefront SOR (DisTuning)
-    // "fused": one CTA per pair runs the whole level (best latency while every pair of the batch is resident,
-    // i.e. up to two CTAs per SM); larger batches take the split path, whose one-warp-per-pair SOR keeps
-    // thousands of pairs resident.  DisTuning::tv_schedule overrides.
-    const bool want_split = p.sor_mode == DISB200_SOR_REDBLACK || (sched ? sched != 1 : n > 2 * 148);
+    // "fused": one CTA per pair runs the whole level; "split": diffusivity / system / SOR kernels per fixed-point
+    // iteration, whose one-warp-per-band SOR keeps thousands of pairs resident.  Measured with the team SOR
+    // (profiles/r02u_fused_vs_team.txt, batches 1 ... 296): optical flow is faster split at EVERY batch size (one C1 pair
+    // 0.83 -> 0.71 ms, 296 pairs 168 k -> 184 k pairs/s), depth - a division per update in the chain - stays faster fused
+    // while every pair of the batch is resident (148 C3 pairs: 130 k fused, 100 k split).  DisTuning::tv_schedule overrides.
+    const bool sorw_level = g.h <= 96 && p.tv_solverit <= 5;   // the one-warp / team SOR takes this level
+    const bool auto_split = (OF && sorw_level) || n > 2 * 148;
+    const bool want_split = p.sor_mode == DISB200_SOR_REDBLACK || (sched ? sched != 1 : auto_split);
     if (!want_split && pipelined && fused_smem <= 100 * 1024) {
       int fthreads = ((g.h * p.tv_solverit + 31) / 32) * 32;
       if (fthreads < 256) fthreads = 256;
