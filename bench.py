@@ -466,12 +466,13 @@ def main():
 
     # per-stage device time (CUDA events on the launching stream) -> roofline of the dominant stage
     hd.set_stage_timing(True)
-    acc = {}
-    for _ in range(3):
+    samples = {}
+    for _ in range(5):
         step()
         hd.sync()
         for k, v in hd.stage_ms().items():
-            acc[k] = acc.get(k, 0.0) + v / 3
+            samples.setdefault(k, []).append(v)
+    acc = {k: float(np.median(v)) for k, v in samples.items()}   # median of 5 passes: one host hiccup does not move a stage
     hd.set_stage_timing(False)
     fused_tv = acc.get("system", 0.0) == 0.0 and acc.get("sor", 0.0) > 0.0     # small batches: one kernel per level
     acc["varref_prep"] = acc.get("varref", 0.0) - acc.get("sor", 0.0) - acc.get("system", 0.0) - acc.get("smooth", 0.0)

@@ -19,9 +19,15 @@
 // sum, so all scalar state is replicated and the loop is uniform inside a group.  Groups of
 // one warp may need different trip counts (min_iter < max_iter): the loop runs until every
 // group of the warp has converged and finished groups stop committing state.
+#include <climits>
+
 #include "dis_internal.h"
 
 namespace disb200 {
+
+#ifndef DISB200_STAGE_MAX_STEP
+#define DISB200_STAGE_MAX_STEP 64
+#endif
 
 // sum / NV; for a power-of-two NV the product with the exact reciprocal is the same bits as the division
 template <int NV, bool APPROX = false>
@@ -139,6 +145,12 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
   float* const win = win_all + (STAGE ? (threadIdx.x >> 5) * 800 : 0);
   const int win_base = ((threadIdx.x >> 3) & 3) * 200 + ((threadIdx.x >> 2) & 1) * 97;
   const int lane32 = threadIdx.x & 31;
+#ifdef DISB200_NO_STAGE_SKIP
+  constexpr bool STAGE_SKIP = false;
+#else
+  constexpr bool STAGE_SKIP = true;
+#endif
+  int win_off = INT_MIN;                                  // origin of the window this group's slot holds (STAGE)
 
   const int lane = threadIdx.x % G;
   const int blk_col = BLK ? (lane % LPR) * CW : 0, blk_row = BLK ? (lane / LPR) * RPL : 0;   // first float / row of the lane's block
@@ -319,19 +331,27 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
     Sum qs;
     if (CP && STAGE) {
       const int my_off = (int)(qb - qimg) - rowstride - 1;       // the window's first element (row -1, column -1)
+      // a window is copied again only when its integer origin moved: late iterations step by fractions of a pixel, and
+      // finished patches sample a fixed position
+      const unsigned moved = STAGE_SKIP ? __ballot_sync(0xffffffffu, my_off != win_off) : 0xffffffffu;
+      win_off = my_off;
+      if (moved) {
 #pragma unroll
-      for (int gp = 0; gp < 8; ++gp) {
-        const float* src = qimg + __shfl_sync(0xffffffffu, my_off, gp * 4);
-        float* dst = win + (gp >> 1) * 200 + (gp & 1) * 97 + lane32;
+        for (int gp = 0; gp < 8; ++gp) {
+          if ((moved >> (4 * gp)) & 1u) {
+            const float* src = qimg + __shfl_sync(0xffffffffu, my_off, gp * 4);
+            float* dst = win + (gp >> 1) * 200 + (gp & 1) * 97 + lane32;
 #pragma unroll
-        for (int k = 0; k < 3; ++k)
-          if (k < 2 || lane32 + 64 < 81) {
-            const unsigned sa = (unsigned)__cvta_generic_to_shared(dst + 32 * k);
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(src + stage_off[k]) : "memory");
+            for (int k = 0; k < 3; ++k)
+              if (k < 2 || lane32 + 64 < 81) {
+                const unsigned sa = (unsigned)__cvta_generic_to_shared(dst + 32 * k);
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(src + stage_off[k]) : "memory");
+              }
           }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
       }
-      asm volatile("cp.async.commit_group;" ::: "memory");
-      asm volatile("cp.async.wait_group 0;" ::: "memory");
       __syncwarp();
       const float* wp = win + win_base + 2 * lane;
       float u0 = wp[0], u1 = wp[1], u2 = wp[2];
@@ -758,9 +778,8 @@ bool launch_patch_search(const PatchArgs& a, const LevelGeom& g, const OptConst&
   switch (key) {
     case 41: launch_one<4, 1, 8>(a, g, o, n, s); break;
     case 81:
-      // tap windows staged in shared memory where the patch grid is dense (grid step <= 4: overlap 0.4 and up); with a
-      // step of 5 (op1) the direct loads are 10 % faster.  profiles/r02o_stage.txt, r02p_stage_params.txt
-      if (blockmap && g.steps <= 4) launch_one<8, 1, 4, 0, false, true>(a, g, o, n, s);
+      // tap windows staged in shared memory; DISB200_STAGE_MAX_STEP bounds the grid step it is used for
+      if (blockmap && g.steps <= DISB200_STAGE_MAX_STEP) launch_one<8, 1, 4, 0, false, true>(a, g, o, n, s);
       else launch_one<8, 1, 4>(a, g, o, n, s);
       break;
     case 121:   // 4 columns x 2 row groups: 6 rows x 3 floats per lane (4 x 1 with 12 rows per lane: 233 registers, 6 % slower)

@@ -140,11 +140,14 @@ def test_varref_tall_level_uses_band_mode(gpu, port):
 
 @pytest.mark.parametrize("mode,ch", [(1, 1), (1, 3), (2, 1), (2, 3)])
 @pytest.mark.parametrize("w0,h0,level,solverit", [(1024, 436, 3, 3), (500, 218, 2, 3), (260, 128, 1, 5), (250, 120, 2, 2), (1920, 1080, 4, 3), (300, 180, 1, 1),
-                                                  (500, 436, 1, 3), (640, 400, 0, 2), (333, 300, 0, 1), (256, 120, 2, 3), (1024, 436, 4, 3)])
+                                                  (500, 436, 1, 3), (640, 400, 0, 2), (333, 300, 0, 1), (256, 120, 2, 3), (1024, 436, 4, 3),
+                                                  (500, 218, 2, 2), (40, 300, 2, 3), (1280, 720, 3, 1)])
 def test_tv_paths_agree_bit_for_bit(gpu, port, monkeypatch, mode, ch, w0, h0, level, solverit):
-    """The three schedules of the lexicographic SOR — one CTA per pair (fused), one warp per pair with shuffles
-    and cp.async row streams (split, used for large batches; levels taller than 96 rows: one warp per band of 32
-    rows, bands chained through tagged boundary rows), general wavefront (old) — are the same iteration."""
+    """The schedules of the lexicographic SOR — one CTA per pair (fused), one warp per pair with shuffles and cp.async
+    row streams (split; levels taller than 96 rows: one warp per band of 32 rows, bands chained through tagged boundary
+    rows), general wavefront (old), system assembled inside the SOR kernel, and the team schedule (one warp per band in
+    one CTA per pair, the automatic choice for 33 - 96 rows: two- and three-band levels with 1, 2 and 3 sweeps, a level
+    ten pixels wide) — are the same iteration."""
     A, B, _ = make_pair(h0, w0, channels=ch, mode="OF" if mode == 1 else "DE", seed=5)
     q = base_orc(mode, ch, sc_f=level, sc_l=level, tv_solverit=solverit)
     W, H, _, _ = port.pad_dims(w0, h0, level)
