@@ -25,6 +25,9 @@
 
 namespace disb200 {
 
+#ifndef DISB200_STAGE12
+#define DISB200_STAGE12 true   // 12 x 12 grey search with staged tap windows (false: loads from global memory, A/B)
+#endif
 #ifndef DISB200_STAGE_MAX_STEP
 #define DISB200_STAGE_MAX_STEP 64
 #endif
@@ -139,10 +142,13 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
 #endif
   constexpr int HV = VPL / 2;
   typedef PSum<G, CP> Sum;
-  static_assert(!STAGE || (CP && PSZ == 8 && G == 4), "tap-window staging is written for the 8 x 8 grey column-pair mapping");
+  static_assert(!STAGE || (CP && PSZ == 8 && G == 4) || (PSZ == 12 && C == 1 && G == 8 && FM && LPR == 4),
+                "tap-window staging is written for the 8 x 8 grey column-pair and the packed 12 x 12 grey mappings");
   // per warp: 8 windows of 81 floats, two per 200-float slab at offsets 0 and 97 (bank-conflict-free tap reads)
-  __shared__ float win_all[STAGE ? 4 * 800 : 1];
-  float* const win = win_all + (STAGE ? (threadIdx.x >> 5) * 800 : 0);
+  constexpr int PKW = PSZ + 1, PKSLOT = PKW * PKW + 24;   // staged 12 x 12 grey: 13 x 13 window, one slot per patch
+  constexpr int WARP_WIN = (PSZ == 12) ? 4 * PKSLOT : 800;
+  __shared__ float win_all[STAGE ? 4 * WARP_WIN : 1];
+  float* const win = win_all + (STAGE ? (threadIdx.x >> 5) * WARP_WIN : 0);
   const int win_base = ((threadIdx.x >> 3) & 3) * 200 + ((threadIdx.x >> 2) & 1) * 97;
   const int lane32 = threadIdx.x & 31;
 #ifdef DISB200_NO_STAGE_SKIP
@@ -378,6 +384,55 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
         qs.add(2 * r + 1, q[2 * r + 1]);
         u0 = l0; u1 = l1; u2 = l2;
       }
+    } else if (PK && STAGE) {
+      // the 13 x 13 tap window of each of the warp's four patches in shared memory, copied only when it moved (op4 runs 128
+      // forced iterations, most of them by fractions of a pixel); taps at fixed offsets from one per-lane pointer
+      const int my_off = (int)(qb - qimg) - rowstride - 1;
+      const unsigned moved = __ballot_sync(0xffffffffu, my_off != win_off);
+      win_off = my_off;
+      if (moved) {
+#pragma unroll
+        for (int gp = 0; gp < 4; ++gp) {
+          if ((moved >> (8 * gp)) & 1u) {
+            const float* src = qimg + __shfl_sync(0xffffffffu, my_off, gp * 8);
+            float* dst = win + gp * PKSLOT;
+#pragma unroll
+            for (int k = 0; k < (PKW * PKW + 31) / 32; ++k) {
+              const int e = lane32 + 32 * k;
+              if (e < PKW * PKW) {
+                const int er = e / PKW;
+                const unsigned sa = (unsigned)__cvta_generic_to_shared(dst + e);
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(src + er * rowstride + (e - er * PKW)) : "memory");
+              }
+            }
+          }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+      }
+      __syncwarp();
+      const float* wp = win + ((threadIdx.x >> 3) & 3) * PKSLOT + blk_row * PKW + blk_col;   // window row 0 = patch row -1
+      const float2 W0 = f2dup(w0), W1 = f2dup(w1), W2 = f2dup(w2), W3 = f2dup(w3);
+      float2 u[CW + C], qs2 = make_float2(0.f, 0.f);
+#pragma unroll
+      for (int i = 0; i < CW + C; ++i) u[i] = make_float2(wp[i], wp[(RPL / 2) * PKW + i]);
+#pragma unroll
+      for (int r = 0; r < RPL / 2; ++r) {
+        float2 l[CW + C];
+#pragma unroll
+        for (int i = 0; i < CW + C; ++i) l[i] = make_float2(wp[(r + 1) * PKW + i], wp[(r + 1 + RPL / 2) * PKW + i]);
+#pragma unroll
+        for (int c = 0; c < CW; ++c) {
+          const float2 v = f2fma(W0, l[c + C], f2fma(W1, l[c], f2fma(W2, u[c + C], f2mul(W3, u[c]))));
+          q[r * CW + c] = v.x;
+          q[r * CW + c + HV] = v.y;
+          qs2 = f2add(qs2, v);
+        }
+#pragma unroll
+        for (int i = 0; i < CW + C; ++i) u[i] = l[i];
+      }
+      qs.a0 = qs2.x + qs2.y;
+      __syncwarp();                                              // all taps read before the next evaluation overwrites them
     } else if (PK) {
       const float* p = qb + blk_row * rowstride + blk_col - C;   // left tap of the block's first value
       const float2 W0 = f2dup(w0), W1 = f2dup(w1), W2 = f2dup(w2), W3 = f2dup(w3);
@@ -783,7 +838,7 @@ bool launch_patch_search(const PatchArgs& a, const LevelGeom& g, const OptConst&
       else launch_one<8, 1, 4>(a, g, o, n, s);
       break;
     case 121:   // 4 columns x 2 row groups: 6 rows x 3 floats per lane (4 x 1 with 12 rows per lane: 233 registers, 6 % slower)
-      if (blockmap) launch_one<12, 1, 8, 4, true>(a, g, o, n, s);
+      if (blockmap) launch_one<12, 1, 8, 4, true, DISB200_STAGE12>(a, g, o, n, s);
       else launch_one<12, 1, 16>(a, g, o, n, s);
       break;
     case 161: launch_one<16, 1, 32>(a, g, o, n, s); break;
