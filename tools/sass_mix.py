@@ -12,7 +12,7 @@ import subprocess
 import sys
 
 HOT = {"patch_search_8x8_grey_of": "patch_search_kernel<8, 1, 4, true, 0, false, true>", "patch_search_8x8_grey_of_direct": "patch_search_kernel<8, 1, 4, true, 0, false, false>",
-       "patch_search_12x12_grey_of_packed": "patch_search_kernel<12, 1, 8, true, 4, true, false>", "sor_warp_of_3sweeps_2bands": "sor_warp_kernel<true, 3, 2>", "sor_team_of_3sweeps_2bands": "sor_team_kernel<true, 3, 2>",
+       "patch_search_12x12_grey_of_packed": "patch_search_kernel<12, 1, 8, true, 4, true, true>", "sor_warp_of_3sweeps_2bands": "sor_warp_kernel<true, 3, 2>", "sor_team_of_3sweeps_2bands": "sor_team_kernel<true, 3, 2>",
        "system_grey_of": "system_kernel<1, true>", "upsample_of": "upsample_crop_kernel<2>", "sor_band_of_3sweeps": "sor_band_kernel<true, 3>",
        "smooth4_of": "smooth_kernel4<true>", "densify_grey_of": "densify_kernel<1, 2>", "tv_solve_fused_grey_of_2bands": "tv_solve_fused_kernel<1, true, 3, 2>"}
 LISTED = ("patch_search_8x8_grey_of", "sor_warp_of_3sweeps_2bands", "sor_team_of_3sweeps_2bands", "system_grey_of")   # full listings
