@@ -29,7 +29,7 @@ namespace disb200 {
 #define DISB200_STAGE12 true   // 12 x 12 grey search with staged tap windows (false: loads from global memory, A/B)
 #endif
 #ifndef DISB200_STAGE_MAX_STEP
-#define DISB200_STAGE_MAX_STEP 64
+#define DISB200_STAGE_MAX_STEP 64   // largest grid step the 8 x 8 grey search is staged for (A/B: 4 was the rule before the window skip)
 #endif
 
 // sum / NV; for a power-of-two NV the product with the exact reciprocal is the same bits as the division
@@ -105,10 +105,12 @@ __device__ __forceinline__ void loss(float d, float bsq, float bsq2, float& pd, 
 // next, so an iteration loads (RPL + 1)(CW + C) values for RPL CW results instead of four per result:
 // 28 for 18 (12 x 12 grey, 8 lanes) and 48 for 27 (12 x 12 BGR, 16 lanes).
 //
-// STAGE (8 x 8 grey column-pair mapping, the default for grid steps <= 4; DisTuning::patch_map = 1 selects the direct global loads): the 9 x 9 tap window of each of the warp's eight
-// patches is first copied to shared memory by the WHOLE warp (81 consecutive-per-row floats: 3 cp.async of 4 bytes per lane
-// and patch, each warp instruction covering 32 consecutive window elements = 4 image rows), then every lane reads its 27
-// taps from there.  Same values, same arithmetic: bit-identical.  Measured against the direct loads in DESIGN.md 3.1b.
+// STAGE (8 x 8 grey column-pair mapping and packed 12 x 12 grey mapping; DisTuning::patch_map = 1 selects the loads from
+// global memory): the tap window of each of the warp's patches - 9 x 9 floats for eight 8 x 8 patches, 13 x 13 for four
+// 12 x 12 patches - is copied to shared memory by the WHOLE warp (4-byte cp.async, each warp instruction covering 32
+// consecutive window elements = 3-4 image rows), and only when the window's integer origin moved since the evaluation
+// before; every lane then reads its taps from there.  Same values, same arithmetic: bit-identical to the direct loads.
+// Measurements: DESIGN.md 3.0 / 3.0c.
 template <int PSZ, int C, int G, bool OF, int LPR = 0, bool FM = false, bool STAGE = false>
 // (0 = no occupancy request: an explicit 1 made ptxas spend up to 228 registers on the other mappings, -15 %.  Four CTAs per SM
 //  = 128 registers for the staged 8 x 8 and the packed 12 x 12 grey mappings, which fit without spilling inside the loop;
@@ -144,7 +146,7 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
   typedef PSum<G, CP> Sum;
   static_assert(!STAGE || (CP && PSZ == 8 && G == 4) || (PSZ == 12 && C == 1 && G == 8 && FM && LPR == 4),
                 "tap-window staging is written for the 8 x 8 grey column-pair and the packed 12 x 12 grey mappings");
-  // per warp: 8 windows of 81 floats, two per 200-float slab at offsets 0 and 97 (bank-conflict-free tap reads)
+  // per warp, 8 x 8: 8 windows of 81 floats, two per 200-float slab at offsets 0 and 97 (bank-conflict-free tap reads)
   constexpr int PKW = PSZ + 1, PKSLOT = PKW * PKW + 24;   // staged 12 x 12 grey: 13 x 13 window, one slot per patch
   constexpr int WARP_WIN = (PSZ == 12) ? 4 * PKSLOT : 800;
   __shared__ float win_all[STAGE ? 4 * WARP_WIN : 1];
