@@ -28,6 +28,9 @@ namespace disb200 {
 #ifndef DISB200_STAGE12
 #define DISB200_STAGE12 true   // 12 x 12 grey search with staged tap windows (false: loads from global memory, A/B)
 #endif
+#ifndef DISB200_STAGE_BGR
+#define DISB200_STAGE_BGR true   // 8 x 8 BGR search with staged tap windows (false: loads from global memory, A/B)
+#endif
 #ifndef DISB200_STAGE_MAX_STEP
 #define DISB200_STAGE_MAX_STEP 64   // largest grid step the 8 x 8 grey search is staged for (A/B: 4 was the rule before the window skip)
 #endif
@@ -115,7 +118,7 @@ template <int PSZ, int C, int G, bool OF, int LPR = 0, bool FM = false, bool STA
 // (0 = no occupancy request: an explicit 1 made ptxas spend up to 228 registers on the other mappings, -15 %.  Four CTAs per SM
 //  = 128 registers for the staged 8 x 8 and the packed 12 x 12 grey mappings, which fit without spilling inside the loop;
 //  capping the column-pair variant at 96 registers for 5 CTAs per SM spills there: 1.60 -> 2.00 ms)
-__global__ void __launch_bounds__(128, (STAGE || (PSZ == 12 && C == 1 && G == 8 && FM)) ? 4 : 0)
+__global__ void __launch_bounds__(128, (C == 1 && (STAGE || (PSZ == 12 && G == 8 && FM))) ? 4 : ((C == 3 && STAGE) ? 3 : 0))
 patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
   constexpr int NV = PSZ * PSZ * C;
   constexpr int VPL = (NV + G - 1) / G;
@@ -144,11 +147,14 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
 #endif
   constexpr int HV = VPL / 2;
   typedef PSum<G, CP> Sum;
-  static_assert(!STAGE || (CP && PSZ == 8 && G == 4) || (PSZ == 12 && C == 1 && G == 8 && FM && LPR == 4),
-                "tap-window staging is written for the 8 x 8 grey column-pair and the packed 12 x 12 grey mappings");
+  static_assert(!STAGE || (CP && PSZ == 8 && G == 4) || (PSZ == 12 && C == 1 && G == 8 && FM && LPR == 4) || (C == 3 && BLK),
+                "tap-window staging is written for the 8 x 8 grey column-pair, the packed 12 x 12 grey and the BGR block mappings");
   // per warp, 8 x 8: 8 windows of 81 floats, two per 200-float slab at offsets 0 and 97 (bank-conflict-free tap reads)
   constexpr int PKW = PSZ + 1, PKSLOT = PKW * PKW + 24;   // staged 12 x 12 grey: 13 x 13 window, one slot per patch
-  constexpr int WARP_WIN = (PSZ == 12) ? 4 * PKSLOT : 800;
+  // staged BGR block mappings: window of (PSZ + 1) rows x (ROWLEN + C) floats, rows padded by one float, slots = 1 mod 32
+  constexpr int BWW = ROWLEN + C, BWWP = BWW + 1, BWH = PSZ + 1, BWN = BWW * BWH;
+  constexpr int BSLOT = BWH * BWWP + (33 - (BWH * BWWP) % 32) % 32;
+  constexpr int WARP_WIN = (C == 3) ? (32 / G) * BSLOT : ((PSZ == 12) ? 4 * PKSLOT : 800);
   __shared__ float win_all[STAGE ? 4 * WARP_WIN : 1];
   float* const win = win_all + (STAGE ? (threadIdx.x >> 5) * WARP_WIN : 0);
   const int win_base = ((threadIdx.x >> 3) & 3) * 200 + ((threadIdx.x >> 2) & 1) * 97;
@@ -457,6 +463,52 @@ patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
         for (int i = 0; i < CW + C; ++i) u[i] = l[i];
       }
       qs.a0 = qs2.x + qs2.y;
+    } else if (BLK && STAGE) {
+      // BGR block mappings: the (PSZ + 1) x (ROWLEN + C) tap window of each of the warp's 32 / G patches in shared memory,
+      // copied only when it moved; the taps of a lane at fixed offsets from one pointer
+      const int my_off = (int)(qb - qimg) - rowstride - C;
+      const unsigned moved = __ballot_sync(0xffffffffu, my_off != win_off);
+      win_off = my_off;
+      if (moved) {
+#pragma unroll
+        for (int gp = 0; gp < 32 / G; ++gp) {
+          if ((moved >> (G * gp)) & 1u) {
+            const float* src = qimg + __shfl_sync(0xffffffffu, my_off, gp * G);
+            float* dst = win + gp * BSLOT;
+#pragma unroll
+            for (int k = 0; k < (BWN + 31) / 32; ++k) {
+              const int e = lane32 + 32 * k;
+              if (e < BWN) {
+                const int er = e / BWW, ec = e - er * BWW;
+                const unsigned sa = (unsigned)__cvta_generic_to_shared(dst + er * BWWP + ec);
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(sa), "l"(src + er * rowstride + ec) : "memory");
+              }
+            }
+          }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+      }
+      __syncwarp();
+      const float* wp = win + (lane32 / G) * BSLOT + blk_row * BWWP + blk_col;   // window row 0 = patch row -1, float 0 = column -1
+      float u[CW + C];
+#pragma unroll
+      for (int i = 0; i < CW + C; ++i) u[i] = wp[i];
+#pragma unroll
+      for (int r = 0; r < RPL; ++r) {
+        float l[CW + C];
+#pragma unroll
+        for (int i = 0; i < CW + C; ++i) l[i] = wp[(r + 1) * BWWP + i];
+#pragma unroll
+        for (int c = 0; c < CW; ++c) {
+          q[r * CW + c] = FM ? fmaf(w0, l[c + C], fmaf(w1, l[c], fmaf(w2, u[c + C], w3 * u[c])))
+                             : w0 * l[c + C] + w1 * l[c] + w2 * u[c + C] + w3 * u[c];
+          qs.add(r * CW + c, q[r * CW + c]);
+        }
+#pragma unroll
+        for (int i = 0; i < CW + C; ++i) u[i] = l[i];
+      }
+      __syncwarp();                                              // all taps read before the next evaluation overwrites them
     } else if (BLK) {
       const float* p = qb + blk_row * rowstride + blk_col - C;   // left tap of the block's first value
       float u[CW + C];
@@ -846,11 +898,11 @@ bool launch_patch_search(const PatchArgs& a, const LevelGeom& g, const OptConst&
     case 161: launch_one<16, 1, 32>(a, g, o, n, s); break;
     case 43: launch_one<4, 3, 8>(a, g, o, n, s); break;
     case 83:    // 4 columns x 2 row groups: 4 rows x 6 floats per lane
-      if (blockmap) launch_one<8, 3, 8, 4, false>(a, g, o, n, s);
+      if (blockmap) launch_one<8, 3, 8, 4, false, DISB200_STAGE_BGR>(a, g, o, n, s);
       else launch_one<8, 3, 32>(a, g, o, n, s);
       break;
     case 123:   // 4 columns x 4 row groups: 3 rows x 9 floats per lane
-      if (blockmap) launch_one<12, 3, 16, 4, true>(a, g, o, n, s);
+      if (blockmap) launch_one<12, 3, 16, 4, true>(a, g, o, n, s);   // (staged: 244 registers, or 140 bytes of spill at three CTAs per SM - left on global loads)
       else launch_one<12, 3, 32>(a, g, o, n, s);
       break;
     case 163: launch_one<16, 3, 32>(a, g, o, n, s); break;
