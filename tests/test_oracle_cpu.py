@@ -463,6 +463,16 @@ def test_bench_reference_arm_prints_the_contract_line():
     assert d["native_so_loaded"] and not any("libdisb200" in x for x in d["native_so_loaded"]), d["native_so_loaded"]
 
 
+def test_bench_parameter_overrides_are_for_kernel_experiments_only():
+    """`bench.py --set k=v` changes the GPU arm's parameters only; it is refused unless the legs that would compare
+    against (or time) the unmodified reference parameters are switched off, so no contract line can carry it by accident."""
+    import subprocess
+    import sys
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--set", "max_iter=3"], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 2 and "--set is for kernel experiments" in r.stderr, (r.returncode, r.stderr[-500:])
+    assert not [l for l in r.stdout.splitlines() if l.startswith("{")]
+
+
 @pytest.mark.parametrize("mode,noc,w0,h0", [(1, 1, 333, 217), (1, 3, 256, 150), (2, 1, 320, 200)])
 def test_cv2_prepost_of_the_cpu_baseline_is_the_oracles(port, mode, noc, w0, h0):
     """bench.py times python-cv2 for the reference's OpenCV steps (oracle/cv2_prepost.py); what it computes must be what
