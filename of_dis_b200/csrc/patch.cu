@@ -31,6 +31,9 @@ namespace disb200 {
 #ifndef DISB200_STAGE_BGR
 #define DISB200_STAGE_BGR true   // 8 x 8 BGR search with staged tap windows (false: loads from global memory, A/B)
 #endif
+#ifndef DISB200_STAGE_BGR12
+#define DISB200_STAGE_BGR12 false   // 12 x 12 BGR search staged: 244 registers (two CTAs per SM); see DESIGN.md 3.0
+#endif
 #ifndef DISB200_STAGE_MAX_STEP
 #define DISB200_STAGE_MAX_STEP 64   // largest grid step the 8 x 8 grey search is staged for (A/B: 4 was the rule before the window skip)
 #endif
@@ -118,7 +121,7 @@ template <int PSZ, int C, int G, bool OF, int LPR = 0, bool FM = false, bool STA
 // (0 = no occupancy request: an explicit 1 made ptxas spend up to 228 registers on the other mappings, -15 %.  Four CTAs per SM
 //  = 128 registers for the staged 8 x 8 and the packed 12 x 12 grey mappings, which fit without spilling inside the loop;
 //  capping the column-pair variant at 96 registers for 5 CTAs per SM spills there: 1.60 -> 2.00 ms)
-__global__ void __launch_bounds__(128, (C == 1 && (STAGE || (PSZ == 12 && G == 8 && FM))) ? 4 : ((C == 3 && STAGE) ? 3 : 0))
+__global__ void __launch_bounds__(128, (C == 1 && (STAGE || (PSZ == 12 && G == 8 && FM))) ? 4 : ((C == 3 && STAGE && PSZ == 8) ? 3 : 0))
 patch_search_kernel(PatchArgs a, LevelGeom g, OptConst o) {
   constexpr int NV = PSZ * PSZ * C;
   constexpr int VPL = (NV + G - 1) / G;
@@ -902,7 +905,7 @@ bool launch_patch_search(const PatchArgs& a, const LevelGeom& g, const OptConst&
       else launch_one<8, 3, 32>(a, g, o, n, s);
       break;
     case 123:   // 4 columns x 4 row groups: 3 rows x 9 floats per lane
-      if (blockmap) launch_one<12, 3, 16, 4, true>(a, g, o, n, s);   // (staged: 244 registers, or 140 bytes of spill at three CTAs per SM - left on global loads)
+      if (blockmap) launch_one<12, 3, 16, 4, true, DISB200_STAGE_BGR12>(a, g, o, n, s);
       else launch_one<12, 3, 32>(a, g, o, n, s);
       break;
     case 163: launch_one<16, 3, 32>(a, g, o, n, s); break;
